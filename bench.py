@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""bench.py — decode tokens/s of the pipeline-sharded GPT-2 hot path on N B200s.
+
+Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]` prints ONE JSON
+line (rank 0).  A "step" is one greedy generation request of the workload: B prompts of P
+tokens -> n_new tokens each (BASELINE.json configs[1]: GPT-2 124M, batch 1, 128 new tokens,
+random-init seeded weights, synthetic prompt).  N GPUs = N pipeline stages; with N > 1 the
+job carries N sequences (one micro-batch per stage in flight), i.e. weak scaling.
+
+ value : generated tokens/s with the prompt already resident in HBM (device time, CUDA events)
+ e2e   : the same through the public API with HOST buffers (pinned prompt H2D + ids D2H
+         inside the timed region)
+ roofline / cpu_baseline : see DESIGN.md §Measurement.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: (preset, B per stream, P, n_new, weight seed)
+    "gpt2-124m-b1-p32-n128": ("gpt2", 1, 32, 128, 1234),
+}
+DEFAULT_WORKLOAD = "gpt2-124m-b1-p32-n128"
+METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
+
+
+def synthetic_prompts(B, P, vocab, seed=7):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randint(0, vocab, (B, P), generator=g, dtype=torch.int32)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def algorithmic_bytes_per_step(dims, B, t_ctx, n_stages, esz=2):
+    """weights once + KV read + KV write + stage hops, per decode step."""
+    H, L, V = dims.n_embd, dims.n_layer, dims.vocab_size
+    w = esz * (L * (12 * H * H + 13 * H) + V * H + 2 * H)
+    kv = esz * 2 * L * H * B * t_ctx + esz * 2 * L * H * B
+    hops = 4 * B * H * (n_stages - 1)
+    return w + kv + hops
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------
+def cpu_reference_tokens_per_s(preset, seed, B, P, n_tokens, full_path_probe=False):
+    """The reference's path on the host cores: full recompute of Shard A then Shard B per token
+    (server.py:169-206) via the oracle port, compute only (no HTTP/JSON).  Returns
+    (tokens/s, p50 s/token, info)."""
+    from oracle import gpt2_oracle as O
+    dims = O.PRESETS[preset]
+    w = O.init_weights(dims, seed, "hf")
+    ids = synthetic_prompts(B, P, dims.vocab_size).long()
+    split = O.split_layers(dims.n_layer, 2)[0][1]
+    lat = []
+    with torch.no_grad():
+        for _ in range(n_tokens):
+            t0 = time.perf_counter()
+            hidden = O.shard_a_forward(w, dims, ids, split)
+            logits = O.shard_b_forward(w, dims, hidden, split)
+            nxt = O.greedy_select(logits[:, -1])
+            ids = torch.cat([ids, nxt.unsqueeze(1)], dim=1)
+            lat.append(time.perf_counter() - t0)
+    info = {}
+    if full_path_probe:
+        # one token of the reference's real wire format: hidden and ALL-position logits as JSON
+        t0 = time.perf_counter()
+        h_json = json.dumps({"hidden_states": hidden.tolist()})
+        hidden2 = torch.tensor(json.loads(h_json)["hidden_states"], dtype=torch.float32)
+        l_json = json.dumps({"logits": logits.tolist()})
+        _ = json.loads(l_json)["logits"][0][-1]
+        info["json_overhead_s_per_token"] = round(time.perf_counter() - t0, 3)
+        info["json_T"] = int(hidden2.shape[1])
+    total = sum(lat)
+    return B * n_tokens / total, statistics.median(lat), info
+
+
+def run_reference(args):
+    preset, B, P, n_new, seed = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+    cores = torch.get_num_threads()
+    sample = min(n_new, 8)
+    for _ in range(args.warmup):
+        cpu_reference_tokens_per_s(preset, seed, B, P, 2)
+    vals, lats = [], []
+    t_all = time.perf_counter()
+    info = {}
+    for i in range(args.steps):
+        v, p50, inf = cpu_reference_tokens_per_s(preset, seed, B, P, sample, full_path_probe=(i == 0))
+        info.update(inf)
+        vals.append(v)
+        lats.append(p50)
+    wall = time.perf_counter() - t_all
+    value = B * sample * args.steps / sum(B * sample / v for v in vals)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": "tokens/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1000 * wall / args.steps, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "model": preset, "batch": B, "prompt": P, "new_tokens": n_new},
+        "p50_token_ms": round(1000 * statistics.median(lats), 3),
+        "cpu_baseline": {"value": round(value, 3), "unit": "tokens/s", "cores": cores, "kind": "port",
+                         "sample": f"first {sample} of {n_new} new tokens per step, full recompute of both shards "
+                                   f"per token (server.py:169-181), compute only (no HTTP/JSON); {info}"},
+        "e2e": {"value": round(value, 3), "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------
+def run_b200(args):
+    import llm_sharding_demo_b200 as L
+    from llm_sharding_demo_b200.pipeline import PipelineRunner
+
+    preset, B, P, n_new, seed = WORKLOADS[args.workload]
+    dims = L.PRESETS[preset]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun for N>1)"
+    torch.cuda.set_device(local)
+    dtype = L.GP_BF16 if args.dtype == "bf16" else L.GP_F32
+    runner = PipelineRunner(dims, seed=seed, dtype=dtype, batch_per_stream=B, max_ctx=P + n_new,
+                            rank=rank, world=world, device=local)
+    n_streams = runner.n_streams            # = world: one micro-batch per stage in flight
+    prompts = synthetic_prompts(B * n_streams, P, dims.vocab_size).pin_memory()
+
+    for _ in range(args.warmup):
+        runner.generate(prompts, n_new)
+    runner.barrier()
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    # --- device-timed steps (value)
+    dev_ms, step_tok_ms, launches = [], [], 0
+    for _ in range(args.steps):
+        out, tm = runner.generate(prompts, n_new, timings=True)
+        dev_ms.append(tm["prefill_ms"] + tm["decode_ms"])
+        step_tok_ms += tm["step_ms"]
+        launches += tm["launches"]
+    runner.barrier()
+    torch.cuda.synchronize()
+    # --- end-to-end steps through the public API, host buffers, wall clock
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = runner.generate(prompts, n_new)
+    torch.cuda.synchronize()
+    runner.barrier()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+
+    dev_total_ms = runner.max_over_ranks(sum(dev_ms))
+    e2e_s = runner.max_over_ranks(e2e_s)
+    if rank != 0:
+        return
+    tokens_per_step = B * n_streams * n_new
+    value = tokens_per_step * args.steps / (dev_total_ms / 1000.0)
+    e2e = tokens_per_step * args.steps / e2e_s
+    p50_tok_ms = statistics.median(step_tok_ms) if step_tok_ms else None
+
+    # roofline of the decode step (HBM-bound): algorithmic bytes per step / measured step time
+    peak, peak_kind = measured_peaks()
+    t_ctx = P + n_new // 2
+    bytes_step = algorithmic_bytes_per_step(dims, B, t_ctx, world, 2 if dtype == L.GP_BF16 else 4)
+    roof = None
+    if p50_tok_ms:
+        per_stage_bytes = bytes_step / world
+        achieved = per_stage_bytes / (p50_tok_ms / 1000.0 / world) / 1e9 if world > 1 else bytes_step / (p50_tok_ms / 1000.0) / 1e9
+        roof = {"bound": "hbm", "kernel": "decode step (all launches of one token; dominated by gemv_kernel + lmhead_argmax_kernel)",
+                "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": None,
+                "algorithmic_bytes_per_launch": int(bytes_step)}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+        sample = 16
+        v, p50, info = cpu_reference_tokens_per_s(preset, seed, B, P, sample)
+        cpu = {"value": round(v, 3), "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
+               "sample": f"first {sample} of {n_new} new tokens of the same prompt, full recompute per token, "
+                         f"compute only (no HTTP/JSON), p50 {1000 * p50:.1f} ms/token"}
+
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(dev_total_ms / args.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": args.workload, "model": preset, "batch_per_stream": B, "streams": n_streams,
+                   "prompt": P, "new_tokens": n_new, "stages": world,
+                   "l2": "inputs larger than L2: %.0f MB of weights are streamed every token" % (bytes_step / 1e6)},
+        "p50_token_ms": None if p50_tok_ms is None else round(p50_tok_ms, 4),
+        "decode_tokens_per_s": None if not p50_tok_ms else round(B * n_streams * 1000.0 / p50_tok_ms, 1),
+        "e2e": {"value": round(e2e, 2), "unit": "tokens/s", "h2d_bytes_per_step": int(prompts.numel() * 4),
+                "d2h_bytes_per_step": int(B * n_streams * (P + n_new) * 4)},
+        "gpu_launches": int(launches),
+        "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3   # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,686 @@
+// The pipeline-stage engine behind the C ABI of include/gpt2pipe.h: owns weights, KV cache
+// and workspaces in HBM and sequences the sm_100a kernels for prefill, cached decode and the
+// device-resident greedy loop.  Host-side C++ only; every kernel lives in k_*.cu / gemm_*.cu.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+using namespace gp;
+
+namespace {
+thread_local std::string g_err;
+
+void set_err(gp_engine* e, const char* fmt, ...);
+
+struct LayerW {
+  float *ln1_g = nullptr, *ln1_b = nullptr, *attn_b = nullptr, *proj_b = nullptr;
+  float *ln2_g = nullptr, *ln2_b = nullptr, *fc_b = nullptr, *mproj_b = nullptr;
+  void *attn_w = nullptr, *proj_w = nullptr, *fc_w = nullptr, *mproj_w = nullptr;  // [N,K] in cfg.dtype
+  void *kc = nullptr, *vc = nullptr;  // [max_batch, nh, max_ctx, d]
+};
+}  // namespace
+
+struct gp_engine {
+  gp_config cfg{};
+  int H = 0, nh = 0, d = 0, V = 0, F = 0, L = 0;
+  size_t esz = 4;  // bytes per storage element
+  std::vector<LayerW> layers;
+  void *wte = nullptr, *wpe = nullptr;
+  float *lnf_g = nullptr, *lnf_b = nullptr;
+  std::set<std::string> required, loaded;
+  std::vector<void*> allocs;
+  int32_t* lens = nullptr;
+  // workspaces
+  float* h = nullptr;       // [max_tokens, H]   residual stream
+  void* xa = nullptr;       // [max_tokens, H]   LN / attention output feeding a GEMM
+  void* qkv = nullptr;      // [max_tokens, 3H]
+  void* act = nullptr;      // [max_tokens, 4H]
+  float* q = nullptr;       // [max_batch, H]    decode query
+  float* attn_f = nullptr;  // [max_batch, H]    decode attention output (GEMV path)
+  float* act_f = nullptr;   // [max_batch, 4H]   decode GELU output (GEMV path)
+  float* hlast = nullptr;   // [max_batch, H]
+  void* lm_scratch = nullptr;
+  float* stage = nullptr;
+  size_t stage_floats = 0;
+  // generate state
+  int32_t* seq = nullptr;      // [max_batch, seq_stride]
+  int32_t* prompt = nullptr;   // [max_batch * n_positions]
+  int32_t* mailbox = nullptr;  // [max_batch] next token ids
+  int seq_stride = 0;
+  cudaStream_t stream = nullptr;
+  std::map<int, cudaGraphExec_t> decode_graphs;  // keyed by batch
+  std::map<int, int64_t> decode_graph_launches;
+  std::vector<cudaEvent_t> events;
+  std::string err;
+  int64_t launches = 0;
+};
+
+namespace {
+
+void set_err(gp_engine* e, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  if (e) e->err = buf;
+}
+
+#define CK(e, call)                                                                          \
+  do {                                                                                       \
+    cudaError_t _c = (call);                                                                 \
+    if (_c != cudaSuccess) {                                                                 \
+      set_err(e, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_c), __FILE__, __LINE__); \
+      return _c == cudaErrorMemoryAllocation ? GP_ENOMEM : GP_ECUDA;                         \
+    }                                                                                        \
+  } while (0)
+// a kernel launch: counted, checked
+#define LAUNCH(e, call)  \
+  do {                   \
+    CK(e, call);         \
+    ++(e)->launches;     \
+  } while (0)
+
+int dev_alloc(gp_engine* e, void** p, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  CK(e, cudaMalloc(p, bytes));
+  e->allocs.push_back(*p);
+  return GP_OK;
+}
+#define ALLOC(e, ptr, bytes)                                    \
+  do {                                                          \
+    int _r = dev_alloc(e, reinterpret_cast<void**>(&(ptr)), (bytes)); \
+    if (_r != GP_OK) return _r;                                 \
+  } while (0)
+
+bool bf(const gp_engine* e) { return e->cfg.dtype == GP_BF16; }
+
+// GEMM dispatch: tcgen05 when the shape allows and the storage type is bf16, else SIMT tiles
+cudaError_t gemm(gp_engine* e, const void* A, int lda, const void* Wt, const float* bias, const float* residual,
+                 int ldr, void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s) {
+  if (bf(e) && !(e->cfg.flags & GP_FLAG_NO_TCGEN05) && gemm_tc_supported(M, N, K) && lda == K)
+    return launch_gemm_tc(A, lda, Wt, bias, residual, ldr, out, ldo, M, N, K, flags, s);
+  return launch_gemm_simt(A, lda, Wt, bias, residual, ldr, out, ldo, M, N, K, flags, e->cfg.dtype, s);
+}
+
+// ln_f + lm_head + argmax over rows x[B,H] in chunks of kGemvMaxBatch
+int run_lm_head(gp_engine* e, const float* x, int ldx, int B, int slot0, float* logits, int32_t* next_ids,
+                int32_t* lens, int32_t* seq, cudaStream_t s) {
+  for (int c = 0; c < B; c += kGemvMaxBatch) {
+    LmheadParams p;
+    p.x = x + (size_t)c * ldx; p.ldx = ldx;
+    p.ln_g = e->lnf_g; p.ln_b = e->lnf_b; p.eps = e->cfg.ln_eps;
+    p.wte = e->wte;
+    p.B = (B - c < kGemvMaxBatch) ? B - c : kGemvMaxBatch;
+    p.V = e->V; p.H = e->H;
+    p.ids_out = (next_ids ? next_ids : e->mailbox) + c;
+    p.logits_out = logits ? logits + (size_t)c * e->V : nullptr; p.ldl = e->V;
+    p.scratch = e->lm_scratch;
+    p.lens = lens; p.slot0 = slot0 + c;
+    p.seq = seq ? seq + (size_t)c * e->seq_stride : nullptr; p.seq_stride = e->seq_stride;
+    LAUNCH(e, launch_lmhead_argmax(p, e->cfg.dtype, s));
+  }
+  return GP_OK;
+}
+
+int check_ready(gp_engine* e) {
+  if (e->loaded.size() != e->required.size()) {
+    for (auto& n : e->required)
+      if (!e->loaded.count(n)) {
+        set_err(e, "weight '%s' has not been loaded (%zu of %zu present)", n.c_str(), e->loaded.size(),
+                e->required.size());
+        return GP_ESTATE;
+      }
+  }
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------------------- prefill
+int prefill_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B, int T, int slot0, int use_cache,
+                 float* hidden_out, float* logits, int logits_all, int32_t* next_ids, int32_t* seq_for_generate,
+                 cudaStream_t s) {
+  const gp_config& c = e->cfg;
+  const int H = e->H, F = e->F, M = B * T;
+  if (B <= 0 || T <= 0) { set_err(e, "prefill: B and T must be positive (B=%d T=%d)", B, T); return GP_EINVAL; }
+  if (T > c.n_positions) {
+    set_err(e, "prefill: T=%d exceeds n_positions=%d (the reference would index past wpe)", T, c.n_positions);
+    return GP_EINVAL;
+  }
+  if ((int64_t)M > (int64_t)c.max_tokens) { set_err(e, "prefill: B*T=%d exceeds max_tokens=%d", M, c.max_tokens); return GP_EINVAL; }
+  if (use_cache && (slot0 < 0 || slot0 + B > c.max_batch || T > c.max_ctx)) {
+    set_err(e, "prefill: slots [%d,%d) / T=%d outside cache (max_batch=%d max_ctx=%d)", slot0, slot0 + B, T,
+            c.max_batch, c.max_ctx);
+    return GP_EINVAL;
+  }
+  if (c.has_embed ? ids == nullptr : hidden_in == nullptr) { set_err(e, "prefill: missing input pointer"); return GP_EINVAL; }
+  if (!c.has_head && hidden_out == nullptr) { set_err(e, "prefill: hidden_out is NULL"); return GP_EINVAL; }
+  int r = check_ready(e);
+  if (r != GP_OK) return r;
+
+  const bool obf = bf(e);
+  const uint32_t oflag = obf ? GP_OUT_BF16 : 0u;
+  if (c.has_embed) {
+    LAUNCH(e, launch_embed(ids, nullptr, 0, T, nullptr, 0, e->wte, e->wpe, e->h, M, H, e->V, c.n_positions, c.dtype, s));
+  } else {
+    CK(e, cudaMemcpyAsync(e->h, hidden_in, (size_t)M * H * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  }
+  for (int li = 0; li < e->L; ++li) {
+    LayerW& w = e->layers[li];
+    LAUNCH(e, launch_layernorm(e->h, H, w.ln1_g, w.ln1_b, e->xa, obf, M, H, c.ln_eps, s));
+    LAUNCH(e, gemm(e, e->xa, H, w.attn_w, w.attn_b, nullptr, 0, e->qkv, 3 * H, M, 3 * H, H, oflag, s));
+    if (use_cache) LAUNCH(e, launch_kv_scatter(e->qkv, w.kc, w.vc, B, T, slot0, H, e->nh, e->d, c.max_ctx, c.dtype, s));
+    LAUNCH(e, launch_attn_prefill(e->qkv, e->xa, B, T, e->nh, e->d, c.dtype, s));
+    LAUNCH(e, gemm(e, e->xa, H, w.proj_w, w.proj_b, e->h, H, e->h, H, M, H, H, 0u, s));
+    LAUNCH(e, launch_layernorm(e->h, H, w.ln2_g, w.ln2_b, e->xa, obf, M, H, c.ln_eps, s));
+    LAUNCH(e, gemm(e, e->xa, H, w.fc_w, w.fc_b, nullptr, 0, e->act, F, M, F, H, oflag | GP_EPI_GELU, s));
+    LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, e->h, H, e->h, H, M, H, F, 0u, s));
+  }
+  if (use_cache) LAUNCH(e, launch_set_lens(e->lens, slot0, B, T, 0, s));
+  if (!c.has_head) {
+    CK(e, cudaMemcpyAsync(hidden_out, e->h, (size_t)M * H * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    return GP_OK;
+  }
+  if (logits && logits_all) {
+    // ShardB semantics: logits for ALL T rows (server.py:101-102)
+    LAUNCH(e, launch_layernorm(e->h, H, e->lnf_g, e->lnf_b, e->xa, obf, M, H, c.ln_eps, s));
+    LAUNCH(e, gemm(e, e->xa, H, e->wte, nullptr, nullptr, 0, logits, e->V, M, e->V, H, 0u, s));
+  }
+  if (next_ids || seq_for_generate || (logits && !logits_all)) {
+    LAUNCH(e, launch_gather_last(e->h, e->hlast, B, T, H, s));
+    // generate: the first new token goes to seq[b][len] with len (= T) unchanged
+    r = run_lm_head(e, e->hlast, H, B, slot0, (logits && !logits_all) ? logits : nullptr, next_ids, nullptr, nullptr, s);
+    if (r != GP_OK) return r;
+  }
+  return GP_OK;
+}
+
+// -------------------------------------------------------------------------------- decode
+int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B, int slot0, float* hidden_out,
+                float* logits, int32_t* next_ids, int32_t* seq, cudaStream_t s) {
+  const gp_config& c = e->cfg;
+  const int H = e->H, F = e->F;
+  if (B <= 0 || slot0 < 0 || slot0 + B > c.max_batch) {
+    set_err(e, "decode: slots [%d,%d) outside cache (max_batch=%d)", slot0, slot0 + B, c.max_batch);
+    return GP_EINVAL;
+  }
+  if (c.has_embed ? ids == nullptr : hidden_in == nullptr) { set_err(e, "decode: missing input pointer"); return GP_EINVAL; }
+  if (!c.has_head && hidden_out == nullptr) { set_err(e, "decode: hidden_out is NULL"); return GP_EINVAL; }
+  int r = check_ready(e);
+  if (r != GP_OK) return r;
+
+  const bool use_gemv = gemv_supported(B, F);
+  const bool obf = bf(e);
+  const uint32_t oflag = obf ? GP_OUT_BF16 : 0u;
+
+  const float* cur = hidden_in;  // current residual stream [B,H]
+  if (c.has_embed) {
+    LAUNCH(e, launch_embed(ids, nullptr, 0, 1, e->lens, slot0, e->wte, e->wpe, e->h, B, H, e->V, c.n_positions, c.dtype, s));
+    cur = e->h;
+  }
+  for (int li = 0; li < e->L; ++li) {
+    LayerW& w = e->layers[li];
+    const bool last = (li == e->L - 1);
+    float* dst = (last && !c.has_head) ? hidden_out : e->h;
+    if (use_gemv) {
+      GemvParams p;
+      // ln_1 + c_attn, q -> e->q, k/v -> cache[pos = len]
+      p.x = cur; p.ldx = H; p.Wt = w.attn_w; p.bias = w.attn_b; p.B = B; p.N = 3 * H; p.K = H;
+      p.ln_g = w.ln1_g; p.ln_b = w.ln1_b; p.eps = c.ln_eps; p.mode = 1; p.q_out = e->q; p.kcache = w.kc;
+      p.vcache = w.vc; p.lens = e->lens; p.slot0 = slot0; p.H = H; p.nh = e->nh; p.d = e->d; p.max_ctx = c.max_ctx;
+      LAUNCH(e, launch_gemv(p, c.dtype, s));
+      LAUNCH(e, launch_attn_decode(e->q, w.kc, w.vc, e->lens, 1, slot0, e->attn_f, false, B, e->nh, e->d, c.max_ctx, c.dtype, s));
+      // attention c_proj + residual
+      GemvParams p2;
+      p2.x = e->attn_f; p2.ldx = H; p2.Wt = w.proj_w; p2.bias = w.proj_b; p2.residual = cur; p2.ldr = H;
+      p2.out = e->h; p2.ldo = H; p2.B = B; p2.N = H; p2.K = H;
+      LAUNCH(e, launch_gemv(p2, c.dtype, s));
+      cur = e->h;
+      // ln_2 + c_fc + gelu_new
+      GemvParams p3;
+      p3.x = e->h; p3.ldx = H; p3.Wt = w.fc_w; p3.bias = w.fc_b; p3.out = e->act_f; p3.ldo = F; p3.B = B; p3.N = F;
+      p3.K = H; p3.ln_g = w.ln2_g; p3.ln_b = w.ln2_b; p3.eps = c.ln_eps; p3.flags = GP_EPI_GELU;
+      LAUNCH(e, launch_gemv(p3, c.dtype, s));
+      // mlp c_proj + residual
+      GemvParams p4;
+      p4.x = e->act_f; p4.ldx = F; p4.Wt = w.mproj_w; p4.bias = w.mproj_b; p4.residual = e->h; p4.ldr = H;
+      p4.out = dst; p4.ldo = H; p4.B = B; p4.N = H; p4.K = F;
+      LAUNCH(e, launch_gemv(p4, c.dtype, s));
+    } else {
+      if (B > c.max_tokens) { set_err(e, "decode: B=%d exceeds max_tokens=%d", B, c.max_tokens); return GP_EINVAL; }
+      LAUNCH(e, launch_layernorm(cur, H, w.ln1_g, w.ln1_b, e->xa, obf, B, H, c.ln_eps, s));
+      LAUNCH(e, gemm(e, e->xa, H, w.attn_w, w.attn_b, nullptr, 0, e->qkv, 3 * H, B, 3 * H, H, oflag, s));
+      LAUNCH(e, launch_qkv_split_decode(e->qkv, e->q, w.kc, w.vc, e->lens, B, slot0, H, e->nh, e->d, c.max_ctx, c.dtype, s));
+      LAUNCH(e, launch_attn_decode(e->q, w.kc, w.vc, e->lens, 1, slot0, e->xa, obf, B, e->nh, e->d, c.max_ctx, c.dtype, s));
+      LAUNCH(e, gemm(e, e->xa, H, w.proj_w, w.proj_b, cur, H, e->h, H, B, H, H, 0u, s));
+      cur = e->h;
+      LAUNCH(e, launch_layernorm(e->h, H, w.ln2_g, w.ln2_b, e->xa, obf, B, H, c.ln_eps, s));
+      LAUNCH(e, gemm(e, e->xa, H, w.fc_w, w.fc_b, nullptr, 0, e->act, F, B, F, H, oflag | GP_EPI_GELU, s));
+      LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, e->h, H, dst, H, B, H, F, 0u, s));
+    }
+  }
+  if (c.has_head) {
+    // the last CTA of the (last) lm_head launch advances the cache lengths and appends to seq
+    r = run_lm_head(e, e->h, H, B, slot0, logits, next_ids, e->lens, seq, s);
+    if (r != GP_OK) return r;
+  } else {
+    LAUNCH(e, launch_set_lens(e->lens, slot0, B, 1, 1, s));
+  }
+  return GP_OK;
+}
+
+int parse_layer(const char* name, int* layer, const char** rest) {
+  if (strncmp(name, "h.", 2) != 0) return 0;
+  char* end = nullptr;
+  long v = strtol(name + 2, &end, 10);
+  if (end == name + 2 || *end != '.') return 0;
+  *layer = (int)v;
+  *rest = end + 1;
+  return 1;
+}
+
+}  // namespace
+
+// =========================================================================== C ABI
+extern "C" {
+
+int gp_version(void) { return GP_VERSION; }
+
+const char* gp_last_error(const gp_engine* e) { return e ? e->err.c_str() : g_err.c_str(); }
+
+int64_t gp_last_launch_count(const gp_engine* e) { return e ? e->launches : 0; }
+
+int64_t gp_lmhead_scratch_bytes(int32_t B, int32_t V) {
+  (void)B; (void)V;
+  return kLmheadScratchHeader + (int64_t)kLmheadMaxGrid * kGemvMaxBatch * (sizeof(float) + sizeof(int));
+}
+
+int gp_engine_create(const gp_config* cfg, gp_engine** out) {
+  if (!cfg || !out) { set_err(nullptr, "gp_engine_create: NULL argument"); return GP_EINVAL; }
+  *out = nullptr;
+  if (cfg->n_embd <= 0 || cfg->n_head <= 0 || cfg->n_embd % cfg->n_head != 0 || cfg->vocab_size <= 0 ||
+      cfg->n_positions <= 0 || cfg->n_layer <= 0 || cfg->layer_begin < 0 || cfg->layer_end > cfg->n_layer ||
+      cfg->layer_begin >= cfg->layer_end || cfg->max_batch <= 0 || cfg->max_ctx <= 0 ||
+      cfg->max_ctx > cfg->n_positions || (cfg->dtype != GP_F32 && cfg->dtype != GP_BF16)) {
+    set_err(nullptr, "gp_engine_create: invalid configuration");
+    return GP_EINVAL;
+  }
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+    set_err(nullptr, "gp_engine_create: CUDA device %d unavailable (%s); this library has no CPU path", cfg->device,
+            ce == cudaSuccess ? "no such ordinal" : cudaGetErrorString(ce));
+    return GP_ECUDA;
+  }
+  gp_engine* e = new gp_engine();
+  e->cfg = *cfg;
+  if (e->cfg.max_tokens <= 0) e->cfg.max_tokens = cfg->max_batch * cfg->max_ctx;
+  if (e->cfg.max_tokens < cfg->max_batch) e->cfg.max_tokens = cfg->max_batch;
+  e->H = cfg->n_embd; e->nh = cfg->n_head; e->d = e->H / e->nh; e->V = cfg->vocab_size; e->F = 4 * e->H;
+  e->L = cfg->layer_end - cfg->layer_begin;
+  e->esz = cfg->dtype == GP_BF16 ? 2 : 4;
+  e->seq_stride = cfg->n_positions + 1;
+  auto fail = [&](int rc) { gp_engine_destroy(e); return rc; };
+#define TRY(x) do { int _r = (x); if (_r != GP_OK) return fail(_r); } while (0)
+#define TRYCK(call) do { cudaError_t _c = (call); if (_c != cudaSuccess) { set_err(nullptr, "%s: %s", #call, cudaGetErrorString(_c)); return fail(GP_ECUDA); } } while (0)
+  TRYCK(cudaSetDevice(cfg->device));
+  TRYCK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  TRYCK(init_gemv_attrs());
+  TRYCK(init_attn_attrs());
+  if (cfg->dtype == GP_BF16 && !(cfg->flags & GP_FLAG_NO_TCGEN05)) TRYCK(init_gemm_tc());
+
+  const size_t H = e->H, F = e->F, V = e->V, esz = e->esz;
+  auto alloc = [&](void** p, size_t bytes) -> int { return dev_alloc(e, p, bytes); };
+  e->layers.resize(e->L);
+  const size_t kv_elems = (size_t)cfg->max_batch * e->nh * cfg->max_ctx * e->d;
+  for (int li = 0; li < e->L; ++li) {
+    LayerW& w = e->layers[li];
+    const std::string p = "h." + std::to_string(cfg->layer_begin + li) + ".";
+    TRY(alloc((void**)&w.ln1_g, H * 4)); TRY(alloc((void**)&w.ln1_b, H * 4));
+    TRY(alloc((void**)&w.ln2_g, H * 4)); TRY(alloc((void**)&w.ln2_b, H * 4));
+    TRY(alloc((void**)&w.attn_b, 3 * H * 4)); TRY(alloc((void**)&w.proj_b, H * 4));
+    TRY(alloc((void**)&w.fc_b, F * 4)); TRY(alloc((void**)&w.mproj_b, H * 4));
+    TRY(alloc(&w.attn_w, 3 * H * H * esz)); TRY(alloc(&w.proj_w, H * H * esz));
+    TRY(alloc(&w.fc_w, F * H * esz)); TRY(alloc(&w.mproj_w, H * F * esz));
+    TRY(alloc(&w.kc, kv_elems * esz)); TRY(alloc(&w.vc, kv_elems * esz));
+    for (const char* n : {"ln_1.weight", "ln_1.bias", "attn.c_attn.weight", "attn.c_attn.bias", "attn.c_proj.weight",
+                          "attn.c_proj.bias", "ln_2.weight", "ln_2.bias", "mlp.c_fc.weight", "mlp.c_fc.bias",
+                          "mlp.c_proj.weight", "mlp.c_proj.bias"})
+      e->required.insert(p + n);
+  }
+  if (cfg->has_embed || cfg->has_head) {
+    TRY(alloc(&e->wte, V * H * esz));
+    e->required.insert("wte.weight");
+  }
+  if (cfg->has_embed) {
+    TRY(alloc(&e->wpe, (size_t)cfg->n_positions * H * esz));
+    e->required.insert("wpe.weight");
+  }
+  if (cfg->has_head) {
+    TRY(alloc((void**)&e->lnf_g, H * 4)); TRY(alloc((void**)&e->lnf_b, H * 4));
+    e->required.insert("ln_f.weight"); e->required.insert("ln_f.bias");
+    TRY(alloc(&e->lm_scratch, (size_t)gp_lmhead_scratch_bytes(kGemvMaxBatch, e->V)));
+    TRYCK(cudaMemset(e->lm_scratch, 0, kLmheadScratchHeader));
+  }
+  const size_t MT = e->cfg.max_tokens, MB = cfg->max_batch;
+  TRY(alloc((void**)&e->lens, MB * sizeof(int32_t)));
+  TRYCK(cudaMemset(e->lens, 0, MB * sizeof(int32_t)));
+  TRY(alloc((void**)&e->h, MT * H * 4));
+  TRY(alloc(&e->xa, MT * H * esz));
+  TRY(alloc(&e->qkv, MT * 3 * H * esz));
+  TRY(alloc(&e->act, MT * F * esz));
+  TRY(alloc((void**)&e->q, MB * H * 4));
+  TRY(alloc((void**)&e->attn_f, MB * H * 4));
+  TRY(alloc((void**)&e->act_f, MB * F * 4));
+  TRY(alloc((void**)&e->hlast, MB * H * 4));
+  TRY(alloc((void**)&e->seq, MB * (size_t)e->seq_stride * sizeof(int32_t)));
+  TRY(alloc((void**)&e->prompt, MB * (size_t)cfg->n_positions * sizeof(int32_t)));
+  TRY(alloc((void**)&e->mailbox, MB * sizeof(int32_t)));
+#undef TRY
+#undef TRYCK
+  *out = e;
+  return GP_OK;
+}
+
+int gp_engine_destroy(gp_engine* e) {
+  if (!e) return GP_OK;
+  cudaSetDevice(e->cfg.device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (auto& kv : e->decode_graphs) cudaGraphExecDestroy(kv.second);
+  for (auto ev : e->events) cudaEventDestroy(ev);
+  for (void* p : e->allocs) cudaFree(p);
+  if (e->stage) cudaFree(e->stage);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+  return GP_OK;
+}
+
+int gp_load_weight(gp_engine* e, const char* name, const float* data_host, const int64_t* shape, int32_t ndim) {
+  if (!e || !name || !data_host || !shape || ndim < 1 || ndim > 2) { set_err(e, "gp_load_weight: bad argument"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(e->cfg.device));
+  const int64_t H = e->H, F = e->F;
+  void* dst = nullptr;
+  int64_t R = shape[0], C = ndim == 2 ? shape[1] : 1, eR = 0, eC = 1;
+  bool transpose = false, keep_f32 = false;
+  std::string nm(name);
+  int layer = -1;
+  const char* rest = nullptr;
+  if (nm == "wte.weight" && e->wte) { dst = e->wte; eR = e->V; eC = H; }
+  else if (nm == "wpe.weight" && e->wpe) { dst = e->wpe; eR = e->cfg.n_positions; eC = H; }
+  else if (nm == "ln_f.weight" && e->lnf_g) { dst = e->lnf_g; eR = H; keep_f32 = true; }
+  else if (nm == "ln_f.bias" && e->lnf_b) { dst = e->lnf_b; eR = H; keep_f32 = true; }
+  else if (parse_layer(name, &layer, &rest) && layer >= e->cfg.layer_begin && layer < e->cfg.layer_end) {
+    LayerW& w = e->layers[layer - e->cfg.layer_begin];
+    std::string r(rest);
+    if (r == "ln_1.weight") { dst = w.ln1_g; eR = H; keep_f32 = true; }
+    else if (r == "ln_1.bias") { dst = w.ln1_b; eR = H; keep_f32 = true; }
+    else if (r == "ln_2.weight") { dst = w.ln2_g; eR = H; keep_f32 = true; }
+    else if (r == "ln_2.bias") { dst = w.ln2_b; eR = H; keep_f32 = true; }
+    else if (r == "attn.c_attn.bias") { dst = w.attn_b; eR = 3 * H; keep_f32 = true; }
+    else if (r == "attn.c_proj.bias") { dst = w.proj_b; eR = H; keep_f32 = true; }
+    else if (r == "mlp.c_fc.bias") { dst = w.fc_b; eR = F; keep_f32 = true; }
+    else if (r == "mlp.c_proj.bias") { dst = w.mproj_b; eR = H; keep_f32 = true; }
+    // Conv1D weights arrive [in,out] ([hf] pytorch_utils.py:97-123) and are stored [out,in]
+    else if (r == "attn.c_attn.weight") { dst = w.attn_w; eR = H; eC = 3 * H; transpose = true; }
+    else if (r == "attn.c_proj.weight") { dst = w.proj_w; eR = H; eC = H; transpose = true; }
+    else if (r == "mlp.c_fc.weight") { dst = w.fc_w; eR = H; eC = F; transpose = true; }
+    else if (r == "mlp.c_proj.weight") { dst = w.mproj_w; eR = F; eC = H; transpose = true; }
+  }
+  if (!dst) { set_err(e, "gp_load_weight: '%s' does not belong to this stage (layers [%d,%d) embed=%d head=%d)", name, e->cfg.layer_begin, e->cfg.layer_end, e->cfg.has_embed, e->cfg.has_head); return GP_EINVAL; }
+  if (R != eR || C != eC) { set_err(e, "gp_load_weight: '%s' has shape [%lld,%lld], expected [%lld,%lld]", name, (long long)R, (long long)C, (long long)eR, (long long)eC); return GP_EINVAL; }
+  const size_t n = (size_t)R * C;
+  if (keep_f32) {
+    CK(e, cudaMemcpy(dst, data_host, n * sizeof(float), cudaMemcpyHostToDevice));
+  } else {
+    if (e->stage_floats < n) {
+      if (e->stage) cudaFree(e->stage);
+      e->stage = nullptr; e->stage_floats = 0;
+      CK(e, cudaMalloc((void**)&e->stage, n * sizeof(float)));
+      e->stage_floats = n;
+    }
+    CK(e, cudaMemcpy(e->stage, data_host, n * sizeof(float), cudaMemcpyHostToDevice));
+    CK(e, launch_convert(e->stage, dst, (int)R, (int)C, transpose, e->cfg.dtype, e->stream));
+    CK(e, cudaStreamSynchronize(e->stream));
+  }
+  e->loaded.insert(nm);
+  return GP_OK;
+}
+
+int gp_weights_ready(gp_engine* e) {
+  if (!e) return GP_EINVAL;
+  int r = check_ready(e);
+  if (r == GP_OK && e->stage) { cudaFree(e->stage); e->stage = nullptr; e->stage_floats = 0; }
+  return r;
+}
+
+int gp_kv_reset(gp_engine* e, int32_t slot, void* stream) {
+  if (!e || slot >= e->cfg.max_batch) { set_err(e, "gp_kv_reset: bad slot"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(e->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (slot < 0) CK(e, cudaMemsetAsync(e->lens, 0, e->cfg.max_batch * sizeof(int32_t), s));
+  else CK(e, cudaMemsetAsync(e->lens + slot, 0, sizeof(int32_t), s));
+  return GP_OK;
+}
+
+int gp_kv_lengths(gp_engine* e, int32_t* lens_host, int32_t n, void* stream) {
+  if (!e || !lens_host || n < 0 || n > e->cfg.max_batch) { set_err(e, "gp_kv_lengths: bad argument"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(e->cfg.device));
+  CK(e, cudaMemcpyAsync(lens_host, e->lens, n * sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CK(e, cudaStreamSynchronize((cudaStream_t)stream));
+  return GP_OK;
+}
+
+int gp_stage_prefill(gp_engine* e, const int32_t* ids, const float* hidden_in, int32_t B, int32_t T, int32_t slot0,
+                     int32_t use_cache, float* hidden_out, float* logits, int32_t logits_all, int32_t* next_ids,
+                     void* stream) {
+  if (!e) return GP_EINVAL;
+  CK(e, cudaSetDevice(e->cfg.device));
+  e->launches = 0;
+  return prefill_impl(e, ids, hidden_in, B, T, slot0, use_cache, hidden_out, logits, logits_all, next_ids, nullptr,
+                      (cudaStream_t)stream);
+}
+
+int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, int32_t B, int32_t slot0,
+                    float* hidden_out, float* logits, int32_t* next_ids, void* stream) {
+  if (!e) return GP_EINVAL;
+  CK(e, cudaSetDevice(e->cfg.device));
+  e->launches = 0;
+  return decode_impl(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, nullptr, (cudaStream_t)stream);
+}
+
+int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t P, int32_t n_new,
+                int32_t* out_ids_host, float* timings_ms_host) {
+  if (!e || !prompt_ids_host || !out_ids_host) { set_err(e, "gp_generate: NULL argument"); return GP_EINVAL; }
+  const gp_config& c = e->cfg;
+  if (!c.has_embed || !c.has_head) { set_err(e, "gp_generate needs a single-stage engine (has_embed && has_head)"); return GP_EINVAL; }
+  if (B <= 0 || B > c.max_batch || P <= 0 || n_new < 0) { set_err(e, "gp_generate: bad B/P/n_new (%d,%d,%d)", B, P, n_new); return GP_EINVAL; }
+  // positions 0 .. P+n_new-2 are run through the model; the reference has no such guard and
+  // would raise IndexError past wpe
+  if (P + n_new - 1 > c.max_ctx || P > c.max_ctx || (int64_t)B * P > c.max_tokens) {
+    set_err(e, "gp_generate: prompt %d + %d new tokens exceeds the context of %d positions", P, n_new, c.max_ctx);
+    return GP_EINVAL;
+  }
+  for (int64_t i = 0; i < (int64_t)B * P; ++i)
+    if (prompt_ids_host[i] < 0 || prompt_ids_host[i] >= e->V) {
+      set_err(e, "gp_generate: token id %d out of range [0,%d)", prompt_ids_host[i], e->V);
+      return GP_EINVAL;
+    }
+  CK(e, cudaSetDevice(c.device));
+  cudaStream_t s = e->stream;
+  e->launches = 0;
+  const int total = P + n_new;
+  const int n_ev = 3 + (timings_ms_host ? n_new : 0);
+  while ((int)e->events.size() < n_ev) {
+    cudaEvent_t ev;
+    CK(e, cudaEventCreate(&ev));
+    e->events.push_back(ev);
+  }
+  CK(e, cudaMemcpyAsync(e->prompt, prompt_ids_host, (size_t)B * P * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+  CK(e, cudaMemcpy2DAsync(e->seq, e->seq_stride * sizeof(int32_t), prompt_ids_host, P * sizeof(int32_t),
+                          P * sizeof(int32_t), B, cudaMemcpyHostToDevice, s));
+  CK(e, cudaMemsetAsync(e->lens, 0, c.max_batch * sizeof(int32_t), s));
+  CK(e, cudaEventRecord(e->events[0], s));
+  if (n_new > 0) {
+    int r = prefill_impl(e, e->prompt, nullptr, B, P, 0, 1, nullptr, nullptr, 0, e->mailbox, nullptr, s);
+    if (r != GP_OK) return r;
+    // first new token: mailbox -> seq[:, P]
+    CK(e, cudaMemcpy2DAsync(e->seq + P, e->seq_stride * sizeof(int32_t), e->mailbox, sizeof(int32_t), sizeof(int32_t), B,
+                            cudaMemcpyDeviceToDevice, s));
+  }
+  CK(e, cudaEventRecord(e->events[1], s));
+  const int steps = n_new > 1 ? n_new - 1 : 0;
+  if (steps > 0) {
+    const bool use_graph = !(c.flags & GP_FLAG_NO_GRAPH);
+    cudaGraphExec_t exec = nullptr;
+    int64_t per_step = 0;
+    if (use_graph) {
+      auto it = e->decode_graphs.find(B);
+      if (it == e->decode_graphs.end()) {
+        const int64_t before = e->launches;
+        CK(e, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        int r = decode_impl(e, e->mailbox, nullptr, B, 0, nullptr, nullptr, e->mailbox, e->seq, s);
+        cudaGraph_t g = nullptr;
+        cudaError_t ce = cudaStreamEndCapture(s, &g);
+        if (r != GP_OK) { if (g) cudaGraphDestroy(g); return r; }
+        CK(e, ce);
+        per_step = e->launches - before;
+        e->launches = before;
+        CK(e, cudaGraphInstantiate(&exec, g, 0));
+        cudaGraphDestroy(g);
+        e->decode_graphs[B] = exec;
+        e->decode_graph_launches[B] = per_step;
+      } else {
+        exec = it->second;
+        per_step = e->decode_graph_launches[B];
+      }
+    }
+    for (int i = 0; i < steps; ++i) {
+      if (use_graph) {
+        CK(e, cudaGraphLaunch(exec, s));
+        e->launches += per_step;
+      } else {
+        int r = decode_impl(e, e->mailbox, nullptr, B, 0, nullptr, nullptr, e->mailbox, e->seq, s);
+        if (r != GP_OK) return r;
+      }
+      if (timings_ms_host) CK(e, cudaEventRecord(e->events[3 + i], s));
+    }
+  }
+  CK(e, cudaEventRecord(e->events[2], s));
+  CK(e, cudaMemcpy2DAsync(out_ids_host, total * sizeof(int32_t), e->seq, e->seq_stride * sizeof(int32_t),
+                          total * sizeof(int32_t), B, cudaMemcpyDeviceToHost, s));
+  CK(e, cudaStreamSynchronize(s));
+  if (timings_ms_host) {
+    float ms = 0.f;
+    CK(e, cudaEventElapsedTime(&ms, e->events[0], e->events[1]));
+    timings_ms_host[0] = ms;
+    CK(e, cudaEventElapsedTime(&ms, e->events[1], e->events[2]));
+    timings_ms_host[1] = ms;
+    for (int i = 0; i < n_new; ++i) timings_ms_host[2 + i] = 0.f;
+    for (int i = 0; i < steps; ++i) {
+      CK(e, cudaEventElapsedTime(&ms, i == 0 ? e->events[1] : e->events[3 + i - 1], e->events[3 + i]));
+      timings_ms_host[2 + i] = ms;
+    }
+  }
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------- op-level entry points
+#define OPCK(call)                                                                   \
+  do {                                                                               \
+    cudaError_t _c = (call);                                                         \
+    if (_c != cudaSuccess) {                                                         \
+      set_err(nullptr, "%s failed: %s", #call, cudaGetErrorString(_c));              \
+      return _c == cudaErrorInvalidValue ? GP_EINVAL : GP_ECUDA;                     \
+    }                                                                                \
+  } while (0)
+
+static int op_init() {
+  static thread_local int inited_dev = -1;
+  int dev = 0;
+  OPCK(cudaGetDevice(&dev));
+  if (inited_dev != dev) {
+    OPCK(init_gemv_attrs());
+    OPCK(init_attn_attrs());
+    OPCK(init_gemm_tc());
+    inited_dev = dev;
+  }
+  return GP_OK;
+}
+
+int gp_op_embed(const int32_t* ids, const int32_t* pos, const void* wte, const void* wpe, float* out, int32_t M,
+                int32_t H, int32_t dtype, void* stream) {
+  if (!ids || !pos || !wte || !wpe || !out) { set_err(nullptr, "gp_op_embed: NULL argument"); return GP_EINVAL; }
+  OPCK(launch_embed(ids, pos, 0, 1, nullptr, 0, wte, wpe, out, M, H, 0x7fffffff, 0x7fffffff, dtype, (cudaStream_t)stream));
+  return GP_OK;
+}
+
+int gp_op_layernorm(const float* x, const float* gamma, const float* beta, void* out, int32_t M, int32_t H, float eps,
+                    uint32_t flags, void* stream) {
+  if (!x || !gamma || !beta || !out) { set_err(nullptr, "gp_op_layernorm: NULL argument"); return GP_EINVAL; }
+  OPCK(launch_layernorm(x, H, gamma, beta, out, flags & GP_OUT_BF16, M, H, eps, (cudaStream_t)stream));
+  return GP_OK;
+}
+
+int gp_op_gemv(const float* x, const void* Wt, const float* bias, const float* residual, float* out, int32_t B,
+               int32_t N, int32_t K, const float* ln_gamma, const float* ln_beta, float eps, uint32_t flags,
+               int32_t dtype, void* stream) {
+  if (!x || !Wt || !out) { set_err(nullptr, "gp_op_gemv: NULL argument"); return GP_EINVAL; }
+  if (!gemv_supported(B, K)) { set_err(nullptr, "gp_op_gemv: B=%d K=%d outside the GEMV envelope (B<=%d, B*K*4<=%d)", B, K, kGemvMaxBatch, kGemvMaxSmem); return GP_EINVAL; }
+  int r = op_init();
+  if (r != GP_OK) return r;
+  GemvParams p;
+  p.x = x; p.ldx = K; p.Wt = Wt; p.bias = bias; p.residual = residual; p.ldr = N; p.out = out; p.ldo = N;
+  p.B = B; p.N = N; p.K = K; p.ln_g = ln_gamma; p.ln_b = ln_beta; p.eps = eps; p.flags = flags;
+  OPCK(launch_gemv(p, dtype, (cudaStream_t)stream));
+  return GP_OK;
+}
+
+int gp_op_gemm(const void* A, const void* Wt, const float* bias, const float* residual, void* out, int32_t M, int32_t N,
+               int32_t K, uint32_t flags, int32_t dtype, void* stream) {
+  if (!A || !Wt || !out) { set_err(nullptr, "gp_op_gemm: NULL argument"); return GP_EINVAL; }
+  int r = op_init();
+  if (r != GP_OK) return r;
+  if (dtype == GP_BF16 && !(flags & GP_GEMM_SIMT)) {
+    if (!gemm_tc_supported(M, N, K)) { set_err(nullptr, "gp_op_gemm: shape M=%d N=%d K=%d not supported by the tcgen05 kernel", M, N, K); return GP_EINVAL; }
+    OPCK(launch_gemm_tc(A, K, Wt, bias, residual, N, out, N, M, N, K, flags, (cudaStream_t)stream));
+  } else {
+    OPCK(launch_gemm_simt(A, K, Wt, bias, residual, N, out, N, M, N, K, flags, dtype, (cudaStream_t)stream));
+  }
+  return GP_OK;
+}
+
+int gp_op_attn_decode(const float* q, const void* kcache, const void* vcache, const int32_t* ctx_len, float* out,
+                      int32_t B, int32_t nh, int32_t d, int32_t max_ctx, int32_t dtype, void* stream) {
+  if (!q || !kcache || !vcache || !ctx_len || !out) { set_err(nullptr, "gp_op_attn_decode: NULL argument"); return GP_EINVAL; }
+  OPCK(launch_attn_decode(q, kcache, vcache, ctx_len, 0, 0, out, false, B, nh, d, max_ctx, dtype, (cudaStream_t)stream));
+  return GP_OK;
+}
+
+int gp_op_attn_prefill(const void* qkv, void* out, int32_t B, int32_t T, int32_t nh, int32_t d, int32_t dtype,
+                       void* stream) {
+  if (!qkv || !out) { set_err(nullptr, "gp_op_attn_prefill: NULL argument"); return GP_EINVAL; }
+  OPCK(launch_attn_prefill(qkv, out, B, T, nh, d, dtype, (cudaStream_t)stream));
+  return GP_OK;
+}
+
+int gp_op_lmhead_argmax(const float* x, const float* gamma, const float* beta, const void* wte, int32_t* ids_out,
+                        float* logits_out, void* scratch, int32_t B, int32_t V, int32_t H, float eps, int32_t dtype,
+                        void* stream) {
+  if (!x || !wte || !ids_out || !scratch) { set_err(nullptr, "gp_op_lmhead_argmax: NULL argument"); return GP_EINVAL; }
+  if (!gemv_supported(B, H)) { set_err(nullptr, "gp_op_lmhead_argmax: B=%d H=%d outside the GEMV envelope", B, H); return GP_EINVAL; }
+  int r = op_init();
+  if (r != GP_OK) return r;
+  LmheadParams p;
+  p.x = x; p.ldx = H; p.ln_g = gamma; p.ln_b = beta; p.eps = eps; p.wte = wte; p.B = B; p.V = V; p.H = H;
+  p.ids_out = ids_out; p.logits_out = logits_out; p.ldl = V; p.scratch = scratch;
+  OPCK(launch_lmhead_argmax(p, dtype, (cudaStream_t)stream));
+  return GP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,85 @@
+// Internal host-side launch interface of the sm_100a kernels (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gpt2pipe.h"
+
+namespace gp {
+
+constexpr int kGemvMaxBatch = 8;        // rows one GEMV launch carries
+constexpr int kGemvMaxSmem = 200 * 1024;  // bytes of x staged in shared memory
+constexpr int kLmheadMaxGrid = 1184;    // 148 SMs x 8 CTAs
+constexpr int kLmheadScratchHeader = 256;
+
+// out[b,n] = epi(sum_k LN?(x)[b,k] Wt[n,k] + bias[n]) (+ residual[b,n]), or the c_attn
+// variant (mode 1) whose epilogue scatters q to `q_out` and k/v into the KV cache.
+struct GemvParams {
+  const float* x = nullptr; int ldx = 0;
+  const void* Wt = nullptr;
+  const float* bias = nullptr;
+  const float* residual = nullptr; int ldr = 0;
+  float* out = nullptr; int ldo = 0;
+  int B = 0, N = 0, K = 0;
+  const float* ln_g = nullptr; const float* ln_b = nullptr; float eps = 1e-5f;
+  uint32_t flags = 0;
+  int mode = 0;                       // 0 plain, 1 qkv scatter
+  float* q_out = nullptr;             // [B,H]
+  void* kcache = nullptr; void* vcache = nullptr;  // [slots, nh, max_ctx, d]
+  const int32_t* lens = nullptr; int slot0 = 0;
+  int H = 0, nh = 0, d = 0, max_ctx = 0;
+};
+cudaError_t launch_gemv(const GemvParams& p, int dtype, cudaStream_t s);
+bool gemv_supported(int B, int K);
+cudaError_t init_gemv_attrs();
+
+struct LmheadParams {
+  const float* x = nullptr; int ldx = 0;   // [B,H] pre-ln_f hidden
+  const float* ln_g = nullptr; const float* ln_b = nullptr; float eps = 1e-5f;
+  const void* wte = nullptr;               // [V,H]
+  int B = 0, V = 0, H = 0;
+  int32_t* ids_out = nullptr;              // [B]
+  float* logits_out = nullptr; int ldl = 0;  // [B,V] optional
+  void* scratch = nullptr;                 // gp_lmhead_scratch_bytes
+  // optional device-side bookkeeping done by the last CTA
+  int32_t* lens = nullptr; int slot0 = 0;  // lens[slot0+b] += 1
+  int32_t* seq = nullptr; int seq_stride = 0;  // seq[b*stride + old_len + 1] = id
+};
+cudaError_t launch_lmhead_argmax(const LmheadParams& p, int dtype, cudaStream_t s);
+
+// ---- attention
+cudaError_t launch_attn_decode(const float* q, const void* kc, const void* vc, const int32_t* lens,
+                               int len_add, int slot0, void* out, bool out_bf16, int B, int nh, int d,
+                               int max_ctx, int dtype, cudaStream_t s);
+cudaError_t launch_attn_prefill(const void* qkv, void* out, int B, int T, int nh, int d, int dtype,
+                                cudaStream_t s);
+cudaError_t init_attn_attrs();
+
+// ---- misc
+cudaError_t launch_embed(const int32_t* ids, const int32_t* pos, int pos0, int T, const int32_t* lens,
+                         int slot0, const void* wte, const void* wpe, float* out, int M, int H, int V,
+                         int n_pos, int dtype, cudaStream_t s);
+cudaError_t launch_layernorm(const float* x, int ldx, const float* g, const float* b, void* out, bool out_bf16,
+                             int M, int H, float eps, cudaStream_t s);
+cudaError_t launch_gemm_simt(const void* A, int lda, const void* Wt, const float* bias, const float* residual,
+                             int ldr, void* out, int ldo, int M, int N, int K, uint32_t flags, int dtype,
+                             cudaStream_t s);
+// qkv [B*T, 3H] -> caches at positions [0,T) of slots slot0.. (prefill)
+cudaError_t launch_kv_scatter(const void* qkv, void* kc, void* vc, int B, int T, int slot0, int H, int nh, int d,
+                              int max_ctx, int dtype, cudaStream_t s);
+// qkv [B, 3H] -> q fp32 [B,H] + caches at position lens[slot] (batched decode on the GEMM path)
+cudaError_t launch_qkv_split_decode(const void* qkv, float* q, void* kc, void* vc, const int32_t* lens, int B,
+                                    int slot0, int H, int nh, int d, int max_ctx, int dtype, cudaStream_t s);
+cudaError_t launch_set_lens(int32_t* lens, int slot0, int B, int value, int add, cudaStream_t s);
+// src fp32 [R,C] -> dst (dtype) [C,R] if transpose else [R,C]
+cudaError_t launch_convert(const float* src, void* dst, int R, int C, bool transpose, int dtype, cudaStream_t s);
+// gather rows: dst[b,:] = src[(b*T + T-1),:]  (last position of each sequence)
+cudaError_t launch_gather_last(const float* src, float* dst, int B, int T, int H, cudaStream_t s);
+
+// ---- tcgen05 GEMM (gemm_tcgen05.cu)
+bool gemm_tc_supported(int M, int N, int K);
+cudaError_t init_gemm_tc();
+cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* bias, const float* residual,
+                           int ldr, void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s);
+
+}  // namespace gp

@@ -1,0 +1,186 @@
+"""Pipeline of stages over GPUs: one process per GPU, stage s = blocks split_layers()[s].
+
+world == 1 : a single-stage engine; the whole greedy loop runs on the device (`gp_generate`).
+world  > 1 : the reference's A -> B handoff (server.py:172-181, HTTP/JSON through the
+             coordinator) becomes an on-device exchange between neighbouring ranks, and the
+             logits -> coordinator hop becomes a ring of int32 token ids from the last stage
+             back to stage 0.  `world` micro-batches ("streams") are kept in flight so every
+             stage works every tick.  Transport: torch.distributed (NCCL) grouped send/recv.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+
+from ._lib import GP_BF16
+from .weights import GPT2Dims, init_weights, split_layers, stage_weight_names
+
+
+def tick_schedule(n_stages: int, n_streams: int, n_rounds: int) -> List[List[Optional[Tuple[int, int]]]]:
+    """schedule[t][s] = (round, stream) that stage s computes at tick t, or None.
+    Item (r, m) enters stage 0 at tick r*n_streams + m and stage s at that + s; with
+    n_streams >= n_stages the ids a round produces are back at stage 0 before the next round
+    needs them.  Pure function (unit-tested on CPU)."""
+    if n_streams < n_stages:
+        raise ValueError("need at least one stream per stage to close the token ring in time")
+    n_ticks = n_rounds * n_streams + n_stages - 1
+    sched = []
+    for t in range(n_ticks):
+        row = []
+        for s in range(n_stages):
+            i = t - s
+            row.append((i // n_streams, i % n_streams) if 0 <= i < n_rounds * n_streams else None)
+        sched.append(row)
+    return sched
+
+
+def run_ticks(rank: int, n_stages: int, n_streams: int, n_rounds: int, exchange, compute, on_ids):
+    """Drives one rank through the systolic schedule.  Transport- and engine-agnostic so the
+    same code runs under NCCL on GPUs and under gloo with a toy stage on CPUs (tests).
+
+      exchange(send_obj, recv_kind) -> received object or None
+          send_obj : what this rank computed last tick (None = nothing to send)
+          recv_kind: None | "ids" | "hidden_prefill" | "hidden_decode" (what the previous
+                     rank in the ring computed last tick)
+      compute(round, stream, received) -> object to pass on next tick
+      on_ids(round, stream, ids)       -> stage 0 only: ids produced by the last stage
+    """
+    if n_rounds <= 0:
+        return
+    first = rank == 0
+    prv = (rank - 1) % n_stages
+    sched = tick_schedule(n_stages, n_streams, n_rounds)
+    sched.append([None] * n_stages)          # drain tick: the last ids travel to stage 0
+    pending = None
+    for t, row in enumerate(sched):
+        prev_item = sched[t - 1][prv] if t > 0 else None
+        recv_kind = None
+        if prev_item is not None:
+            recv_kind = "ids" if first else ("hidden_prefill" if prev_item[0] == 0 else "hidden_decode")
+        got = exchange(pending, recv_kind)
+        pending = None
+        if first and prev_item is not None:
+            on_ids(prev_item[0], prev_item[1], got)
+        item = row[rank]
+        if item is not None:
+            pending = compute(item[0], item[1], got)
+
+
+class PipelineRunner:
+    def __init__(self, dims: GPT2Dims, seed: int = 0, dtype: int = GP_BF16, batch_per_stream: int = 1,
+                 max_ctx: Optional[int] = None, rank: int = 0, world: int = 1, device: int = 0, recipe: str = "hf",
+                 weights=None, flags: int = 0):
+        from .engine import StageEngine
+        self.dims, self.rank, self.world, self.B = dims, rank, world, batch_per_stream
+        self.n_streams = world
+        self.device = torch.device("cuda", device)
+        b, e = split_layers(dims.n_layer, world)[rank]
+        self.first, self.last = rank == 0, rank == world - 1
+        self.engine = StageEngine(dims, b, e, has_embed=self.first, has_head=self.last, dtype=dtype,
+                                  max_batch=batch_per_stream * self.n_streams, max_ctx=max_ctx,
+                                  max_tokens=batch_per_stream * (max_ctx or dims.n_positions), device=device,
+                                  flags=flags)
+        names = stage_weight_names(dims, b, e, self.first, self.last)
+        w = weights if weights is not None else init_weights(dims, seed, recipe, only=names)
+        self.engine.load_weights(w)
+        if world > 1:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                dist.init_process_group("nccl", device_id=self.device)
+            self.dist = dist
+        else:
+            self.dist = None
+
+    # ---- small collectives for the bench harness
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def max_over_ranks(self, v: float) -> float:
+        if self.dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- generation
+    def generate(self, prompts: torch.Tensor, n_new: int, timings: bool = False):
+        """prompts: CPU int32 [B*n_streams, P].  Returns CPU int32 [B*n_streams, P+n_new] on
+        rank 0 (other ranks return None) and, with timings=True, a dict of device times."""
+        if self.world == 1:
+            if timings:
+                out, tm = self.engine.generate(prompts, n_new, timings=True)
+                tm["launches"] = self.engine.last_launch_count()
+                return out, tm
+            return self.engine.generate(prompts, n_new)
+        return self._generate_pipelined(prompts, n_new, timings)
+
+    def _generate_pipelined(self, prompts, n_new, timings):
+        dist, eng, B, S, M = self.dist, self.engine, self.B, self.world, self.n_streams
+        H = self.dims.n_embd
+        P = prompts.shape[1]
+        dev = self.device
+        nxt, prv = (self.rank + 1) % S, (self.rank - 1) % S
+        eng.kv_reset(-1)
+        ev = lambda: torch.cuda.Event(enable_timing=True)
+        e_start, e_prefill, e_end = ev(), ev(), ev()
+        e_start.record()
+        seq = None
+        if self.first:
+            seq = torch.empty((B * M, P + n_new), dtype=torch.int32, device=dev)
+            seq[:, :P].copy_(prompts, non_blocking=True)
+        bufs = {"ids": torch.empty((B,), dtype=torch.int32, device=dev),
+                "hidden_prefill": torch.empty((B, P, H), dtype=torch.float32, device=dev),
+                "hidden_decode": torch.empty((B, H), dtype=torch.float32, device=dev)}
+        state = {"launches": 0, "step_events": []}
+
+        def exchange(send_t, recv_kind):
+            ops = []
+            if send_t is not None:
+                ops.append(dist.P2POp(dist.isend, send_t, nxt))
+            recv_t = bufs[recv_kind] if recv_kind is not None else None
+            if recv_t is not None:
+                ops.append(dist.P2POp(dist.irecv, recv_t, prv))
+            if ops:
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+            return recv_t
+
+        def on_ids(r, m, ids):
+            seq[m * B:(m + 1) * B, P + r] = ids
+
+        def compute(r, m, got):
+            slot0 = m * B
+            if r == 0:
+                x = seq[slot0:slot0 + B, :P].contiguous() if self.first else got
+                out = eng.prefill(x, slot0=slot0, use_cache=True, want_ids=self.last)
+            else:
+                out = eng.decode(got, slot0=slot0)
+            state["launches"] += eng.last_launch_count()
+            if self.last and timings and m == M - 1:
+                e = ev()
+                e.record()
+                state["step_events"].append(e)
+            if r == 0 and m == M - 1:
+                e_prefill.record()
+            return out["next_ids"] if self.last else out["hidden"]
+
+        run_ticks(self.rank, S, M, n_new, exchange, compute, on_ids)
+        if n_new <= 0:
+            e_prefill.record()
+        e_end.record()
+        torch.cuda.synchronize(dev)
+        result = seq.cpu() if self.first else None
+        if not timings:
+            return result
+        tm = {"prefill_ms": e_start.elapsed_time(e_prefill), "decode_ms": e_prefill.elapsed_time(e_end),
+              "step_ms": [], "launches": state["launches"]}
+        se = state["step_events"]
+        if self.last and len(se) > 1:
+            # one entry per round: time for ALL streams to advance one token
+            tm["step_ms"] = [se[i - 1].elapsed_time(se[i]) for i in range(1, len(se))]
+        gathered = [None] * S
+        dist.all_gather_object(gathered, tm["step_ms"])
+        tm["step_ms"] = gathered[S - 1]
+        return result, tm

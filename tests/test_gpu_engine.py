@@ -1,0 +1,242 @@
+"""Stage- and pipeline-level parity of the CUDA engine (through the C ABI) against
+ (1) the golden fixtures captured from the reference's own server.py (tests/golden/), and
+ (2) the CPU oracle on the same seeded weights and prompts.
+
+Tolerances (north_star: logits within a stated fp32/bf16 tolerance; greedy ids bit-exact
+wherever the top-2 margin exceeds it):
+  fp32 storage : |dlogit| <= 3e-4 ; ids must match where margin > 6e-4
+  bf16 storage : |dlogit| <= 0.06 vs the fp32 reference (weights, KV cache and GEMM-path
+                 activations are rounded to bf16; SURVEY.md §8(c) measured 0.031 max for an
+                 all-bf16 CPU run of 124M); ids must match where margin > 0.12; and
+                 |dlogit| <= 0.02 vs the oracle evaluated on bf16-rounded WEIGHTS (what is
+                 left is KV/activation rounding).
+Comparisons are teacher-forced on the reference's ids so one flip cannot cascade."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gpt2_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+TOL_F32, TOL_BF16, TOL_BF16_W = 3e-4, 0.06, 0.02
+
+
+@pytest.fixture(scope="module")
+def L():
+    import llm_sharding_demo_b200 as pkg
+    return pkg
+
+
+def load_golden(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    dims = O.GPT2Dims(**meta["dims"])
+    return z, meta, dims, O.init_weights(dims, meta["seed"], meta["recipe"])
+
+
+def make_stages(L, dims, w, n_stages, dtype, max_batch=1, flags=0, max_ctx=None):
+    pd = L.GPT2Dims(**dims.to_dict())
+    engines = []
+    for s, (b, e) in enumerate(L.split_layers(dims.n_layer, n_stages)):
+        eng = L.StageEngine(pd, b, e, has_embed=(s == 0), has_head=(s == n_stages - 1), dtype=dtype,
+                            max_batch=max_batch, max_ctx=max_ctx, flags=flags)
+        eng.load_weights(w)
+        engines.append(eng)
+    return engines
+
+
+def run_prefill(engines, ids, use_cache=True, want_logits="last"):
+    x = ids.to(DEV, torch.int32)
+    for eng in engines[:-1]:
+        x = eng.prefill(x, use_cache=use_cache)["hidden"]
+    return engines[-1].prefill(x, use_cache=use_cache, want_logits=want_logits, want_ids=True), x
+
+
+def run_decode(engines, tok):
+    x = tok.to(DEV, torch.int32)
+    for eng in engines[:-1]:
+        x = eng.decode(x)["hidden"]
+    return engines[-1].decode(x, want_logits=True)
+
+
+def rounded(w, dt):
+    """oracle weights as the engine stores them (matrices in dt; LN params and biases fp32)"""
+    return {k: (v.to(dt).float() if v.dim() == 2 else v) for k, v in w.items()}
+
+
+# ----------------------------------------------------------------------------- goldens, fp32
+@pytest.mark.parametrize("name", ["tiny_gpt2", "tiny_gpt2_dense", "mini", "mini32"])
+def test_reference_golden_fp32_two_stage(L, golden_dir, name):
+    z, meta, dims, w = load_golden(golden_dir, name)
+    assert meta["split_at"] == O.split_layers(dims.n_layer, 2)[0][1]
+    eng = make_stages(L, dims, w, 2, L.GP_F32)
+    prompt = torch.tensor(z["prompt_ids"]).unsqueeze(0)
+    ref_ids = torch.tensor(z["greedy_ids"])
+    P, n_new = prompt.shape[1], len(ref_ids) - prompt.shape[1]
+    # stateless full-sequence routes: /forward hidden and /forward_b logits for ALL T rows
+    out, hidden = run_prefill(eng, prompt, use_cache=False, want_logits="all")
+    np.testing.assert_allclose(hidden.cpu().numpy(), z["hidden_step0"], rtol=0, atol=TOL_F32)
+    ref0 = z["logits_step0"]
+    got0 = out["logits"][0].cpu().numpy()
+    np.testing.assert_allclose(got0 if ref0.shape[0] == P else got0[-1:], ref0, rtol=0, atol=TOL_F32)
+    assert eng[0].kv_lengths() == [0] and eng[1].kv_lengths() == [0]   # stateless: cache untouched
+    # cached decode, teacher-forced on the reference's greedy ids
+    out, _ = run_prefill(eng, prompt)
+    margins, ll = z["margins"], z["last_logits"]
+    for t in range(n_new):
+        if t > 0:
+            out = run_decode(eng, ref_ids[P + t - 1:P + t])
+        if margins[t] > 2 * TOL_F32:
+            assert int(out["next_ids"][0]) == int(ref_ids[P + t]), t
+        if ll.shape[0] == n_new or t in (0, n_new - 1):
+            ref_row = ll[t] if ll.shape[0] == n_new else ll[0 if t == 0 else 1]
+            np.testing.assert_allclose(out["logits"][0].cpu().numpy(), ref_row, rtol=0, atol=TOL_F32)
+    assert eng[0].kv_lengths() == [P + n_new - 1]
+
+
+@pytest.mark.parametrize("name", ["tiny_gpt2_dense", "mini", "mini32"])
+def test_reference_golden_generate_single_stage(L, golden_dir, name):
+    z, meta, dims, w = load_golden(golden_dir, name)
+    (eng,) = make_stages(L, dims, w, 1, L.GP_F32)
+    prompt = torch.tensor(z["prompt_ids"], dtype=torch.int32).unsqueeze(0)
+    ref_ids = z["greedy_ids"]
+    n_new = len(ref_ids) - prompt.shape[1]
+    got, tm = eng.generate(prompt, n_new, timings=True)
+    safe = 0   # tokens before the first sub-tolerance margin are bit-exact
+    while safe < n_new and z["margins"][safe] > 2 * TOL_F32:
+        safe += 1
+    assert got[0, :prompt.shape[1] + safe].tolist() == ref_ids[:prompt.shape[1] + safe].tolist()
+    assert safe >= 3
+    assert tm["decode_ms"] > 0 and eng.last_launch_count() > 0
+    # max_new_tokens = 0 returns the prompt (server.py:169,209) and 1 is prefill only
+    assert eng.generate(prompt, 0).tolist() == prompt.tolist()
+    assert eng.generate(prompt, 1)[0, -1] == ref_ids[prompt.shape[1]]
+    # graph replay and direct launches agree bit for bit
+    (eng2,) = make_stages(L, dims, w, 1, L.GP_F32, flags=2)
+    assert torch.equal(eng2.generate(prompt, n_new), got)
+
+
+# ----------------------------------------------------------------------- 124M golden (cfg 2)
+@pytest.mark.parametrize("dtype_name", ["f32", "bf16"])
+def test_gpt2_124m_golden(L, golden_dir, dtype_name):
+    z, meta, dims, w = load_golden(golden_dir, "gpt2_124m")
+    dtype, tol = (L.GP_F32, TOL_F32) if dtype_name == "f32" else (L.GP_BF16, TOL_BF16)
+    eng = make_stages(L, dims, w, 2, dtype, max_ctx=64)
+    prompt = torch.tensor(z["prompt_ids"]).unsqueeze(0)
+    ref_ids = torch.tensor(z["greedy_ids"])
+    P, n_new = 32, len(ref_ids) - 32
+    out, hidden = run_prefill(eng, prompt)
+    htol = 3e-4 if dtype_name == "f32" else 0.05
+    np.testing.assert_allclose(hidden[0, -1].cpu().numpy(), z["hidden_step0_last"], rtol=0, atol=htol)
+    np.testing.assert_allclose(out["logits"][0].cpu().numpy(), z["last_logits"][0], rtol=0, atol=tol)
+    worst = 0.0
+    for t in range(n_new):
+        if t > 0:
+            out = run_decode(eng, ref_ids[P + t - 1:P + t])
+        lg = out["logits"][0].cpu()
+        err = float((lg[torch.tensor(z["top8_idx"][t])] - torch.tensor(z["top8_val"][t])).abs().max())
+        worst = max(worst, err)
+        assert err <= tol, (t, err)
+        if z["margins"][t] > 2 * tol:
+            assert int(out["next_ids"][0]) == int(ref_ids[P + t]), t
+    print(f"124M {dtype_name}: worst top-8 logit error vs reference {worst:.3e}")
+    if dtype_name == "f32":
+        (single,) = make_stages(L, dims, w, 1, dtype, max_ctx=64)
+        got = single.generate(prompt.to(torch.int32), n_new)
+        assert got[0].tolist() == ref_ids.tolist()   # min reference margin 4.9e-2 >> 6e-4
+
+
+# -------------------------------------------------------------- oracle parity, both dtypes
+@pytest.mark.parametrize("dtype_name", ["f32", "bf16"])
+@pytest.mark.parametrize("preset,n_stages,B,P,n_new", [("mini", 1, 1, 5, 6), ("mini", 2, 3, 9, 5), ("mini", 4, 2, 33, 4),
+                                                        ("mini32", 2, 4, 7, 5), ("tiny-gpt2", 2, 2, 4, 5),
+                                                        ("mini", 2, 12, 6, 4)])
+def test_stage_pipeline_vs_oracle(L, dtype_name, preset, n_stages, B, P, n_new):
+    dims = O.PRESETS[preset]
+    w = O.init_weights(dims, 77, "dense")
+    dtype = L.GP_F32 if dtype_name == "f32" else L.GP_BF16
+    eng = make_stages(L, dims, w, n_stages, dtype, max_batch=B)
+    g = torch.Generator().manual_seed(5)
+    prompt = torch.randint(0, dims.vocab_size, (B, P), generator=g)
+    ref_ids, ref_logits = O.generate_cached(w, dims, prompt, n_new, n_stages=n_stages, return_logits=True)
+    if dtype_name == "bf16":
+        _, ref_logits_w = O.generate_cached(rounded(w, torch.bfloat16), dims, prompt, n_new, teacher=ref_ids,
+                                            return_logits=True)
+    margins = O.top2_margin(ref_logits)
+    tol = TOL_F32 if dtype_name == "f32" else TOL_BF16
+    out, _ = run_prefill(eng, prompt)
+    for t in range(n_new):
+        if t > 0:
+            out = run_decode(eng, ref_ids[:, P + t - 1])
+        lg = out["logits"].cpu()
+        assert float((lg - ref_logits[:, t]).abs().max()) <= tol, t
+        if dtype_name == "bf16":
+            assert float((lg - ref_logits_w[:, t]).abs().max()) <= TOL_BF16_W, t
+        for b in range(B):
+            if margins[b, t] > 2 * tol:
+                assert int(out["next_ids"][b]) == int(ref_ids[b, P + t]), (b, t)
+    for e in eng:
+        assert e.kv_lengths() == [P + n_new - 1] * B
+
+
+def test_pipeline_depth_does_not_change_results(L):
+    """S = 1, 2, 4 on identical weights: same logits (the stage boundary carries fp32)."""
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 5, "dense")
+    prompt = torch.tensor([[3, 1040, 7, 9, 11, 500]])
+    res = []
+    for S in (1, 2, 4):
+        eng = make_stages(L, dims, w, S, L.GP_BF16)
+        out, _ = run_prefill(eng, prompt)
+        o2 = run_decode(eng, out["next_ids"].cpu())
+        res.append((out["logits"].cpu(), o2["logits"].cpu()))
+    for a, b in zip(res[0], res[1]):
+        assert torch.equal(a, b)
+    for a, b in zip(res[0], res[2]):
+        assert torch.equal(a, b)
+
+
+def test_batch_rows_are_independent(L):
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 9, "dense")
+    (eng,) = make_stages(L, dims, w, 1, L.GP_BF16, max_batch=3)
+    g = torch.Generator().manual_seed(1)
+    prompts = torch.randint(0, dims.vocab_size, (3, 8), generator=g, dtype=torch.int32)
+    both = eng.generate(prompts, 6)
+    for b in range(3):
+        single = eng.generate(prompts[b:b + 1], 6)
+        assert torch.equal(single[0], both[b])
+
+
+def test_errors_are_reported_not_faulted(L):
+    dims = O.PRESETS["mini"]
+    pd = L.GPT2Dims(**dims.to_dict())
+    w = O.init_weights(dims, 1, "hf")
+    eng = L.StageEngine(pd, 0, 2, has_embed=True, has_head=False, dtype=L.GP_F32)
+    ids = torch.zeros((1, 4), dtype=torch.int32, device=DEV)
+    with pytest.raises(L.GPError, match="has not been loaded"):
+        eng.prefill(ids)
+    eng.load_weights(w)
+    with pytest.raises(L.GPError, match="n_positions"):
+        eng.prefill(torch.zeros((1, dims.n_positions + 1), dtype=torch.int32, device=DEV))
+    with pytest.raises(L.GPError, match="single-stage"):
+        eng.generate(torch.zeros((1, 4), dtype=torch.int32), 2)
+    lib = L.load_library()
+    import ctypes as C
+    t = w["h.3.ln_1.weight"]
+    shape = (C.c_int64 * 1)(*t.shape)
+    rc = lib.gp_load_weight(eng._h, b"h.3.ln_1.weight", C.c_void_p(t.data_ptr()), shape, 1)
+    assert rc == -1 and b"does not belong to this stage" in lib.gp_last_error(eng._h)
+    t = w["h.0.attn.c_attn.weight"].t().contiguous()
+    shape = (C.c_int64 * 2)(*t.shape)
+    rc = lib.gp_load_weight(eng._h, b"h.0.attn.c_attn.weight", C.c_void_p(t.data_ptr()), shape, 2)
+    assert rc == -1 and b"expected" in lib.gp_last_error(eng._h)
+    (full,) = make_stages(L, dims, w, 1, L.GP_F32)
+    with pytest.raises(L.GPError, match="exceeds the context"):
+        full.generate(torch.zeros((1, 60), dtype=torch.int32), 10)
+    with pytest.raises(L.GPError, match="out of range"):
+        full.generate(torch.full((1, 4), dims.vocab_size, dtype=torch.int32), 2)

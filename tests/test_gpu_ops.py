@@ -1,0 +1,171 @@
+"""Op-level parity: every hot-path CUDA kernel, called through the C ABI, against the CPU
+oracle's restatement of the same op on the same seeded tensors.
+
+Tolerances (stated per north_star): fp32 storage -> 2e-4 abs on O(1) values (only the
+summation order differs); bf16 storage -> compared against the oracle evaluated on the SAME
+bf16-rounded operands with 2e-3 abs (fp32 accumulation in both), i.e. the kernel arithmetic is
+checked independently of the quantisation, whose end-to-end effect test_gpu_engine.py bounds."""
+import math
+
+import pytest
+import torch
+
+from oracle import gpt2_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+TOL = {torch.float32: 2e-4, torch.bfloat16: 2e-3}
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from llm_sharding_demo_b200 import ops as _ops
+    return _ops
+
+
+def rnd(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(*shape, generator=g) * scale
+
+
+def q(t, dt):
+    """storage rounding: what the kernel sees, as fp32 for the oracle"""
+    return t.to(dt).float()
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("H", [2, 96, 768, 1600])
+def test_embed(ops, dt, H):
+    V, NP, M = 523, 64, 9
+    wte, wpe = rnd(V, H, seed=1, scale=0.02), rnd(NP, H, seed=2, scale=0.02)
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, V, (M,), generator=g, dtype=torch.int32)
+    pos = torch.randint(0, NP, (M,), generator=g, dtype=torch.int32)
+    got = ops.embed(ids.to(DEV), pos.to(DEV), wte.to(DEV, dt), wpe.to(DEV, dt)).cpu()
+    ref = q(wte, dt)[ids.long()] + q(wpe, dt)[pos.long()]
+    assert torch.equal(got, ref)  # a gather and one add: bit-exact
+
+
+@pytest.mark.parametrize("out_bf16", [False, True])
+@pytest.mark.parametrize("M,H", [(1, 768), (5, 2), (33, 1600), (7, 1024), (3, 4100)])
+def test_layernorm(ops, M, H, out_bf16):
+    x = rnd(M, H, seed=4) * 3 + 0.5
+    gm, bt = 1 + 0.1 * rnd(H, seed=5), 0.1 * rnd(H, seed=6)
+    got = ops.layernorm(x.to(DEV), gm.to(DEV), bt.to(DEV), 1e-5, out_bf16).cpu().float()
+    ref = O.layer_norm(x, gm, bt, 1e-5)
+    if out_bf16:
+        ref = ref.bfloat16().float()
+    assert (got - ref).abs().max() <= (2e-2 if out_bf16 else 2e-5)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,N,K", [(1, 2304, 768), (1, 768, 3072), (3, 6, 2), (8, 1041, 128), (2, 4800, 1600),
+                                   (4, 1600, 6400), (1, 50257, 768)])
+@pytest.mark.parametrize("variant", ["plain", "ln_gelu", "bias_res"])
+def test_gemv(ops, dt, B, N, K, variant):
+    x = rnd(B, K, seed=7)
+    W = rnd(K, N, seed=8, scale=0.02)            # Conv1D layout [in, out]
+    Wt = W.t().contiguous()                      # engine layout [out, in]
+    bias, res = rnd(N, seed=9, scale=0.05), rnd(B, N, seed=10)
+    gm, bt = 1 + 0.1 * rnd(K, seed=11), 0.1 * rnd(K, seed=12)
+    d = lambda t: t.to(DEV)
+    if variant == "plain":
+        got = ops.gemv(d(x), Wt.to(DEV, dt))
+        ref = x @ q(W, dt)
+    elif variant == "ln_gelu":
+        got = ops.gemv(d(x), Wt.to(DEV, dt), bias=d(bias), ln=(d(gm), d(bt)), gelu=True)
+        ref = O.gelu_new(O.conv1d(O.layer_norm(x, gm, bt, 1e-5), q(W, dt), bias))
+    else:
+        got = ops.gemv(d(x), Wt.to(DEV, dt), bias=d(bias), residual=d(res))
+        ref = O.conv1d(x, q(W, dt), bias) + res
+    assert (got.cpu() - ref).abs().max() <= TOL[dt]
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,N,K", [(4, 6, 2), (40, 384, 128), (65, 1041, 128), (130, 2304, 768), (32, 768, 3072)])
+@pytest.mark.parametrize("variant", ["bias", "gelu_bf16out", "res"])
+def test_gemm_simt(ops, dt, M, N, K, variant):
+    A = rnd(M, K, seed=13)
+    W = rnd(K, N, seed=14, scale=0.02)
+    bias, res = rnd(N, seed=15, scale=0.05), rnd(M, N, seed=16)
+    Ad, Wd = A.to(DEV, dt), W.t().contiguous().to(DEV, dt)
+    if variant == "bias":
+        got = ops.gemm(Ad, Wd, bias=bias.to(DEV), simt=True)
+        ref = O.conv1d(q(A, dt), q(W, dt), bias)
+        tol = TOL[dt]
+    elif variant == "gelu_bf16out":
+        if dt != torch.bfloat16:
+            pytest.skip("bf16 output only exists in bf16 mode")
+        got = ops.gemm(Ad, Wd, bias=bias.to(DEV), gelu=True, out_bf16=True, simt=True).float()
+        ref = O.gelu_new(O.conv1d(q(A, dt), q(W, dt), bias)).bfloat16().float()
+        tol = 2e-2
+    else:
+        got = ops.gemm(Ad, Wd, bias=bias.to(DEV), residual=res.to(DEV), simt=True)
+        ref = O.conv1d(q(A, dt), q(W, dt), bias) + res
+        tol = TOL[dt]
+    assert (got.cpu() - ref).abs().max() <= tol
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,nh,d,max_ctx,lens", [(1, 12, 64, 1024, [160]), (3, 2, 64, 64, [1, 64, 37]),
+                                                 (2, 2, 1, 32, [5, 32]), (2, 3, 32, 48, [48, 7]),
+                                                 (2, 25, 64, 1024, [1024, 513])])
+def test_attn_decode(ops, dt, B, nh, d, max_ctx, lens):
+    H = nh * d
+    qv = rnd(B, H, seed=17)
+    kc, vc = rnd(B, nh, max_ctx, d, seed=18), rnd(B, nh, max_ctx, d, seed=19)
+    got = ops.attn_decode(qv.to(DEV), kc.to(DEV, dt), vc.to(DEV, dt),
+                          torch.tensor(lens, dtype=torch.int32, device=DEV)).cpu()
+    for b in range(B):
+        T = lens[b]
+        qq = qv[b].view(1, nh, 1, d)
+        k, v = q(kc, dt)[b:b + 1, :, :T], q(vc, dt)[b:b + 1, :, :T]
+        ref = O.attention(qq, k, v, T - 1).transpose(1, 2).reshape(H)
+        assert (got[b] - ref).abs().max() <= TOL[dt], b
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,T,nh,d", [(1, 32, 12, 64), (2, 100, 2, 64), (1, 4, 2, 1), (2, 7, 3, 32), (1, 200, 3, 64)])
+def test_attn_prefill(ops, dt, B, T, nh, d):
+    H = nh * d
+    qkv = rnd(B, T, 3 * H, seed=20)
+    got = ops.attn_prefill(qkv.to(DEV, dt), nh).cpu().float()
+    x = q(qkv, dt)
+    qq, k, v = [t.view(B, T, nh, d).transpose(1, 2) for t in x.split(H, dim=2)]
+    ref = O.attention(qq, k, v, 0).transpose(1, 2).reshape(B, T, H)
+    if dt == torch.bfloat16:
+        ref = ref.bfloat16().float()
+    assert (got - ref).abs().max() <= (2e-2 if dt == torch.bfloat16 else 2e-4)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,V,H", [(1, 50257, 768), (5, 1041, 128), (2, 50257, 2), (8, 523, 96), (3, 50257, 1600)])
+def test_lmhead_argmax(ops, dt, B, V, H):
+    x = rnd(B, H, seed=21)
+    wte = rnd(V, H, seed=22, scale=0.02)
+    gm, bt = 1 + 0.1 * rnd(H, seed=23), 0.1 * rnd(H, seed=24)
+    scratch = ops.lmhead_scratch(DEV)
+    for rep in range(2):   # second call checks that the ticket in `scratch` was re-armed
+        ids, logits = ops.lmhead_argmax(x.to(DEV), gm.to(DEV), bt.to(DEV), wte.to(DEV, dt), want_logits=True,
+                                        scratch=scratch)
+        ref = O.layer_norm(x, gm, bt, 1e-5) @ q(wte, dt).t()
+        assert (logits.cpu() - ref).abs().max() <= TOL[dt]
+        # the fused argmax must be the argmax of the kernel's own logits, lowest index on ties
+        assert torch.equal(ids.cpu().long(), torch.argmax(logits.cpu(), dim=-1))
+        margin = O.top2_margin(ref)
+        for b in range(B):
+            if margin[b] > 2 * TOL[dt]:
+                assert int(ids[b]) == int(torch.argmax(ref[b]))
+    ids2 = ops.lmhead_argmax(x.to(DEV), gm.to(DEV), bt.to(DEV), wte.to(DEV, dt), scratch=scratch)
+    assert torch.equal(ids2.cpu(), ids.cpu())
+
+
+def test_lmhead_argmax_ties_pick_lowest_index(ops):
+    V, H = 4099, 64
+    x = torch.ones(1, H)
+    wte = torch.zeros(V, H)
+    wte[[7, 1000, 4098]] = 0.5   # three equal maxima
+    gm, bt = torch.zeros(H), torch.ones(H)   # LN output == 1 everywhere
+    ids = ops.lmhead_argmax(x.to(DEV), gm.to(DEV), bt.to(DEV), wte.to(DEV))
+    assert int(ids[0]) == 7
