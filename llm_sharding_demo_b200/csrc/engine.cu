@@ -366,11 +366,11 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
     TRY(alloc((void**)&e->lnf_g, H * 4)); TRY(alloc((void**)&e->lnf_b, H * 4));
     e->required.insert("ln_f.weight"); e->required.insert("ln_f.bias");
     TRY(alloc(&e->lm_scratch, (size_t)gp_lmhead_scratch_bytes(kGemvMaxBatch, e->V)));
-    TRYCK(cudaMemset(e->lm_scratch, 0, kLmheadScratchHeader));
+    TRYCK(cudaMemsetAsync(e->lm_scratch, 0, kLmheadScratchHeader, e->stream));
   }
   const size_t MT = e->cfg.max_tokens, MB = cfg->max_batch;
   TRY(alloc((void**)&e->lens, MB * sizeof(int32_t)));
-  TRYCK(cudaMemset(e->lens, 0, MB * sizeof(int32_t)));
+  TRYCK(cudaMemsetAsync(e->lens, 0, MB * sizeof(int32_t), e->stream));
   TRY(alloc((void**)&e->h, MT * H * 4));
   TRY(alloc(&e->xa, MT * H * esz));
   TRY(alloc(&e->qkv, MT * 3 * H * esz));
@@ -382,6 +382,7 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRY(alloc((void**)&e->seq, MB * (size_t)e->seq_stride * sizeof(int32_t)));
   TRY(alloc((void**)&e->prompt, MB * (size_t)cfg->n_positions * sizeof(int32_t)));
   TRY(alloc((void**)&e->mailbox, MB * sizeof(int32_t)));
+  TRYCK(cudaStreamSynchronize(e->stream));
 #undef TRY
 #undef TRYCK
   *out = e;
@@ -436,7 +437,10 @@ int gp_load_weight(gp_engine* e, const char* name, const float* data_host, const
   if (R != eR || C != eC) { set_err(e, "gp_load_weight: '%s' has shape [%lld,%lld], expected [%lld,%lld]", name, (long long)R, (long long)C, (long long)eR, (long long)eC); return GP_EINVAL; }
   const size_t n = (size_t)R * C;
   if (keep_f32) {
-    CK(e, cudaMemcpy(dst, data_host, n * sizeof(float), cudaMemcpyHostToDevice));
+    // stream-ordered copy + sync: a plain cudaMemcpy from pageable memory may return before
+    // the DMA lands and is only ordered against the legacy stream
+    CK(e, cudaMemcpyAsync(dst, data_host, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(e, cudaStreamSynchronize(e->stream));
   } else {
     if (e->stage_floats < n) {
       if (e->stage) cudaFree(e->stage);
@@ -444,7 +448,7 @@ int gp_load_weight(gp_engine* e, const char* name, const float* data_host, const
       CK(e, cudaMalloc((void**)&e->stage, n * sizeof(float)));
       e->stage_floats = n;
     }
-    CK(e, cudaMemcpy(e->stage, data_host, n * sizeof(float), cudaMemcpyHostToDevice));
+    CK(e, cudaMemcpyAsync(e->stage, data_host, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
     CK(e, launch_convert(e->stage, dst, (int)R, (int)C, transpose, e->cfg.dtype, e->stream));
     CK(e, cudaStreamSynchronize(e->stream));
   }
