@@ -182,6 +182,25 @@ int gp_op_lmhead_argmax(const float* x, const float* gamma, const float* beta, c
                         int32_t* ids_out, float* logits_out, void* scratch, int32_t B, int32_t V,
                         int32_t H, float eps, int32_t dtype, void* stream);
 
+/* Same computation as gp_op_lmhead_argmax for callers that cannot provide (or allocate)
+ * scratch memory.  No counterpart in the reference: it exists for hosts that run this kernel
+ * where device allocation is impossible or unwelcome - all HBM already belongs to another
+ * allocator (a serving runtime's or framework's pool), or the decode loop cannot tolerate the
+ * device-wide synchronisation of cudaMalloc/cudaFree, or the caller owns no allocator at all.
+ * The partial results and arrival ticket live in a fixed 76,032-byte array inside the library
+ * (resident on every GPU that loads it, until process exit); the call performs no cudaMalloc,
+ * cudaFree or other allocating call.  Limits: 1 <= B <= 8 and padded(B)*H*4 <= 204,800 bytes of
+ * shared memory; anything larger returns GP_EINVAL with the limits in gp_last_error(NULL).
+ * The first call on each device looks up the array's device address
+ * (cudaGetSymbolAddress) and sets kernel attributes: make that first call before starting any
+ * stream capture on that device.  All calls share the one array: it still holds the previous
+ * call's partials (the ticket is cleared on `stream` before every launch), and two calls whose
+ * kernels overlap on the GPU - different streams, or different host threads - race on it;
+ * serialise them.  Arguments as gp_op_lmhead_argmax, minus `scratch`. */
+int gp_op_lmhead_argmax_static(const float* x, const float* gamma, const float* beta, const void* wte,
+                               int32_t* ids_out, float* logits_out, int32_t B, int32_t V, int32_t H,
+                               float eps, int32_t dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

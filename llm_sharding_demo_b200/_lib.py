@@ -54,6 +54,7 @@ SIGNATURES = {
     "gp_op_attn_prefill": (C.c_int, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "gp_lmhead_scratch_bytes": (C.c_int64, [_I, _I]),
     "gp_op_lmhead_argmax": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _I, _P]),
+    "gp_op_lmhead_argmax_static": (C.c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _I, _P]),
 }
 
 _lib = None

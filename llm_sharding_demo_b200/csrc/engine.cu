@@ -287,6 +287,10 @@ int parse_layer(const char* name, int* layer, const char** rest) {
 
 }  // namespace
 
+namespace gp {
+void record_error(const char* msg) { set_err(nullptr, "%s", msg); }
+}  // namespace gp
+
 // =========================================================================== C ABI
 extern "C" {
 

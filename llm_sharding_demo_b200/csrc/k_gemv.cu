@@ -298,3 +298,75 @@ cudaError_t launch_lmhead_argmax(const LmheadParams& p, int dtype, cudaStream_t 
 }
 
 }  // namespace gp
+
+// ------------------------------------------------------------------------------------------
+// gp_op_lmhead_argmax_static: the fused ln_f + lm_head + argmax with NO caller- or
+// library-allocated scratch.  Who needs this: a host that embeds the kernel in a decode loop
+// where device allocation is off the table - the process's HBM has been handed in full to
+// another allocator (a serving runtime or framework pool, so cudaMalloc fails or fragments
+// it), or the loop is latency-critical and cannot afford the device-wide synchronisation a
+// cudaMalloc/cudaFree implies, or the caller simply owns no allocator it could get the
+// `scratch` argument of gp_op_lmhead_argmax from.  The cross-CTA partials and the arrival
+// ticket live in the fixed array below instead; every GPU that loads this library carries
+// its kStaticScratchBytes until the process exits.
+#include <cstdio>
+namespace gp {
+namespace {
+constexpr size_t kStaticScratchBytes =
+    kLmheadScratchHeader + (size_t)kLmheadMaxGrid * kGemvMaxBatch * (sizeof(float) + sizeof(int));  // 76,032 B
+static __device__ __align__(256) unsigned char g_lmhead_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+void* g_static_scratch_addr[kMaxDevices];  // device address of the array, per CUDA ordinal
+bool g_static_scratch_ready[kMaxDevices];
+}  // namespace
+}  // namespace gp
+
+extern "C" int gp_op_lmhead_argmax_static(const float* x, const float* gamma, const float* beta, const void* wte,
+                                          int32_t* ids_out, float* logits_out, int32_t B, int32_t V, int32_t H,
+                                          float eps, int32_t dtype, void* stream) {
+  using namespace gp;
+  auto fail = [&](int code, const char* msg, const char* detail) {
+    char buf[400];
+    snprintf(buf, sizeof buf, "gp_op_lmhead_argmax_static: %s%s", msg, detail);
+    record_error(buf);  // readable through gp_last_error(NULL)
+    return code;
+  };
+  if (!x || !wte || !ids_out) return fail(GP_EINVAL, "NULL argument", "");
+  if (dtype != GP_F32 && dtype != GP_BF16) return fail(GP_EINVAL, "dtype must be GP_F32 or GP_BF16", "");
+  // the fixed array holds partials for at most kGemvMaxBatch rows; x must fit shared memory
+  if (B < 1 || B > kGemvMaxBatch || V < 1 || H < 1 || !gemv_supported(B, H)) {
+    char lim[160];
+    snprintf(lim, sizeof lim, " (got B=%d V=%d H=%d; limits: 1 <= B <= %d and padded(B)*H*4 <= %d bytes)", B, V, H,
+             kGemvMaxBatch, kGemvMaxSmem);
+    return fail(GP_EINVAL, "size beyond what the static scratch serves", lim);
+  }
+  int dev = -1;
+  cudaError_t ce = cudaGetDevice(&dev);
+  if (ce != cudaSuccess) return fail(GP_ECUDA, "cudaGetDevice: ", cudaGetErrorString(ce));
+  if (dev < 0 || dev >= kMaxDevices) return fail(GP_EINVAL, "device ordinal out of range", "");
+  if (!g_static_scratch_ready[dev]) {
+    // One-time set-up on this device (it is current).  In host code the array's NAME is only a
+    // host-side handle, not a device address: handing it to a kernel would fault, or silently hit
+    // the wrong memory where the GPU can reach host memory.  Ask the runtime for the real address.
+    void* p = nullptr;
+    ce = cudaGetSymbolAddress(&p, g_lmhead_static_scratch);
+    if (ce != cudaSuccess || p == nullptr)
+      return fail(GP_ECUDA, "cudaGetSymbolAddress: ", cudaGetErrorString(ce));
+    if ((ce = init_gemv_attrs()) != cudaSuccess) return fail(GP_ECUDA, "kernel attribute set-up: ", cudaGetErrorString(ce));
+    g_static_scratch_addr[dev] = p;
+    g_static_scratch_ready[dev] = true;
+  }
+  void* scratch = g_static_scratch_addr[dev];
+  cudaStream_t s = (cudaStream_t)stream;
+  // The array keeps whatever the previous call (or an aborted one) left; only the arrival
+  // ticket has to start at zero, the partials are fully rewritten by every launch.
+  ce = cudaMemsetAsync(scratch, 0, kLmheadScratchHeader, s);
+  if (ce != cudaSuccess) return fail(GP_ECUDA, "cudaMemsetAsync: ", cudaGetErrorString(ce));
+  LmheadParams p;
+  p.x = x; p.ldx = H; p.ln_g = gamma; p.ln_b = beta; p.eps = eps; p.wte = wte; p.B = B; p.V = V; p.H = H;
+  p.ids_out = ids_out; p.logits_out = logits_out; p.ldl = V; p.scratch = scratch;
+  ce = launch_lmhead_argmax(p, dtype, s);
+  if (ce != cudaSuccess) return fail(ce == cudaErrorInvalidValue ? GP_EINVAL : GP_ECUDA, "launch: ", cudaGetErrorString(ce));
+  return GP_OK;
+}

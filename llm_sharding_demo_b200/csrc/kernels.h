@@ -76,6 +76,9 @@ cudaError_t launch_convert(const float* src, void* dst, int R, int C, bool trans
 // gather rows: dst[b,:] = src[(b*T + T-1),:]  (last position of each sequence)
 cudaError_t launch_gather_last(const float* src, float* dst, int B, int T, int H, cudaStream_t s);
 
+// stores `msg` as this thread's last error (what gp_last_error(NULL) returns); engine.cu
+void record_error(const char* msg);
+
 // ---- tcgen05 GEMM (gemm_tcgen05.cu)
 bool gemm_tc_supported(int M, int N, int K);
 cudaError_t init_gemm_tc();

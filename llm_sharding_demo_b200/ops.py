@@ -98,3 +98,18 @@ def lmhead_argmax(x, gamma, beta, wte, eps=1e-5, want_logits=False, scratch=None
     check(lib.gp_op_lmhead_argmax(_p(x), _p(gamma), _p(beta), _p(wte), _p(ids), _p(logits), _p(scratch), B, V, H, eps,
                                   _dt(wte), _s(x)))
     return (ids, logits) if want_logits else ids
+
+
+def lmhead_argmax_static(x, gamma, beta, wte, eps=1e-5, want_logits=False):
+    """ln_f + lm_head + argmax for callers that cannot allocate device memory: like
+    `lmhead_argmax` but the kernel's cross-CTA scratch is a fixed array inside the library, so
+    nothing is allocated by the call itself (the outputs here are ordinary caller tensors).
+    B <= 8; calls that overlap on the GPU race on the shared array, so keep them on one stream."""
+    lib = load_library()
+    B, H = x.shape
+    V = wte.shape[0]
+    ids = torch.empty((B,), dtype=torch.int32, device=x.device)
+    logits = torch.empty((B, V), dtype=torch.float32, device=x.device) if want_logits else None
+    check(lib.gp_op_lmhead_argmax_static(_p(x), _p(gamma), _p(beta), _p(wte), _p(ids), _p(logits), B, V, H, eps,
+                                         _dt(wte), _s(x)))
+    return (ids, logits) if want_logits else ids
