@@ -1,8 +1,311 @@
-// placeholder: replaced by the tcgen05 + TMA GEMM
+// tcgen05 + TMA GEMM for prefill and batched decode (K3/K5/K6/K7 of SURVEY.md §2.3):
+//     out[m,n] = epi( sum_k A[m,k] * Wt[n,k] + bias[n] ) (+ residual[m,n])
+// "Weights-stationary" operand assignment: the 128-row tcgen05 operand is a tile of Wt[N,K]
+// (the layout the GEMV kernels stream), the N-side operand is a tile of the activations
+// A[M,K].  The accumulator D^T[n, m] lives in TMEM: lane = weight row n, column = token m.
+// Small M (batched decode, short prompts) therefore costs a narrow UMMA_N instead of a mostly
+// empty 128-row tile, and the epilogue's global accesses are coalesced along n.
+//
+// Pipeline: warp 0 = TMA producer (cp.async.bulk.tensor, SWIZZLE_128B tiles, mbarrier
+// complete_tx), warp 1 = TMEM allocator + single-thread tcgen05.mma issuer (tcgen05.commit
+// releases smem stages and finally signals the epilogue), warps 2..5 = epilogue (tcgen05.ld
+// 32x32b, bias / gelu_new / residual, coalesced stores).
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
 #include "kernels.h"
+
 namespace gp {
-bool gemm_tc_supported(int, int, int) { return false; }
-cudaError_t init_gemm_tc() { return cudaSuccess; }
-cudaError_t launch_gemm_tc(const void*, int, const void*, const float*, const float*, int, void*, int, int, int, int,
-                           uint32_t, cudaStream_t) { return cudaErrorNotSupported; }
+namespace {
+
+constexpr int kBlockN = 128;  // weight rows per CTA  (UMMA M)
+constexpr int kBlockK = 64;   // bf16 elements per k-block = 128 bytes = one swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kThreads = 192;
+constexpr int kWBytes = kBlockN * kBlockK * 2;  // 16 KB
+
+template <int BM> struct Cfg {
+  static constexpr int kABytes = BM * kBlockK * 2;
+  static constexpr int kStageBytes = kWBytes + kABytes;
+  static constexpr int kStages = (BM <= 32) ? 8 : (BM <= 64 ? 7 : 6);
+  static constexpr int kTmemCols = BM < 32 ? 32 : BM;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor):
+//  [0,14) start>>4 | [16,30) LBO>>4 (unused for swizzled K-major) | [32,46) SBO>>4 = 1024 B
+//  between 8-row groups | [46,48) version = 1 | [61,64) layout = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// kind::f16 instruction descriptor (cute::UMMA::InstrDescriptor): c=F32 [4,6)=1, a=BF16
+// [7,10)=1, b=BF16 [10,13)=1, both K-major (bits 15,16 = 0), N>>3 at [17,23), M>>4 at [24,29)
+__host__ __device__ constexpr uint32_t make_idesc(int umma_m, int umma_n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(umma_n >> 3) << 17) | ((uint32_t)(umma_m >> 4) << 24);
+}
+
+template <typename OT> __device__ __forceinline__ void store1(OT* p, float v) { *p = from_f<OT>(v); }
+
+template <int BM, typename OT>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
+               const float* __restrict__ bias, const float* residual, int ldr, OT* out, int ldo, int M, int N, int K,
+               uint32_t flags) {
+  using C = Cfg<BM>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sW = smem;
+  uint8_t* sA = smem + C::kStages * kWBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty = full + C::kStages;
+  uint64_t* tmem_full = empty + C::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * kBlockN, m0 = blockIdx.y * BM;
+  const int nk = (K + kBlockK - 1) / kBlockK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < nk; ++kb) {
+        const int s = kb % C::kStages;
+        const uint32_t ph = (kb / C::kStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], C::kStageBytes);
+        tma_load_2d(sW + s * kWBytes, &tmW, kb * kBlockK, n0, &full[s]);
+        tma_load_2d(sA + s * C::kABytes, &tmA, kb * kBlockK, m0, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kBlockN, BM < 16 ? 16 : BM);
+      for (int kb = 0; kb < nk; ++kb) {
+        const int s = kb % C::kStages;
+        const uint32_t ph = (kb / C::kStages) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint64_t adesc = make_desc(smem_u32(sW + s * kWBytes));
+        const uint64_t bdesc = make_desc(smem_u32(sA + s * C::kABytes));
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // advance 16 elements = 32 bytes inside the 128-byte swizzle row: +2 in the >>4 address field
+          tc_mma_bf16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+        }
+        tc_commit(&empty[s]);  // frees the stage once these MMAs have read it
+      }
+      tc_commit(tmem_full);    // accumulator complete
+    }
+  } else {
+    // epilogue: warp w may touch TMEM lanes [32*(w%4), 32*(w%4)+32)
+    const int q = warp & 3;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const int n = n0 + q * 32 + lane;
+    const bool n_ok = n < N;
+    const float bv = (bias != nullptr && n_ok) ? bias[n] : 0.f;
+    const bool gelu = flags & GP_EPI_GELU;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BM; c0 += 16) {
+      if (m0 + c0 >= M) break;  // warp-uniform
+      uint32_t r[16];
+      tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int m = m0 + c0 + j;
+        if (n_ok && m < M) {
+          float v = __uint_as_float(r[j]) + bv;
+          if (gelu) v = gelu_new(v);
+          if (residual != nullptr) v += residual[(size_t)m * ldr + n];
+          store1(out + (size_t)m * ldo + n, v);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::kTmemCols)
+                 : "memory");
+  }
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+std::mutex g_mu;
+std::map<std::tuple<const void*, int, int, int>, CUtensorMap> g_maps;
+
+cudaError_t get_encode() {
+  if (g_encode) return cudaSuccess;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess) return e;
+  if (qres != cudaDriverEntryPointSuccess || fn == nullptr) return cudaErrorNotSupported;
+  g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  return cudaSuccess;
+}
+
+// 2-D bf16 row-major [rows, cols] tensor, box [box_rows, 64], 128-byte swizzle, zero OOB fill
+cudaError_t tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto key = std::make_tuple(ptr, rows, cols, box_rows);
+  auto it = g_maps.find(key);
+  if (it != g_maps.end()) {
+    *out = it->second;
+    return cudaSuccess;
+  }
+  cudaError_t e = get_encode();
+  if (e != cudaSuccess) return e;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = g_encode(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps[key] = m;
+  *out = m;
+  return cudaSuccess;
+}
+
+template <int BM, typename OT>
+cudaError_t launch_t(const CUtensorMap& tw, const CUtensorMap& ta, const float* bias, const float* residual, int ldr,
+                     void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s) {
+  dim3 grid((N + kBlockN - 1) / kBlockN, (M + BM - 1) / BM);
+  gemm_tc_kernel<BM, OT><<<grid, kThreads, Cfg<BM>::kSmemBytes, s>>>(tw, ta, bias, residual, ldr, (OT*)out, ldo, M, N,
+                                                                    K, flags);
+  return cudaGetLastError();
+}
+
+template <int BM, typename OT> cudaError_t set_attr() {
+  return cudaFuncSetAttribute(gemm_tc_kernel<BM, OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BM>::kSmemBytes);
+}
+
+}  // namespace
+
+bool gemm_tc_supported(int M, int N, int K) {
+  // TMA needs 16-byte aligned row strides: K % 8 == 0 (bf16).  Tails in M, N, K are zero-filled.
+  return M >= 1 && N >= 1 && K >= 8 && (K % 8) == 0;
+}
+
+cudaError_t init_gemm_tc() {
+  cudaError_t e;
+  if ((e = get_encode()) != cudaSuccess) return e;
+  if ((e = set_attr<32, float>()) != cudaSuccess) return e;
+  if ((e = set_attr<32, bf16>()) != cudaSuccess) return e;
+  if ((e = set_attr<128, float>()) != cudaSuccess) return e;
+  if ((e = set_attr<128, bf16>()) != cudaSuccess) return e;
+  return cudaSuccess;
+}
+
+cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* bias, const float* residual, int ldr,
+                           void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s) {
+  if (!gemm_tc_supported(M, N, K) || lda != K) return cudaErrorInvalidValue;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Wt) & 15)) return cudaErrorInvalidValue;
+  const int BM = (M <= 32) ? 32 : 128;
+  CUtensorMap tw, ta;
+  cudaError_t e;
+  if ((e = tensor_map(Wt, N, K, kBlockN, &tw)) != cudaSuccess) return e;
+  if ((e = tensor_map(A, M, K, BM, &ta)) != cudaSuccess) return e;
+  const bool obf = flags & GP_OUT_BF16;
+  if (BM == 32)
+    return obf ? launch_t<32, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s)
+               : launch_t<32, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s);
+  return obf ? launch_t<128, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s)
+             : launch_t<128, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s);
+}
+
 }  // namespace gp

@@ -1,0 +1,207 @@
+"""FastAPI mirror of the reference's `server.py` API surface on top of the CUDA engine.
+
+Same three routes, request bodies, defaults, env vars and role-gate behaviour:
+  POST /forward    {"input_ids":[int]}            -> {"hidden_states":[[[float]*H]*T]}   (server.py:132-140)
+  POST /forward_b  {"hidden_states":[B][T][H]}    -> {"logits":[B][T][V]}                (server.py:143-151)
+  POST /generate   {"prompt":str,"max_new_tokens":int=20} -> {"generated":str}           (server.py:154-210)
+Env: MODEL_ID, SHARD_ROLE (a|b|coordinator), SPLIT_AT, SHARD_A_SERVICE, SHARD_B_SERVICE, SHARD_PORT
+(server.py:20-25).  New optional env: GP_DTYPE (bf16|f32), GP_SEED, GP_COORD_MODE (device|http).
+
+Differences, all deliberate:
+  * selection is greedy (BASELINE.json north_star) instead of temperature/top-k sampling;
+  * a coordinator that has a GPU runs the whole loop on the device (`gp_generate`); with
+    GP_COORD_MODE=http it drives /forward and /forward_b of remote shards exactly like the
+    reference, so unmodified reference shards or coordinators interoperate;
+  * sequences longer than n_positions are refused with a clear error (the reference would
+    raise IndexError -> 500);
+  * weights: seeded random init from the model's GPT2Config shape (no checkpoints offline); a
+    `weights` dict (HF state_dict) can be passed to `create_app`.
+"""
+from __future__ import annotations
+
+import os
+import threading
+from typing import Dict, Optional
+
+import torch
+from pydantic import BaseModel
+
+from . import weights as W
+from ._lib import GP_BF16, GP_F32
+
+
+# request bodies: same names, fields and default as server.py:116-124
+class InputIDs(BaseModel):
+    input_ids: list[int]
+
+
+class HiddenStates(BaseModel):
+    hidden_states: list  # nested lists (batch, seq, hidden_dim); untyped like server.py:120
+
+
+class GenerateReq(BaseModel):
+    prompt: str
+    max_new_tokens: int = 20
+
+
+class ByteTokenizer:
+    """Offline stand-in when the GPT-2 BPE files are unavailable: ids are UTF-8 bytes."""
+
+    def encode(self, text):
+        return list(text.encode("utf-8"))
+
+    def decode(self, ids, skip_special_tokens=True):
+        return bytes(int(i) & 0xFF for i in ids).decode("utf-8", errors="replace")
+
+
+def load_tokenizer(model_id: str):
+    try:  # tokenizer stays host-side, as in server.py:40,160,209
+        from transformers import AutoTokenizer
+        return AutoTokenizer.from_pretrained(model_id, local_files_only=True)
+    except Exception:
+        return ByteTokenizer()
+
+
+def read_env(env=None) -> Dict:
+    env = os.environ if env is None else env
+    return {
+        "MODEL_ID": env.get("MODEL_ID", "sshleifer/tiny-gpt2"),
+        "SHARD_ROLE": env.get("SHARD_ROLE", "coordinator").lower(),
+        "SPLIT_AT": int(env.get("SPLIT_AT", "1")),
+        "SHARD_A_SERVICE": env.get("SHARD_A_SERVICE", "llm-shard-a"),
+        "SHARD_B_SERVICE": env.get("SHARD_B_SERVICE", "llm-shard-b"),
+        "SHARD_PORT": int(env.get("SHARD_PORT", "5000")),
+        "GP_DTYPE": env.get("GP_DTYPE", "bf16"),
+        "GP_SEED": int(env.get("GP_SEED", "0")),
+        "GP_COORD_MODE": env.get("GP_COORD_MODE", "device"),
+    }
+
+
+def validate_split(dims: W.GPT2Dims, split_at: int):
+    """The reference ships SPLIT_AT=2 on shard A and 1 on shard B (k8s/*-deployment.yaml:22-23),
+    which silently runs block 1 twice; here the split must leave both shards non-empty."""
+    if not 0 < split_at < dims.n_layer:
+        raise ValueError(f"SPLIT_AT={split_at} must satisfy 0 < SPLIT_AT < n_layer={dims.n_layer}")
+
+
+def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokenizer=None, http_post=None):
+    """Build the FastAPI app for one role.  `dims`/`weights`/`tokenizer`/`http_post` are
+    injection points for tests; production use reads everything from the environment."""
+    from fastapi import FastAPI, HTTPException
+
+    cfg = read_env(env)
+    role = cfg["SHARD_ROLE"]
+    dims = dims or W.PRESETS.get(cfg["MODEL_ID"])
+    if dims is None:
+        raise ValueError(f"unknown MODEL_ID {cfg['MODEL_ID']!r}; known: {sorted(W.PRESETS)}")
+    validate_split(dims, cfg["SPLIT_AT"])
+    tokenizer = tokenizer or load_tokenizer(cfg["MODEL_ID"])
+    dtype = GP_BF16 if cfg["GP_DTYPE"] == "bf16" else GP_F32
+    print("Starting server role:", role, "model:", cfg["MODEL_ID"])
+
+    lock = threading.Lock()   # an engine handle is not re-entrant; handlers run on a thread pool
+    state = {"engine": None}
+
+    def engine():
+        if state["engine"] is None:
+            from .engine import StageEngine
+            split = cfg["SPLIT_AT"]
+            if role == "a":
+                rng = (0, split, True, False)
+            elif role == "b":
+                rng = (split, dims.n_layer, False, True)
+            else:
+                rng = (0, dims.n_layer, True, True)
+            eng = StageEngine(dims, rng[0], rng[1], has_embed=rng[2], has_head=rng[3], dtype=dtype, max_batch=1)
+            names = eng.weight_names()
+            w = weights if weights is not None else W.init_weights(dims, cfg["GP_SEED"], "hf", only=names)
+            eng.load_weights(w)
+            state["engine"] = eng
+        return state["engine"]
+
+    app = FastAPI()
+    app.state.cfg = cfg
+
+    def bad(msg):
+        return HTTPException(status_code=400, detail=msg)
+
+    def check_ids(ids):
+        if len(ids) == 0:
+            raise bad("input_ids is empty")
+        if len(ids) > dims.n_positions:
+            raise bad(f"sequence of {len(ids)} tokens exceeds n_positions={dims.n_positions}")
+        if min(ids) < 0 or max(ids) >= dims.vocab_size:
+            raise bad(f"token id outside [0,{dims.vocab_size})")
+
+    @app.post("/forward")
+    def forward_a(req: InputIDs):
+        if role != "a":
+            return {"error": "This instance is not shard A."}
+        check_ids(req.input_ids)
+        with lock:
+            eng = engine()
+            ids = torch.tensor([req.input_ids], dtype=torch.int32, device=eng.device)
+            hidden = eng.prefill(ids, use_cache=False)["hidden"]
+            return {"hidden_states": hidden.cpu().tolist()}
+
+    @app.post("/forward_b")
+    def forward_b(req: HiddenStates):
+        if role != "b":
+            return {"error": "This instance is not shard B."}
+        try:
+            hidden = torch.tensor(req.hidden_states, dtype=torch.float32)
+        except (ValueError, TypeError) as ex:
+            raise bad(f"hidden_states is not a rectangular nested list of numbers: {ex}")
+        if hidden.dim() != 3 or hidden.shape[2] != dims.n_embd or hidden.shape[1] == 0:
+            raise bad(f"hidden_states must be [batch, seq, {dims.n_embd}]")
+        if hidden.shape[1] > dims.n_positions:
+            raise bad(f"sequence of {hidden.shape[1]} tokens exceeds n_positions={dims.n_positions}")
+        with lock:
+            eng = engine()
+            outs = []
+            for b in range(hidden.shape[0]):   # one sequence per call keeps the workspace at T*V
+                x = hidden[b:b + 1].to(eng.device)
+                outs.append(eng.prefill(x, use_cache=False, want_logits="all")["logits"].cpu())
+            return {"logits": torch.cat(outs, 0).tolist()}
+
+    @app.post("/generate")
+    def generate(req: GenerateReq):
+        if role != "coordinator":
+            return {"error": "This instance is not coordinator."}
+        input_ids = tokenizer.encode(req.prompt)
+        n_new = max(0, int(req.max_new_tokens))
+        if n_new == 0:
+            return {"generated": tokenizer.decode(input_ids, skip_special_tokens=True)}
+        check_ids(input_ids)
+        if len(input_ids) + n_new - 1 > dims.n_positions:
+            raise bad(f"prompt of {len(input_ids)} tokens + {n_new} new tokens exceeds "
+                      f"n_positions={dims.n_positions}")
+        if cfg["GP_COORD_MODE"] == "http":
+            # the reference's wire protocol (server.py:169-206), greedy selection
+            import requests
+            post = http_post or requests.post
+            ids = list(input_ids)
+            for _ in range(n_new):
+                url_a = f"http://{cfg['SHARD_A_SERVICE']}:{cfg['SHARD_PORT']}/forward"
+                resp = post(url_a, json={"input_ids": ids}, timeout=30)
+                resp.raise_for_status()
+                hidden = resp.json()["hidden_states"]
+                url_b = f"http://{cfg['SHARD_B_SERVICE']}:{cfg['SHARD_PORT']}/forward_b"
+                resp2 = post(url_b, json={"hidden_states": hidden}, timeout=30)
+                resp2.raise_for_status()
+                last = torch.tensor(resp2.json()["logits"][0][-1], dtype=torch.float32)
+                ids.append(int(torch.argmax(last)))
+            return {"generated": tokenizer.decode(ids, skip_special_tokens=True)}
+        with lock:
+            eng = engine()
+            out = eng.generate(torch.tensor([input_ids], dtype=torch.int32), n_new)
+        return {"generated": tokenizer.decode(out[0].tolist(), skip_special_tokens=True)}
+
+    return app
+
+
+def __getattr__(name):
+    # `uvicorn llm_sharding_demo_b200.server:app` (Dockerfile:19 of the reference uses server:app)
+    if name == "app":
+        return create_app()
+    raise AttributeError(name)

@@ -240,3 +240,17 @@ def test_errors_are_reported_not_faulted(L):
         full.generate(torch.zeros((1, 60), dtype=torch.int32), 10)
     with pytest.raises(L.GPError, match="out of range"):
         full.generate(torch.full((1, 4), dims.vocab_size, dtype=torch.int32), 2)
+
+
+def test_tcgen05_and_simt_engines_agree(L):
+    """bf16 engine with the tcgen05 GEMMs vs the same engine forced onto the SIMT GEMM."""
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 13, "dense")
+    g = torch.Generator().manual_seed(2)
+    prompt = torch.randint(0, dims.vocab_size, (2, 40), generator=g)
+    outs = []
+    for flags in (0, 1):
+        eng = make_stages(L, dims, w, 1, L.GP_BF16, max_batch=2, flags=flags)
+        out, _ = run_prefill(eng, prompt, use_cache=False, want_logits="all")
+        outs.append(out["logits"].cpu())
+    assert float((outs[0] - outs[1]).abs().max()) <= 5e-3

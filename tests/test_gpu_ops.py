@@ -169,3 +169,47 @@ def test_lmhead_argmax_ties_pick_lowest_index(ops):
     gm, bt = torch.zeros(H), torch.ones(H)   # LN output == 1 everywhere
     ids = ops.lmhead_argmax(x.to(DEV), gm.to(DEV), bt.to(DEV), wte.to(DEV))
     assert int(ids[0]) == 7
+
+
+@pytest.mark.parametrize("M,N,K", [(32, 768, 768), (5, 2304, 768), (130, 768, 3072), (33, 1041, 128), (16, 384, 200),
+                                   (128, 128, 64), (300, 3072, 768), (8, 1600, 6400), (257, 50257, 768)])
+@pytest.mark.parametrize("variant", ["plain", "bias_gelu_bf16out", "bias_res"])
+def test_gemm_tcgen05(ops, M, N, K, variant):
+    """tcgen05 + TMA GEMM against the oracle's Conv1D on the same bf16-rounded operands
+    (fp32 accumulation on both sides): 2e-3 abs; bf16 outputs are compared after rounding."""
+    dt = torch.bfloat16
+    A = rnd(M, K, seed=31)
+    W = rnd(K, N, seed=32, scale=0.02)
+    bias, res = rnd(N, seed=33, scale=0.05), rnd(M, N, seed=34)
+    Ad, Wd = A.to(DEV, dt), W.t().contiguous().to(DEV, dt)
+    if variant == "plain":
+        got = ops.gemm(Ad, Wd)
+        ref, tol = q(A, dt) @ q(W, dt), 2e-3
+    elif variant == "bias_gelu_bf16out":
+        got = ops.gemm(Ad, Wd, bias=bias.to(DEV), gelu=True, out_bf16=True).float()
+        ref, tol = O.gelu_new(O.conv1d(q(A, dt), q(W, dt), bias)).bfloat16().float(), 2e-2
+    else:
+        got = ops.gemm(Ad, Wd, bias=bias.to(DEV), residual=res.to(DEV))
+        ref, tol = O.conv1d(q(A, dt), q(W, dt), bias) + res, 2e-3
+    err = (got.cpu() - ref).abs().max()
+    assert err <= tol, float(err)
+    # and it agrees with the SIMT kernel on the same operands
+    simt = ops.gemm(Ad, Wd, simt=True) if variant == "plain" else None
+    if simt is not None:
+        assert (simt.cpu() - got.cpu()).abs().max() <= 2e-3
+
+
+def test_gemm_tcgen05_in_place_residual(ops):
+    M, N, K = 40, 768, 768
+    A, W = rnd(M, K, seed=41), rnd(K, N, seed=42, scale=0.02)
+    h = rnd(M, N, seed=43).to(DEV)
+    ref = q(A, torch.bfloat16) @ q(W, torch.bfloat16) + h.cpu()
+    import ctypes as C
+    from llm_sharding_demo_b200 import load_library
+    lib = load_library()
+    Ad, Wd = A.to(DEV, torch.bfloat16), W.t().contiguous().to(DEV, torch.bfloat16)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    rc = lib.gp_op_gemm(p(Ad), p(Wd), None, p(h), p(h), M, N, K, 0, 1, None)   # out aliases residual
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert (h.cpu() - ref).abs().max() <= 2e-3

@@ -1,0 +1,132 @@
+"""The FastAPI mirror of the reference's API surface (server.py:116-210): CPU tests cover the
+role gates, schemas, defaults, env contract and guards (none of which touch the GPU); GPU tests
+check the routes' numbers against the fixtures captured from the reference's own routes."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+from fastapi.testclient import TestClient
+
+import llm_sharding_demo_b200 as L
+from llm_sharding_demo_b200 import server as S
+
+TINY = L.PRESETS["tiny-gpt2"]
+
+
+def app_for(role, **kw):
+    env = {"SHARD_ROLE": role, "MODEL_ID": "sshleifer/tiny-gpt2", "SPLIT_AT": "1"}
+    env.update(kw.pop("env", {}))
+    return S.create_app(env=env, tokenizer=S.ByteTokenizer(), **kw)
+
+
+def test_env_contract_defaults_match_reference():
+    cfg = S.read_env({})
+    assert cfg["MODEL_ID"] == "sshleifer/tiny-gpt2" and cfg["SHARD_ROLE"] == "coordinator"   # server.py:20-21
+    assert cfg["SPLIT_AT"] == 1 and cfg["SHARD_PORT"] == 5000                               # :22,25
+    assert cfg["SHARD_A_SERVICE"] == "llm-shard-a" and cfg["SHARD_B_SERVICE"] == "llm-shard-b"  # :23-24
+    assert S.read_env({"SHARD_ROLE": "A"})["SHARD_ROLE"] == "a"                              # lower-cased :21
+
+
+def test_role_gates_return_200_and_reference_strings(golden_dir):
+    extra = json.loads(str(np.load(os.path.join(golden_dir, "tiny_gpt2.npz"))["extra"]))
+    a, b, c = (TestClient(app_for(r)) for r in ("a", "b", "coordinator"))
+    r = b.post("/forward", json={"input_ids": [1]})
+    assert r.status_code == 200 and r.json() == extra["gate_a"]
+    r = a.post("/forward_b", json={"hidden_states": [[[0.0, 0.0]]]})
+    assert r.status_code == 200 and r.json() == extra["gate_b"]
+    r = a.post("/generate", json={"prompt": "x"})
+    assert r.status_code == 200 and r.json() == extra["gate_c"]
+    r = c.post("/forward", json={"input_ids": [1]})
+    assert r.json() == extra["gate_a"]
+
+
+def test_schema_violations_are_422_and_guards_are_400():
+    a, b, c = (TestClient(app_for(r)) for r in ("a", "b", "coordinator"))
+    assert a.post("/forward", json={"input_ids": "no"}).status_code == 422
+    assert a.post("/forward", json={}).status_code == 422
+    assert c.post("/generate", json={"max_new_tokens": 3}).status_code == 422
+    assert a.post("/forward", json={"input_ids": []}).status_code == 400
+    assert a.post("/forward", json={"input_ids": [50257]}).status_code == 400
+    assert a.post("/forward", json={"input_ids": [1] * 1025}).status_code == 400          # would index past wpe
+    assert b.post("/forward_b", json={"hidden_states": [[[0.0] * 3]]}).status_code == 400  # wrong H
+    assert b.post("/forward_b", json={"hidden_states": [[1.0], [[2.0]]]}).status_code == 400
+    r = c.post("/generate", json={"prompt": "x" * 1020, "max_new_tokens": 20})
+    assert r.status_code == 400 and "n_positions" in r.json()["detail"]
+
+
+def test_generate_zero_tokens_returns_prompt_without_gpu(golden_dir):
+    extra = json.loads(str(np.load(os.path.join(golden_dir, "tiny_gpt2.npz"))["extra"]))
+    c = TestClient(app_for("coordinator"))
+    r = c.post("/generate", json={"prompt": "Hi, ", "max_new_tokens": 0})
+    assert r.status_code == 200 and r.json() == {"generated": extra["generate0"]}
+
+
+def test_split_validation_rejects_the_shipped_k8s_mismatch():
+    S.validate_split(L.PRESETS["gpt2"], 6)
+    with pytest.raises(ValueError):
+        S.create_app(env={"SHARD_ROLE": "a", "SPLIT_AT": "2", "MODEL_ID": "sshleifer/tiny-gpt2"})  # 2 of 2 layers
+    with pytest.raises(ValueError):
+        S.create_app(env={"MODEL_ID": "nope"})
+
+
+# ------------------------------------------------------------------------------------ GPU
+def _golden(golden_dir, name):
+    from oracle import gpt2_oracle as O
+    z = np.load(os.path.join(golden_dir, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    dims = O.GPT2Dims(**meta["dims"])
+    return z, meta, L.GPT2Dims(**meta["dims"]), O.init_weights(dims, meta["seed"], meta["recipe"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["tiny_gpt2_dense", "mini"])
+def test_routes_match_reference_routes(golden_dir, name):
+    z, meta, dims, w = _golden(golden_dir, name)
+    env = {"SPLIT_AT": str(meta["split_at"]), "GP_DTYPE": "f32", "MODEL_ID": "x"}
+    mk = lambda role, **kw: TestClient(S.create_app(env=dict(env, SHARD_ROLE=role), dims=dims, weights=w,
+                                                    tokenizer=S.ByteTokenizer(), **kw))
+    a, b = mk("a"), mk("b")
+    prompt = z["prompt_ids"].tolist()
+    r = a.post("/forward", json={"input_ids": prompt})
+    assert r.status_code == 200
+    hidden = r.json()["hidden_states"]
+    np.testing.assert_allclose(np.asarray(hidden, np.float32), z["hidden_step0"], rtol=0, atol=3e-4)
+    r = b.post("/forward_b", json={"hidden_states": hidden})
+    logits = np.asarray(r.json()["logits"], np.float32)
+    assert logits.shape == (1, len(prompt), dims.vocab_size)
+    ref = z["logits_step0"]
+    np.testing.assert_allclose(logits[0] if ref.shape[0] == len(prompt) else logits[0, -1:], ref, rtol=0, atol=3e-4)
+    # B > 1 is accepted by /forward_b (server.py:120 is untyped) and rows stay independent
+    r2 = b.post("/forward_b", json={"hidden_states": hidden + hidden})
+    l2 = np.asarray(r2.json()["logits"], np.float32)
+    assert l2.shape[0] == 2 and np.array_equal(l2[0], l2[1]) and np.array_equal(l2[0], logits[0])
+
+    # coordinator: device loop and the reference's HTTP protocol give the same greedy text
+    class Resp:
+        def __init__(self, r):
+            self.r = r
+
+        def raise_for_status(self):
+            self.r.raise_for_status()
+
+        def json(self):
+            return self.r.json()
+
+    def post(url, json=None, timeout=None):
+        return Resp((a if url.endswith("/forward") else b).post("/" + url.rsplit("/", 1)[1], json=json))
+
+    n_new = 5
+    text_prompt = bytes(prompt).decode("latin-1") if max(prompt) < 128 else None
+    if text_prompt is not None:
+        c_dev = mk("coordinator")
+        c_http = TestClient(S.create_app(env=dict(env, SHARD_ROLE="coordinator", GP_COORD_MODE="http"), dims=dims,
+                                         weights=w, tokenizer=S.ByteTokenizer(), http_post=post))
+        g1 = c_dev.post("/generate", json={"prompt": text_prompt, "max_new_tokens": n_new}).json()["generated"]
+        g2 = c_http.post("/generate", json={"prompt": text_prompt, "max_new_tokens": n_new}).json()["generated"]
+        ref_ids = z["greedy_ids"][:len(prompt) + n_new].tolist()
+        assert g1 == g2 == S.ByteTokenizer().decode(ref_ids)
+        # default max_new_tokens is 20 (server.py:124)
+        g3 = c_dev.post("/generate", json={"prompt": text_prompt}).json()["generated"]
+        assert len(S.ByteTokenizer().encode(g3)) >= len(prompt)
