@@ -40,6 +40,7 @@ extern "C" {
 /* gp_config.flags */
 #define GP_FLAG_NO_TCGEN05 1u /* route every GEMM through the SIMT tile kernel      */
 #define GP_FLAG_NO_GRAPH 2u   /* gp_generate launches kernels directly (no CUDA graph) */
+#define GP_FLAG_NO_MEGA 4u    /* decode with one kernel per op instead of the persistent kernel */
 
 /* epilogue / behaviour bits of the op-level entry points */
 #define GP_EPI_GELU 1u   /* gelu_new (tanh form) after bias, before the residual add */

@@ -57,6 +57,14 @@ struct gp_engine {
   std::map<int, cudaGraphExec_t> decode_graphs;  // keyed by batch
   std::map<int, int64_t> decode_graph_launches;
   std::vector<cudaEvent_t> events;
+  // persistent decode kernel
+  MegaLayer* mega_layers = nullptr;
+  float *qkv_f = nullptr, *h2_f = nullptr, *part_v = nullptr;
+  int* part_i = nullptr;
+  unsigned* mega_bar = nullptr;
+  unsigned long long* step_clock = nullptr;
+  bool mega_uploaded = false;
+  int num_sms = 0;
   std::string err;
   int64_t launches = 0;
 };
@@ -142,6 +150,42 @@ int check_ready(gp_engine* e) {
   return GP_OK;
 }
 
+bool use_mega(const gp_engine* e, int B) {
+  return !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->cfg.max_ctx, e->cfg.dtype);
+}
+
+int upload_mega_layers(gp_engine* e) {
+  if (e->mega_uploaded) return GP_OK;
+  std::vector<MegaLayer> h(e->L);
+  for (int i = 0; i < e->L; ++i) {
+    const LayerW& w = e->layers[i];
+    h[i] = MegaLayer{w.attn_w, w.proj_w, w.fc_w, w.mproj_w, w.attn_b, w.proj_b, w.fc_b, w.mproj_b,
+                     w.ln1_g,  w.ln1_b,  w.ln2_g, w.ln2_b,  w.kc,     w.vc};
+  }
+  CK(e, cudaMemcpyAsync(e->mega_layers, h.data(), sizeof(MegaLayer) * e->L, cudaMemcpyHostToDevice, e->stream));
+  CK(e, cudaStreamSynchronize(e->stream));
+  e->mega_uploaded = true;
+  return GP_OK;
+}
+
+// one launch = n_steps cached decode steps of this stage (n_steps > 1 only for single-stage engines)
+int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B, int slot0, float* hidden_out,
+                float* logits, int32_t* next_ids, int32_t* seq, int n_steps, bool clock, cudaStream_t s) {
+  int r = upload_mega_layers(e);
+  if (r != GP_OK) return r;
+  const gp_config& c = e->cfg;
+  MegaParams p;
+  p.layers = e->mega_layers; p.L = e->L; p.H = e->H; p.nh = e->nh; p.V = e->V; p.n_pos = c.n_positions;
+  p.max_ctx = c.max_ctx; p.eps = c.ln_eps; p.B = B; p.slot0 = slot0; p.has_embed = c.has_embed; p.has_head = c.has_head;
+  p.wte = e->wte; p.wpe = e->wpe; p.lnf_g = e->lnf_g; p.lnf_b = e->lnf_b; p.ids = ids; p.hidden_in = hidden_in;
+  p.hidden_out = hidden_out; p.lens = e->lens; p.hbuf = e->h; p.qkv = e->qkv_f; p.attn = e->attn_f; p.h2 = e->h2_f;
+  p.act = e->act_f; p.part_v = e->part_v; p.part_i = e->part_i; p.ids_out = next_ids ? next_ids : e->mailbox;
+  p.seq = seq; p.seq_stride = e->seq_stride; p.logits_out = logits; p.bar = e->mega_bar; p.n_steps = n_steps;
+  p.step_clock = clock ? e->step_clock : nullptr;
+  LAUNCH(e, launch_decode_mega(p, c.dtype, e->num_sms, s));
+  return GP_OK;
+}
+
 // ------------------------------------------------------------------------------- prefill
 int prefill_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B, int T, int slot0, int use_cache,
                  float* hidden_out, float* logits, int logits_all, int32_t* next_ids, int32_t* seq_for_generate,
@@ -214,6 +258,8 @@ int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   if (!c.has_head && hidden_out == nullptr) { set_err(e, "decode: hidden_out is NULL"); return GP_EINVAL; }
   int r = check_ready(e);
   if (r != GP_OK) return r;
+
+  if (use_mega(e, B)) return decode_mega(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, seq, 1, false, s);
 
   const bool use_gemv = gemv_supported(B, F);
   const bool obf = bf(e);
@@ -386,6 +432,16 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRY(alloc((void**)&e->seq, MB * (size_t)e->seq_stride * sizeof(int32_t)));
   TRY(alloc((void**)&e->prompt, MB * (size_t)cfg->n_positions * sizeof(int32_t)));
   TRY(alloc((void**)&e->mailbox, MB * sizeof(int32_t)));
+  TRY(alloc((void**)&e->mega_layers, sizeof(MegaLayer) * e->L));
+  TRY(alloc((void**)&e->qkv_f, MB * 3 * H * 4));
+  TRY(alloc((void**)&e->h2_f, MB * H * 4));
+  TRY(alloc((void**)&e->part_v, 1024 * kGemvMaxBatch * sizeof(float)));
+  TRY(alloc((void**)&e->part_i, 1024 * kGemvMaxBatch * sizeof(int)));
+  TRY(alloc((void**)&e->mega_bar, 256));
+  TRY(alloc((void**)&e->step_clock, (size_t)(cfg->n_positions + 2) * sizeof(unsigned long long)));
+  TRYCK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
+  if (e->num_sms > 1024) e->num_sms = 1024;
+  TRYCK(init_mega_attrs());
   TRYCK(cudaStreamSynchronize(e->stream));
 #undef TRY
 #undef TRYCK
@@ -543,7 +599,13 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
   }
   CK(e, cudaEventRecord(e->events[1], s));
   const int steps = n_new > 1 ? n_new - 1 : 0;
-  if (steps > 0) {
+  const bool mega = steps > 0 && use_mega(e, B);
+  if (mega) {
+    // the whole greedy loop is ONE persistent launch; per-step times come from %globaltimer
+    int r = decode_mega(e, e->mailbox, nullptr, B, 0, nullptr, nullptr, e->mailbox, e->seq, steps,
+                        timings_ms_host != nullptr, s);
+    if (r != GP_OK) return r;
+  } else if (steps > 0) {
     const bool use_graph = !(c.flags & GP_FLAG_NO_GRAPH);
     cudaGraphExec_t exec = nullptr;
     int64_t per_step = 0;
@@ -590,9 +652,16 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
     CK(e, cudaEventElapsedTime(&ms, e->events[1], e->events[2]));
     timings_ms_host[1] = ms;
     for (int i = 0; i < n_new; ++i) timings_ms_host[2 + i] = 0.f;
-    for (int i = 0; i < steps; ++i) {
-      CK(e, cudaEventElapsedTime(&ms, i == 0 ? e->events[1] : e->events[3 + i - 1], e->events[3 + i]));
-      timings_ms_host[2 + i] = ms;
+    if (mega) {
+      std::vector<unsigned long long> clk(steps + 1);
+      CK(e, cudaMemcpy(clk.data(), e->step_clock, sizeof(unsigned long long) * (steps + 1), cudaMemcpyDeviceToHost));
+      for (int i = 0; i < steps; ++i)
+        timings_ms_host[2 + i] = (float)((double)(clk[i] - (i == 0 ? clk[steps] : clk[i - 1])) * 1e-6);
+    } else {
+      for (int i = 0; i < steps; ++i) {
+        CK(e, cudaEventElapsedTime(&ms, i == 0 ? e->events[1] : e->events[3 + i - 1], e->events[3 + i]));
+        timings_ms_host[2 + i] = ms;
+      }
     }
   }
   return GP_OK;

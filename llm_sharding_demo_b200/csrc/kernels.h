@@ -76,6 +76,32 @@ cudaError_t launch_convert(const float* src, void* dst, int R, int C, bool trans
 // gather rows: dst[b,:] = src[(b*T + T-1),:]  (last position of each sequence)
 cudaError_t launch_gather_last(const float* src, float* dst, int B, int T, int H, cudaStream_t s);
 
+// ---- persistent decode kernel (k_mega.cu)
+struct MegaLayer {
+  const void *attn_w, *proj_w, *fc_w, *mproj_w;              // [N,K] storage dtype
+  const float *attn_b, *proj_b, *fc_b, *mproj_b, *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+  void *kc, *vc;                                             // [slots, nh, max_ctx, 64]
+};
+struct MegaParams {
+  const MegaLayer* layers = nullptr; int L = 0;              // device array of this stage's layers
+  int H = 0, nh = 0, V = 0, n_pos = 0, max_ctx = 0; float eps = 1e-5f;
+  int B = 0, slot0 = 0, has_embed = 0, has_head = 0;
+  const void *wte = nullptr, *wpe = nullptr; const float *lnf_g = nullptr, *lnf_b = nullptr;
+  const int32_t* ids = nullptr;                              // [B] token to process (has_embed)
+  const float* hidden_in = nullptr; float* hidden_out = nullptr;
+  int32_t* lens = nullptr;
+  float *hbuf = nullptr, *qkv = nullptr, *attn = nullptr, *h2 = nullptr, *act = nullptr;  // fp32 exchange buffers
+  float* part_v = nullptr; int* part_i = nullptr;            // [grid][8] argmax partials
+  int32_t* ids_out = nullptr; int32_t* seq = nullptr; int seq_stride = 0; float* logits_out = nullptr;
+  unsigned* bar = nullptr;                                   // grid barrier counter
+  int n_steps = 1;
+  unsigned long long* step_clock = nullptr;                  // [n_steps+1] globaltimer ns: end of each step, then start
+  int n_slots = 0;                                           // filled by the launcher
+};
+bool mega_supported(int B, int H, int nh, int max_ctx, int dtype);
+cudaError_t init_mega_attrs();
+cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_t s);
+
 // stores `msg` as this thread's last error (what gp_last_error(NULL) returns); engine.cu
 void record_error(const char* msg);
 

@@ -254,3 +254,42 @@ def test_tcgen05_and_simt_engines_agree(L):
         out, _ = run_prefill(eng, prompt, use_cache=False, want_logits="all")
         outs.append(out["logits"].cpu())
     assert float((outs[0] - outs[1]).abs().max()) <= 5e-3
+
+
+@pytest.mark.parametrize("dtype_name", ["f32", "bf16"])
+@pytest.mark.parametrize("B", [1, 3])
+def test_persistent_decode_kernel_matches_per_op_kernels(L, dtype_name, B):
+    """The persistent decode kernel (one cooperative launch per step / per whole loop) against
+    the one-kernel-per-op path (GP_FLAG_NO_MEGA) on the same engine configuration: same
+    arithmetic per element, different summation order -> logits within 1e-4 (fp32 storage) /
+    2e-3 (bf16 storage: K/V rounding points can flip by one ulp), same greedy ids wherever the
+    margin allows."""
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 21, "dense")
+    dtype = L.GP_F32 if dtype_name == "f32" else L.GP_BF16
+    tol = 1e-4 if dtype_name == "f32" else 2e-3
+    g = torch.Generator().manual_seed(3)
+    prompt = torch.randint(0, dims.vocab_size, (B, 7), generator=g)
+    n_new = 12
+    ref_ids, ref_logits = O.generate_cached(w, dims, prompt, n_new, return_logits=True)
+    res = {}
+    for name, flags in (("mega", 0), ("ops", 4)):
+        (eng,) = make_stages(L, dims, w, 1, dtype, max_batch=B, flags=flags)
+        out, _ = run_prefill([eng], prompt)
+        logs = [out["logits"].cpu()]
+        for t in range(1, n_new):
+            out = run_decode([eng], ref_ids[:, 7 + t - 1])
+            logs.append(out["logits"].cpu())
+        res[name] = (torch.stack(logs, 1), eng.generate(prompt.to(torch.int32), n_new, timings=True))
+        assert eng.kv_lengths() == [7 + n_new - 1] * B
+    assert float((res["mega"][0] - res["ops"][0]).abs().max()) <= tol
+    margins = O.top2_margin(ref_logits)
+    ids_m, tm_m = res["mega"][1]
+    ids_o, _ = res["ops"][1]
+    for b in range(B):
+        for t in range(n_new):
+            if float(margins[b, t]) <= 2 * (3e-4 if dtype_name == "f32" else 0.06):
+                break
+            assert int(ids_m[b, 7 + t]) == int(ids_o[b, 7 + t]) == int(ref_ids[b, 7 + t]), (b, t)
+    assert len(tm_m["step_ms"]) == n_new - 1 and all(x > 0 for x in tm_m["step_ms"])
+    assert abs(sum(tm_m["step_ms"]) - tm_m["decode_ms"]) < 0.5 * tm_m["decode_ms"] + 0.05
