@@ -3,6 +3,7 @@
 // device-resident greedy loop.  Host-side C++ only; every kernel lives in k_*.cu / gemm_*.cu.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <set>
@@ -64,6 +65,7 @@ struct gp_engine {
   unsigned* mega_bar = nullptr;
   unsigned long long* step_clock = nullptr;
   bool mega_uploaded = false;
+  long long* trace = nullptr;
   int num_sms = 0;
   std::string err;
   int64_t launches = 0;
@@ -151,7 +153,7 @@ int check_ready(gp_engine* e) {
 }
 
 bool use_mega(const gp_engine* e, int B) {
-  return !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->cfg.max_ctx, e->cfg.dtype);
+  return !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype);
 }
 
 int upload_mega_layers(gp_engine* e) {
@@ -182,7 +184,21 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   p.act = e->act_f; p.part_v = e->part_v; p.part_i = e->part_i; p.ids_out = next_ids ? next_ids : e->mailbox;
   p.seq = seq; p.seq_stride = e->seq_stride; p.logits_out = logits; p.bar = e->mega_bar; p.n_steps = n_steps;
   p.step_clock = clock ? e->step_clock : nullptr;
+  const bool trace = getenv("GP_MEGA_TRACE") != nullptr && n_steps > 1;
+  if (trace) {  // debug aid: phase-boundary clocks of the last step, printed to stderr
+    if (!e->trace) CK(e, cudaMalloc((void**)&e->trace, 2048 * sizeof(long long)));
+    CK(e, cudaMemsetAsync(e->trace, 0, 2048 * sizeof(long long), s));
+    p.trace = e->trace; p.trace_cap = 2048;
+  }
   LAUNCH(e, launch_decode_mega(p, c.dtype, e->num_sms, s));
+  if (trace) {
+    std::vector<long long> t(2048);
+    CK(e, cudaStreamSynchronize(s));
+    CK(e, cudaMemcpy(t.data(), e->trace, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "GP_MEGA_TRACE cycles between phase boundaries of the last step:");
+    for (size_t i = 1; i < t.size() && t[i] != 0; ++i) fprintf(stderr, "%s%lld", (i % 12 == 1) ? "\n  " : " ", t[i] - t[i - 1]);
+    fprintf(stderr, "\n");
+  }
   return GP_OK;
 }
 
@@ -457,6 +473,7 @@ int gp_engine_destroy(gp_engine* e) {
   for (auto ev : e->events) cudaEventDestroy(ev);
   for (void* p : e->allocs) cudaFree(p);
   if (e->stage) cudaFree(e->stage);
+  if (e->trace) cudaFree(e->trace);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return GP_OK;

@@ -97,8 +97,9 @@ struct MegaParams {
   int n_steps = 1;
   unsigned long long* step_clock = nullptr;                  // [n_steps+1] globaltimer ns: end of each step, then start
   int n_slots = 0;                                           // filled by the launcher
+  long long* trace = nullptr; int trace_cap = 0;             // debug: clock64 of CTA 0 per phase boundary
 };
-bool mega_supported(int B, int H, int nh, int max_ctx, int dtype);
+bool mega_supported(int B, int H, int nh, int L, int dtype);
 cudaError_t init_mega_attrs();
 cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_t s);
 
