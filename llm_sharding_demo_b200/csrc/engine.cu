@@ -60,9 +60,11 @@ struct gp_engine {
   std::vector<cudaEvent_t> events;
   // persistent decode kernel
   MegaLayer* mega_layers = nullptr;
-  float *qkv_f = nullptr, *h2_f = nullptr, *part_v = nullptr;
-  int* part_i = nullptr;
-  unsigned* mega_bar = nullptr;
+  unsigned long long *qkv_ll = nullptr, *attn_ll = nullptr, *h2_ll = nullptr, *act_ll = nullptr, *h_ll = nullptr;
+  unsigned long long* part_ll = nullptr;
+  uint32_t* mega_flags = nullptr;
+  uint32_t mega_ctr[64] = {0};   // host mirror of the device "published" counters
+  uint32_t mega_epoch = 8;
   unsigned long long* step_clock = nullptr;
   bool mega_uploaded = false;
   long long* trace = nullptr;
@@ -153,7 +155,7 @@ int check_ready(gp_engine* e) {
 }
 
 bool use_mega(const gp_engine* e, int B) {
-  return !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype);
+  return !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms);
 }
 
 int upload_mega_layers(gp_engine* e) {
@@ -180,24 +182,40 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   p.layers = e->mega_layers; p.L = e->L; p.H = e->H; p.nh = e->nh; p.V = e->V; p.n_pos = c.n_positions;
   p.max_ctx = c.max_ctx; p.eps = c.ln_eps; p.B = B; p.slot0 = slot0; p.has_embed = c.has_embed; p.has_head = c.has_head;
   p.wte = e->wte; p.wpe = e->wpe; p.lnf_g = e->lnf_g; p.lnf_b = e->lnf_b; p.ids = ids; p.hidden_in = hidden_in;
-  p.hidden_out = hidden_out; p.lens = e->lens; p.hbuf = e->h; p.qkv = e->qkv_f; p.attn = e->attn_f; p.h2 = e->h2_f;
-  p.act = e->act_f; p.part_v = e->part_v; p.part_i = e->part_i; p.ids_out = next_ids ? next_ids : e->mailbox;
-  p.seq = seq; p.seq_stride = e->seq_stride; p.logits_out = logits; p.bar = e->mega_bar; p.n_steps = n_steps;
+  p.hidden_out = hidden_out; p.lens = e->lens; p.qkv_ll = e->qkv_ll; p.attn_ll = e->attn_ll; p.h2_ll = e->h2_ll;
+  p.act_ll = e->act_ll; p.h_ll = e->h_ll; p.part_ll = e->part_ll; p.flags = e->mega_flags; p.ids_out = next_ids ? next_ids : e->mailbox;
+  p.seq = seq; p.seq_stride = e->seq_stride; p.logits_out = logits; p.n_steps = n_steps;
+  const uint32_t span = mega_epochs_per_launch(e->L, n_steps);
+  if (e->mega_epoch > 0xFFFFFFFFu - span - 8u) {
+    // epoch counter about to wrap: start over on zeroed exchange buffers
+    const size_t MBx = c.max_batch;
+    CK(e, cudaMemsetAsync(e->qkv_ll, 0, MBx * 3 * e->H * 8, s)); CK(e, cudaMemsetAsync(e->attn_ll, 0, MBx * e->H * 8, s));
+    CK(e, cudaMemsetAsync(e->h2_ll, 0, MBx * e->H * 8, s)); CK(e, cudaMemsetAsync(e->act_ll, 0, MBx * e->F * 8, s));
+    CK(e, cudaMemsetAsync(e->h_ll, 0, MBx * e->H * 8, s)); CK(e, cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, s));
+    CK(e, cudaMemsetAsync(e->mega_flags, 0, mega_flag_words() * 4, s));
+    memset(e->mega_ctr, 0, sizeof(e->mega_ctr));
+    e->mega_epoch = 8;
+  }
+  p.epoch0 = e->mega_epoch;
+  e->mega_epoch += span;
+  memcpy(p.ctr_base, e->mega_ctr, sizeof(p.ctr_base));
+  mega_advance_counters(e->mega_ctr, e->L, n_steps, B, e->nh, e->num_sms, c.has_head);
   p.step_clock = clock ? e->step_clock : nullptr;
-  const bool trace = getenv("GP_MEGA_TRACE") != nullptr && n_steps > 1;
-  if (trace) {  // debug aid: phase-boundary clocks of the last step, printed to stderr
-    if (!e->trace) CK(e, cudaMalloc((void**)&e->trace, 2048 * sizeof(long long)));
-    CK(e, cudaMemsetAsync(e->trace, 0, 2048 * sizeof(long long), s));
-    p.trace = e->trace; p.trace_cap = 2048;
+  const char* trace_path = getenv("GP_MEGA_TRACE");
+  const bool trace = trace_path != nullptr && n_steps > 1;
+  const int kTraceCap = 256;
+  if (trace) {  // debug aid: per-CTA %globaltimer at every phase boundary of the last step -> raw int64 file
+    if (!e->trace) CK(e, cudaMalloc((void**)&e->trace, (size_t)e->num_sms * kTraceCap * sizeof(long long)));
+    CK(e, cudaMemsetAsync(e->trace, 0, (size_t)e->num_sms * kTraceCap * sizeof(long long), s));
+    p.trace = e->trace; p.trace_cap = kTraceCap;
   }
   LAUNCH(e, launch_decode_mega(p, c.dtype, e->num_sms, s));
   if (trace) {
-    std::vector<long long> t(2048);
+    std::vector<long long> t((size_t)e->num_sms * kTraceCap);
     CK(e, cudaStreamSynchronize(s));
     CK(e, cudaMemcpy(t.data(), e->trace, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
-    fprintf(stderr, "GP_MEGA_TRACE cycles between phase boundaries of the last step:");
-    for (size_t i = 1; i < t.size() && t[i] != 0; ++i) fprintf(stderr, "%s%lld", (i % 12 == 1) ? "\n  " : " ", t[i] - t[i - 1]);
-    fprintf(stderr, "\n");
+    FILE* f = fopen(trace_path, "wb");
+    if (f) { fwrite(t.data(), sizeof(long long), t.size(), f); fclose(f); }
   }
   return GP_OK;
 }
@@ -449,11 +467,13 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRY(alloc((void**)&e->prompt, MB * (size_t)cfg->n_positions * sizeof(int32_t)));
   TRY(alloc((void**)&e->mailbox, MB * sizeof(int32_t)));
   TRY(alloc((void**)&e->mega_layers, sizeof(MegaLayer) * e->L));
-  TRY(alloc((void**)&e->qkv_f, MB * 3 * H * 4));
-  TRY(alloc((void**)&e->h2_f, MB * H * 4));
-  TRY(alloc((void**)&e->part_v, 1024 * kGemvMaxBatch * sizeof(float)));
-  TRY(alloc((void**)&e->part_i, 1024 * kGemvMaxBatch * sizeof(int)));
-  TRY(alloc((void**)&e->mega_bar, 256));
+  TRY(alloc((void**)&e->qkv_ll, MB * 3 * H * 8)); TRYCK(cudaMemsetAsync(e->qkv_ll, 0, MB * 3 * H * 8, e->stream));
+  TRY(alloc((void**)&e->attn_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->attn_ll, 0, MB * H * 8, e->stream));
+  TRY(alloc((void**)&e->h2_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->h2_ll, 0, MB * H * 8, e->stream));
+  TRY(alloc((void**)&e->act_ll, MB * F * 8)); TRYCK(cudaMemsetAsync(e->act_ll, 0, MB * F * 8, e->stream));
+  TRY(alloc((void**)&e->h_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->h_ll, 0, MB * H * 8, e->stream));
+  TRY(alloc((void**)&e->part_ll, mega_part_words() * 8)); TRYCK(cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, e->stream));
+  TRY(alloc((void**)&e->mega_flags, mega_flag_words() * 4)); TRYCK(cudaMemsetAsync(e->mega_flags, 0, mega_flag_words() * 4, e->stream));
   TRY(alloc((void**)&e->step_clock, (size_t)(cfg->n_positions + 2) * sizeof(unsigned long long)));
   TRYCK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
   if (e->num_sms > 1024) e->num_sms = 1024;

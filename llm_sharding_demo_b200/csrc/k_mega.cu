@@ -1,34 +1,51 @@
 // Persistent decode kernel for the bandwidth-bound regime (a few sequences per step): ONE
 // cooperative launch runs every phase of every layer of a cached decode step - and, for a
-// single-stage engine, every step of the greedy loop - so no launch gaps remain and the weight
-// stream never stops at a phase boundary.
+// single-stage engine, every step of the greedy loop.  At batch 1 a GPT-2 124M step is ~60
+// dependent phases of a few hundred KB each, so the cost is latency, not bandwidth; the design
+// removes every latency that is not a data dependency:
 //
-//   * one CTA per SM; warp 16 is the PRODUCER: a single thread walks the (static) sequence of
+//   * one CTA per SM; warp 15 is the PRODUCER: a single thread walks the (static) sequence of
 //     weight row-chunks this CTA will need and streams them HBM -> shared memory with
-//     cp.async.bulk (TMA bulk copy, mbarrier complete_tx) into a ring of 24 KB slots.  Weights
-//     do not depend on activations, so the producer runs ahead across phases, layers and steps
-//     up to the ring depth (~190 KB per SM in flight).
-//   * warps 0..15 are CONSUMERS: per phase they stage the activation vector(s) from the L2-
-//     resident exchange buffer into shared memory (LayerNorm fused), then each warp takes one
-//     weight row of the current slot, dots it with 128-bit shared-memory loads, reduces with
-//     shuffles and applies the epilogue (bias / gelu_new / residual / argmax candidate).
-//   * phases exchange activations through small fp32 buffers in global memory (L2) and a
-//     monotonic grid barrier (release add + acquire poll); 5 barriers per layer.
-//   * decode attention is a phase of the same kernel: CTA (b, head) appends the new K/V row to
-//     the cache and attends over it.
-// Arithmetic per element is the same as the stand-alone GEMV / attention kernels (fp32
-// accumulation of storage-rounded weights), restating [hf] modeling_gpt2.py:262-309.
+//     cp.async.bulk (TMA bulk copy, mbarrier complete_tx) into a ring of 24 KB slots, the
+//     matching bias slice riding in the same transaction.  Weights do not depend on activations,
+//     so the producer runs ahead across phases, layers and steps (~190 KB per SM in flight).
+//   * warps 0..14 are CONSUMERS: per phase they collect the activation vector into shared memory
+//     (LayerNorm fused, row held in registers), then each warp dots one weight row of the current
+//     slot (128-bit shared loads, shuffle reduction) and applies the epilogue.
+//   * phases exchange activations through "flag-in-data" buffers in L2: every fp32 value travels
+//     in one 64-bit word together with the epoch of the phase that produced it, so a reader can
+//     verify each element by itself - no grid barrier and no memory fence anywhere.  To keep the
+//     polling traffic off L2, each CTA also publishes one flag word per phase; one warp watches
+//     the (coalesced) flag array while the others sleep at the CTA barrier.  Reuse of a buffer
+//     one layer later is ordered by the data dependencies themselves.
+//   * the residual stream slice a CTA owns stays in its shared memory across phases and layers;
+//     decode attention is a phase of the same kernel: CTA (b, head) prefetches the cached K/V rows
+//     while it waits for q, appends the new row and runs an online softmax per 8-lane group.
+// Arithmetic per element is that of the stand-alone GEMV / attention kernels (fp32 accumulation
+// of storage-rounded weights), restating [hf] modeling_gpt2.py:262-309.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
 namespace gp {
 namespace {
 
-constexpr int kNW = 16;                    // consumer warps
-constexpr int kConsumers = kNW * 32;       // 512
+typedef unsigned long long u64;
+
+constexpr int kNW = 15;                    // consumer warps (+1 producer warp = 512 threads, 128 registers each)
+constexpr int kConsumers = kNW * 32;       // 480
 constexpr int kMegaThreads = kConsumers + 32;
-constexpr int kSlotBytes = 24 * 1024;
-constexpr int kMaxSlots = 8;
+constexpr int kGroups = kNW * 4;           // 8-lane groups of the attention phase
+constexpr int kSlotData = 32 * 1024;       // weight rows of one chunk
+constexpr int kMaxRows = 24;               // rows per chunk (a warp may own two)
+constexpr int kSlotBias = 128;             // fp32 bias window of the chunk (<= 24 rows + alignment slack)
+constexpr int kSlotBytes = kSlotData + kSlotBias;
+constexpr int kMaxSlots = 6;
+constexpr int kOwnMax = 16;                // residual rows one CTA owns (ceil(H/G)+1 <= 16)
+constexpr int kLnPer = 4;                  // LayerNorm elements per thread: H <= 4 * 480
+constexpr int kCopyPer = 16;               // plain staging elements per thread: K <= 16 * 480
+constexpr int kFlagStride = 256;           // flag words per exchange buffer (>= CTAs, >= B*nh)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -60,42 +77,61 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
                : "memory");
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
-__device__ __forceinline__ unsigned ld_acquire(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long globaltimer() {
-  unsigned long long t;
+__device__ __forceinline__ u64 globaltimer() {
+  u64 t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
 
-// sum over the 512 consumer threads; `red` = kNW floats of shared memory
-__device__ __forceinline__ float consumer_sum(float v, float* red) {
-  v = warp_sum(v);
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  consumer_sync();
-  if (l == 0) red[w] = v;
-  consumer_sync();
-  float t = 0.f;
-#pragma unroll
-  for (int i = 0; i < kNW; ++i) t += red[i];
-  return t;
+// ---- flag-in-data exchange: {epoch:32 | fp32 bits:32} in one naturally aligned 64-bit word.
+// A 64-bit access is single-copy atomic, so a reader that sees the epoch also sees the value.
+__device__ __forceinline__ void ll_store(u64* p, float v, uint32_t epoch) {
+  const u64 w = ((u64)epoch << 32) | (u64)__float_as_uint(v);
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
 }
-__device__ __forceinline__ float consumer_max(float v, float* red) {
-  v = warp_max(v);
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  consumer_sync();
-  if (l == 0) red[w] = v;
-  consumer_sync();
-  float t = red[0];
-#pragma unroll
-  for (int i = 1; i < kNW; ++i) t = fmaxf(t, red[i]);
-  return t;
+__device__ __forceinline__ void ll_store_int(u64* p, int v, uint32_t epoch) {
+  const u64 w = ((u64)epoch << 32) | (u64)(uint32_t)v;
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ u64 ll_load(const u64* p) {
+  u64 w;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+  return w;
+}
+__device__ __forceinline__ uint32_t ll_wait_bits(const u64* p, uint32_t epoch) {
+  u64 w = ll_load(p);
+  while ((uint32_t)(w >> 32) != epoch) w = ll_load(p);
+  return (uint32_t)w;
+}
+__device__ __forceinline__ void flag_store(uint32_t* p, uint32_t epoch) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(epoch) : "memory");
+}
+__device__ __forceinline__ uint32_t flag_load(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// "Published" counters: every exchange buffer has kSub monotonic counters, each on its own 128-byte
+// line; producer i bumps counter i % kSub (a fire-and-forget reduction), lanes 0..kSub-1 of warp 0
+// poll one counter each until it reaches its target.  The counters only throttle polling;
+// correctness rests on the per-element epochs, so no fence is needed on either side.
+constexpr int kSub = 8;
+constexpr int kCtrWords = kSub * 32;   // words per exchange buffer id
+__device__ __forceinline__ void ctr_bump(uint32_t* ctr, int producer) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(ctr + (producer % kSub) * 32) : "memory");
+}
+// target_j = base_j + n_j where n_j = number of producers i < n with i % kSub == j
+__device__ __forceinline__ void gate_ctr(const uint32_t* ctr, const uint32_t* base, uint32_t rounds, int n) {
+  if ((threadIdx.x >> 5) != 0 || ctr == nullptr) return;
+  const int lane = threadIdx.x & 31;
+  if (lane < kSub) {
+    const uint32_t per_round = (uint32_t)((n - lane + kSub - 1) / kSub);
+    const uint32_t target = base[lane] + rounds * per_round;
+    while ((int32_t)(flag_load(ctr + lane * 32) - target) < 0) {}
+  }
+  __syncwarp();
 }
 
-// 8 consecutive storage elements of a shared-memory weight row -> floats
 __device__ __forceinline__ void lds8(const bf16* p, float (&v)[8]) {
   const uint4 u = *reinterpret_cast<const uint4*>(p);
   unpack8(u, v);
@@ -118,13 +154,13 @@ __device__ __forceinline__ void rows_of(int cta, int G, int N, int& r0, int& r1)
   r1 = (int)(((long long)(cta + 1) * N) / G);
 }
 __device__ __forceinline__ int rows_per_slot(int rowbytes) {
-  int r = kSlotBytes / rowbytes;
-  return r > kNW ? kNW : r;
+  int r = kSlotData / rowbytes;
+  return r > kMaxRows ? kMaxRows : r;
 }
 
-// ---- producer: stream this CTA's rows [r0,r1) of W[N,K] through the ring
+// ---- producer: stream this CTA's rows [r0,r1) of W[N,K] (+ their biases) through the ring
 template <typename WT>
-__device__ __forceinline__ void produce_phase(Ring& rg, const void* W, int N, int K, int cta, int G) {
+__device__ __forceinline__ void produce_phase(Ring& rg, const void* W, const float* bias, int N, int K, int cta, int G) {
   int r0, r1;
   rows_of(cta, G, N, r0, r1);
   const int rowbytes = K * (int)sizeof(WT);
@@ -134,103 +170,146 @@ __device__ __forceinline__ void produce_phase(Ring& rg, const void* W, int N, in
     const int n = min(rps, r1 - r);
     const int s = rg.it % rg.n_slots;
     const uint32_t ph = (rg.it / rg.n_slots) & 1;
+    uint8_t* slot = rg.slots + (size_t)s * kSlotBytes;
     mbar_wait(&rg.empty[s], ph ^ 1);
-    mbar_expect_tx(&rg.full[s], (uint32_t)(n * rowbytes));
-    bulk_g2s(rg.slots + (size_t)s * kSlotBytes, base + (size_t)r * rowbytes, (uint32_t)(n * rowbytes), &rg.full[s]);
+    // bias window: 16-byte aligned superset [r & ~3, (r + n + 3) & ~3) of the chunk's rows
+    const int b0 = r & ~3, b1 = (r + n + 3) & ~3;
+    const uint32_t bias_bytes = bias ? (uint32_t)(b1 - b0) * 4u : 0u;
+    mbar_expect_tx(&rg.full[s], (uint32_t)(n * rowbytes) + bias_bytes);
+    bulk_g2s(slot, base + (size_t)r * rowbytes, (uint32_t)(n * rowbytes), &rg.full[s]);
+    if (bias) bulk_g2s(slot + kSlotData, bias + b0, bias_bytes, &rg.full[s]);
     ++rg.it;
   }
 }
 
-// ---- consumers: every warp walks the same chunk sequence; warp w owns row w of each chunk.
-// pre(row) runs BEFORE the wait on the weight slot (it issues the bias / residual loads so their
-// L2 latency overlaps the wait); epi(row, acc[], pre_value) is called by all lanes of the
-// owning warp with the reduced sums.
-template <typename WT, int BT, typename Pre, typename Epi>
-__device__ __forceinline__ void consume_phase(Ring& rg, const float* xs, int N, int K, int cta, int G, Pre pre,
-                                              Epi epi) {
-  int r0, r1;
-  rows_of(cta, G, N, r0, r1);
-  const int rowbytes = K * (int)sizeof(WT);
-  const int rps = rows_per_slot(rowbytes);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int r = r0; r < r1; r += rps) {
-    const int n = min(rps, r1 - r);
-    const int s = rg.it % rg.n_slots;
-    const uint32_t ph = (rg.it / rg.n_slots) & 1;
-    float pv = 0.f;
-    if (warp < n) pv = pre(r + warp);
-    mbar_wait(&rg.full[s], ph);
-    if (warp < n) {
-      const WT* wrow = reinterpret_cast<const WT*>(rg.slots + (size_t)s * kSlotBytes + (size_t)warp * rowbytes);
-      float acc[BT];
-#pragma unroll
-      for (int b = 0; b < BT; ++b) acc[b] = 0.f;
-#pragma unroll 4
-      for (int k0 = lane * 8; k0 < K; k0 += 256) {
-        float w[8];
-        lds8(wrow + k0, w);
-#pragma unroll
-        for (int b = 0; b < BT; ++b) {
-          const float4 x0 = *reinterpret_cast<const float4*>(xs + b * K + k0);
-          const float4 x1 = *reinterpret_cast<const float4*>(xs + b * K + k0 + 4);
-          acc[b] = fmaf(w[0], x0.x, acc[b]); acc[b] = fmaf(w[1], x0.y, acc[b]);
-          acc[b] = fmaf(w[2], x0.z, acc[b]); acc[b] = fmaf(w[3], x0.w, acc[b]);
-          acc[b] = fmaf(w[4], x1.x, acc[b]); acc[b] = fmaf(w[5], x1.y, acc[b]);
-          acc[b] = fmaf(w[6], x1.z, acc[b]); acc[b] = fmaf(w[7], x1.w, acc[b]);
-        }
-      }
-#pragma unroll
-      for (int b = 0; b < BT; ++b) acc[b] = warp_sum(acc[b]);
-      epi(r + warp, acc, pv);
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&rg.empty[s]);
-    ++rg.it;
+// ======================================================================================
+// Consumer side.  The whole step is ~60 phases that differ only in parameters, so every phase
+// runs through the SAME three non-inlined routines (stage, rows, attention): the hot loop must
+// fit the instruction cache - a fully inlined version was 120 KB of SASS and ran every phase on
+// cold instruction fetches, 5-10x slower than the arithmetic warrants.
+// ======================================================================================
+enum { SRC_LL = 0, SRC_PLAIN = 1, SRC_EMBED = 2 };
+enum { EPI_QKV = 0, EPI_PROJ = 1, EPI_FC = 2, EPI_PROJ2 = 3, EPI_HEAD = 4 };
+
+struct Phase {
+  // ---- input vector x[B,K]
+  int src_kind; const u64* src_ll; const float* src_plain; int K; uint32_t src_epoch;
+  const uint32_t* src_ctr; const uint32_t* src_base; uint32_t src_rounds; int src_nprod;
+  const float* ln_g; const float* ln_b;              // LayerNorm affine, or NULL for a plain copy
+  // ---- what to publish for the previous phase (counter block + producer index), or NULL
+  uint32_t* pub_ctr; int pub_idx;
+  // ---- rows
+  int N; int has_bias; int mode;
+  u64* dst_ll; float* dst_plain; uint32_t dst_epoch;
+};
+
+template <typename WT> struct Ctx {
+  Ring rg;
+  float *xs, *red, *hloc, *h2loc, *sbv; int* sbi; int *s_ids, *s_pos;
+  const WT *wte, *wpe;
+  int B, H, V, n_pos, G, cta, c0; float eps; float* logits_out;
+};
+
+template <typename WT>
+__device__ __forceinline__ bool fetch_x(const Ctx<WT>& cx, const Phase& ph, int b, int k, float& v) {
+  if (ph.src_kind == SRC_LL) {
+    const u64 w = ll_load(ph.src_ll + (size_t)b * ph.K + k);
+    v = __uint_as_float((uint32_t)w);
+    return (uint32_t)(w >> 32) == ph.src_epoch;
   }
+  if (ph.src_kind == SRC_PLAIN) {
+    v = __ldcg(ph.src_plain + (size_t)b * ph.K + k);
+    return true;
+  }
+  v = to_f(cx.wte[(size_t)cx.s_ids[b] * cx.H + k]) + to_f(cx.wpe[(size_t)min(cx.s_pos[b], cx.n_pos - 1) * cx.H + k]);
+  return true;
 }
 
-// Stage x[B,K] (fp32, written by other CTAs in the previous phase: read through L2) into shared
-// memory.  Plain copy variant.
-template <int BT>
-__device__ __forceinline__ void stage_copy(float* xs, const float* x, int ldx, int B, int K) {
-  const int tid = threadIdx.x;
-#pragma unroll
-  for (int b = 0; b < BT; ++b) {
-    if (b < B) {
-      for (int k = tid * 4; k < K; k += kConsumers * 4)
-        *reinterpret_cast<float4*>(xs + b * K + k) = __ldcg(reinterpret_cast<const float4*>(x + (size_t)b * ldx + k));
-    } else {
-      for (int k = tid; k < K; k += kConsumers) xs[b * K + k] = 0.f;
-    }
-  }
+// barrier (previous phase fully done in this CTA) -> publish it -> wait for this phase's producers
+__device__ __forceinline__ void stage_enter(uint32_t* pub_ctr, int pub_idx, const uint32_t* ctr, const uint32_t* base,
+                                         uint32_t rounds, int n_prod) {
+  consumer_sync();
+  if (threadIdx.x == 0 && pub_ctr != nullptr) ctr_bump(pub_ctr, pub_idx);
+  gate_ctr(ctr, base, rounds, n_prod);
   consumer_sync();
 }
 
-// LayerNorm variant (K = H <= 2048): the row lives in registers, mean and the two-pass biased
-// variance each cost one shared-memory exchange; three barriers in all.
-constexpr int kLnPer = 4;  // elements per thread: H <= 4 * 512
-template <int BT>
-__device__ __forceinline__ void stage_ln(float* xs, float* red, const float* x, int ldx, int B, int K,
-                                         const float* __restrict__ g, const float* __restrict__ bta, float eps) {
-  const int tid = threadIdx.x, w = tid >> 5, l = tid & 31;
+// Collect x[B,K] into shared memory; elements not yet visible are re-read until they are.
+// LayerNorm variant (K = H <= 1920): the row lives in registers; mean and the two-pass biased
+// variance ([hf] modeling_gpt2.py:252,254,505) each cost one shared-memory exchange.  Fully
+// unrolled on purpose: every load of a thread is in flight before the first one is checked.
+template <typename WT, int BT>
+__device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
+  const int tid = threadIdx.x, w = tid >> 5, l = tid & 31, K = ph.K, B = cx.B;
+  float* xs = cx.xs;
+  if (ph.ln_g == nullptr) {
+    stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
+                ph.src_nprod);
+#pragma unroll
+    for (int b = 0; b < BT; ++b) {
+      if (b >= B) {
+        for (int k = tid; k < K; k += kConsumers) xs[b * K + k] = 0.f;
+        continue;
+      }
+      unsigned pending = 0;
+#pragma unroll
+      for (int i = 0; i < kCopyPer; ++i) {
+        const int k = tid + i * kConsumers;
+        if (k < K) {
+          float v;
+          if (fetch_x(cx, ph, b, k, v)) xs[b * K + k] = v;
+          else pending |= 1u << i;
+        }
+      }
+      while (pending) {
+#pragma unroll
+        for (int i = 0; i < kCopyPer; ++i)
+          if (pending & (1u << i)) {
+            float v;
+            if (fetch_x(cx, ph, b, tid + i * kConsumers, v)) { xs[b * K + tid + i * kConsumers] = v; pending &= ~(1u << i); }
+          }
+      }
+    }
+    consumer_sync();
+    return;
+  }
   float v[BT][kLnPer], gg[kLnPer], bb[kLnPer];
 #pragma unroll
   for (int i = 0; i < kLnPer; ++i) {
     const int k = tid + i * kConsumers;
-    gg[i] = (k < K) ? g[k] : 0.f;
-    bb[i] = (k < K) ? bta[k] : 0.f;
-#pragma unroll
-    for (int b = 0; b < BT; ++b) v[b][i] = (b < B && k < K) ? __ldcg(x + (size_t)b * ldx + k) : 0.f;
+    gg[i] = (k < K) ? ph.ln_g[k] : 0.f;
+    bb[i] = (k < K) ? ph.ln_b[k] : 0.f;
   }
-  float* redA = red;             // [BT][kNW]
-  float* redB = red + BT * kNW;  // [BT][kNW]
+  stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
+              ph.src_nprod);
+  unsigned pending = 0;
+#pragma unroll
+  for (int i = 0; i < kLnPer; ++i) {
+    const int k = tid + i * kConsumers;
+#pragma unroll
+    for (int b = 0; b < BT; ++b) {
+      v[b][i] = 0.f;
+      if (b < B && k < K && !fetch_x(cx, ph, b, k, v[b][i])) pending |= 1u << (b * kLnPer + i);
+    }
+  }
+  while (pending) {
+#pragma unroll
+    for (int b = 0; b < BT; ++b)
+#pragma unroll
+      for (int i = 0; i < kLnPer; ++i)
+        if (pending & (1u << (b * kLnPer + i))) {
+          if (fetch_x(cx, ph, b, tid + i * kConsumers, v[b][i])) pending &= ~(1u << (b * kLnPer + i));
+        }
+  }
+  float* redA = cx.red;             // [BT][kNW]
+  float* redB = cx.red + BT * kNW;  // [BT][kNW]
 #pragma unroll
   for (int b = 0; b < BT; ++b) {
-    float s = 0.f;
+    float sum = 0.f;
 #pragma unroll
-    for (int i = 0; i < kLnPer; ++i) s += v[b][i];
-    s = warp_sum(s);
-    if (l == 0) redA[b * kNW + w] = s;
+    for (int i = 0; i < kLnPer; ++i) sum += v[b][i];
+    sum = warp_sum(sum);
+    if (l == 0) redA[b * kNW + w] = sum;
   }
   consumer_sync();
   float mean[BT];
@@ -256,7 +335,7 @@ __device__ __forceinline__ void stage_ln(float* xs, float* red, const float* x, 
     float t = 0.f;
 #pragma unroll
     for (int i = 0; i < kNW; ++i) t += redB[b * kNW + i];
-    const float rstd = rsqrtf(t / (float)K + eps);
+    const float rstd = rsqrtf(t / (float)K + cx.eps);
 #pragma unroll
     for (int i = 0; i < kLnPer; ++i) {
       const int k = tid + i * kConsumers;
@@ -272,6 +351,79 @@ struct Best {
 };
 __device__ __forceinline__ void best_merge(Best& a, float v, int i) {
   if (v > a.v || (v == a.v && i < a.i)) { a.v = v; a.i = i; }
+}
+
+// Every warp walks the same chunk sequence; warp w owns rows w, w+15 of each chunk.
+template <typename WT, int BT>
+__device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
+  Ring& rg = cx.rg;
+  int r0, r1;
+  rows_of(cx.cta, cx.G, ph.N, r0, r1);
+  const int K = ph.K, B = cx.B;
+  const int rowbytes = K * (int)sizeof(WT);
+  const int rps = rows_per_slot(rowbytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float* xs = cx.xs;
+  Best best[BT];
+#pragma unroll
+  for (int b = 0; b < BT; ++b) { best[b].v = -INFINITY; best[b].i = 0x7fffffff; }
+  for (int r = r0; r < r1; r += rps) {
+    const int n = min(rps, r1 - r);
+    const int s = rg.it % rg.n_slots;
+    const uint32_t phs = (rg.it / rg.n_slots) & 1;
+    const uint8_t* slot = rg.slots + (size_t)s * kSlotBytes;
+    if (lane == 0) mbar_wait(&rg.full[s], phs);   // one waiter per warp
+    __syncwarp();
+    for (int rr = warp; rr < n; rr += kNW) {
+      const WT* wrow = reinterpret_cast<const WT*>(slot + (size_t)rr * rowbytes);
+      float acc[BT];
+#pragma unroll
+      for (int b = 0; b < BT; ++b) acc[b] = 0.f;
+#pragma unroll 4
+      for (int k0 = lane * 8; k0 < K; k0 += 256) {
+        float w[8];
+        lds8(wrow + k0, w);
+#pragma unroll
+        for (int b = 0; b < BT; ++b) {
+          const float4 x0 = *reinterpret_cast<const float4*>(xs + b * K + k0);
+          const float4 x1 = *reinterpret_cast<const float4*>(xs + b * K + k0 + 4);
+          acc[b] = fmaf(w[0], x0.x, acc[b]); acc[b] = fmaf(w[1], x0.y, acc[b]);
+          acc[b] = fmaf(w[2], x0.z, acc[b]); acc[b] = fmaf(w[3], x0.w, acc[b]);
+          acc[b] = fmaf(w[4], x1.x, acc[b]); acc[b] = fmaf(w[5], x1.y, acc[b]);
+          acc[b] = fmaf(w[6], x1.z, acc[b]); acc[b] = fmaf(w[7], x1.w, acc[b]);
+        }
+      }
+      const float bv = ph.has_bias ? reinterpret_cast<const float*>(slot + kSlotData)[(r & 3) + rr] : 0.f;
+      const int row = r + rr;
+#pragma unroll
+      for (int b = 0; b < BT; ++b) acc[b] = warp_sum(acc[b]);
+      if (ph.mode == EPI_HEAD) {
+#pragma unroll
+        for (int b = 0; b < BT; ++b) {
+          best_merge(best[b], acc[b], row);
+          if (cx.logits_out != nullptr && lane == 0 && b < B) cx.logits_out[(size_t)b * cx.V + row] = acc[b];
+        }
+      } else if (lane < B) {
+        float v = 0.f;
+#pragma unroll
+        for (int b = 0; b < BT; ++b) if (lane == b) v = acc[b];
+        v += bv;
+        const int own = lane * kOwnMax + (row - cx.c0);
+        if (ph.mode == EPI_PROJ) { v += cx.hloc[own]; cx.h2loc[own] = v; }
+        else if (ph.mode == EPI_FC) v = gelu_new(v);
+        else if (ph.mode == EPI_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
+        if (ph.dst_plain != nullptr) ph.dst_plain[(size_t)lane * ph.N + row] = v;
+        else ll_store(ph.dst_ll + (size_t)lane * ph.N + row, v, ph.dst_epoch);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&rg.empty[s]);
+    ++rg.it;
+  }
+  if (ph.mode == EPI_HEAD && lane == 0) {
+#pragma unroll
+    for (int b = 0; b < BT; ++b) { cx.sbv[warp * BT + b] = best[b].v; cx.sbi[warp * BT + b] = best[b].i; }
+  }
 }
 
 // raw (still packed) 8-element chunk of a K/V cache row, so a prefetch costs few registers
@@ -306,6 +458,120 @@ __device__ __forceinline__ void soft_merge(SoftState& a, float mo, float lo, con
   a.m = mn;
 }
 
+struct AttnArgs {
+  void *kc, *vc; const u64* qkv_ll; u64* attn_ll; uint32_t ep_qkv, ep_attn;
+  uint32_t *ctr_qkv, *ctr_attn; const uint32_t* base_qkv; uint32_t rounds;
+  int nh, slot0, max_ctx; float *part, *pm, *pl, *qkv_s;
+};
+
+// Decode attention for one (b, head) task.  Cached K/V rows do not depend on this step, so the
+// first two rows of every 8-lane group are fetched before q is waited for.  `pub_ctr` (the
+// CTA's own qkv publish) is consumed by the first task.
+template <typename WT>
+__device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, int task, uint32_t* pub_ctr) {
+  constexpr int D = 64;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, sub = lane >> 3, l8 = lane & 7;
+  const int grp = warp * 4 + sub;                    // key rows t = grp + kGroups*j belong to this 8-lane group
+  const unsigned grp_mask = 0xFFu << (sub * 8);
+  const int H = cx.H, nh = a.nh;
+  const int b = task / nh, head = task - b * nh;
+  const size_t base = ((size_t)(a.slot0 + b) * nh + head) * (size_t)a.max_ctx * D;
+  WT* Kc = reinterpret_cast<WT*>(a.kc) + base;
+  WT* Vc = reinterpret_cast<WT*>(a.vc) + base;
+  const int pos = cx.s_pos[b];
+  Raw8<WT> pk0, pk1, pv0, pv1;
+  if (grp < pos) {
+    pk0.load(Kc + (size_t)grp * D + l8 * 8);
+    pv0.load(Vc + (size_t)grp * D + l8 * 8);
+  }
+  if (grp + kGroups < pos) {
+    pk1.load(Kc + (size_t)(grp + kGroups) * D + l8 * 8);
+    pv1.load(Vc + (size_t)(grp + kGroups) * D + l8 * 8);
+  }
+  stage_enter(pub_ctr, cx.cta, a.ctr_qkv, a.base_qkv, a.rounds, cx.G);
+  // q, k_new, v_new of this head: 192 values, one per thread, into shared memory
+  if (tid < 3 * D) {
+    const int which = tid / D, i = tid - which * D;
+    const float val = __uint_as_float(ll_wait_bits(a.qkv_ll + (size_t)b * 3 * H + which * H + head * D + i, a.ep_qkv));
+    if (which == 0) {
+      a.qkv_s[i] = val * 0.125f;                     // 64^-0.5
+    } else {
+      // the new row goes into the cache for later steps, storage-rounded like every row
+      const WT r = from_f<WT>(val);
+      (which == 1 ? Kc : Vc)[(size_t)pos * D + i] = r;
+      a.qkv_s[which * D + i] = to_f(r);
+    }
+  }
+  consumer_sync();
+  float qv[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) qv[i] = a.qkv_s[l8 * 8 + i];
+  SoftState st;
+  st.m = -INFINITY; st.l = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) st.acc[i] = 0.f;
+  for (int j = 0; grp + kGroups * j <= pos; ++j) {
+    const int t = grp + kGroups * j;
+    float kk[8], vv[8];
+    if (t == pos) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { kk[i] = a.qkv_s[D + l8 * 8 + i]; vv[i] = a.qkv_s[2 * D + l8 * 8 + i]; }
+    } else if (j == 0) {
+      pk0.get(kk);
+      pv0.get(vv);
+    } else if (j == 1) {
+      pk1.get(kk);
+      pv1.get(vv);
+    } else {
+      load8(Kc + (size_t)t * D + l8 * 8, kk);
+      load8(Vc + (size_t)t * D + l8 * 8, vv);
+    }
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) dot = fmaf(qv[i], kk[i], dot);
+    dot += __shfl_xor_sync(grp_mask, dot, 1);
+    dot += __shfl_xor_sync(grp_mask, dot, 2);
+    dot += __shfl_xor_sync(grp_mask, dot, 4);
+    const float mn = fmaxf(st.m, dot);
+    const float c1 = expf(st.m - mn), pe = expf(dot - mn);
+    st.l = st.l * c1 + pe;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) st.acc[i] = st.acc[i] * c1 + pe * vv[i];
+    st.m = mn;
+  }
+  __syncwarp();
+  // merge the four groups of the warp, then the 15 warps through shared memory
+#pragma unroll
+  for (int o = 8; o <= 16; o <<= 1) {
+    const float mo = __shfl_xor_sync(FULL_MASK, st.m, o), lo = __shfl_xor_sync(FULL_MASK, st.l, o);
+    float ao[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ao[i] = __shfl_xor_sync(FULL_MASK, st.acc[i], o);
+    soft_merge(st, mo, lo, ao);
+  }
+  if (sub == 0) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a.part[warp * D + l8 * 8 + i] = st.acc[i];
+    if (l8 == 0) { a.pm[warp] = st.m; a.pl[warp] = st.l; }
+  }
+  consumer_sync();
+  if (tid < D) {
+    float M = a.pm[0];
+#pragma unroll
+    for (int ww = 1; ww < kNW; ++ww) M = fmaxf(M, a.pm[ww]);
+    float Lsum = 0.f, o = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < kNW; ++ww) {
+      const float c = (a.pm[ww] == -INFINITY) ? 0.f : expf(a.pm[ww] - M);
+      Lsum += a.pl[ww] * c;
+      o += a.part[ww * D + tid] * c;
+    }
+    ll_store(a.attn_ll + (size_t)b * H + head * D + tid, o / Lsum, a.ep_attn);
+  }
+  consumer_sync();
+  if (tid == 0) ctr_bump(a.ctr_attn, task);
+}
+
 template <typename WT, int BT>
 __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const MegaParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -319,16 +585,22 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   float* pm = part + kNW * D;                                                   // [kNW]
   float* pl = pm + kNW;                                                         // [kNW]
   float* red = pl + kNW;                                                        // [2][BT][kNW]
-  float* sbv = red + 2 * BT * kNW;                                              // [kNW][BT]
+  float* hloc = red + 2 * BT * kNW;                                             // [BT][kOwnMax] residual h
+  float* h2loc = hloc + BT * kOwnMax;                                           // [BT][kOwnMax] residual h2
+  float* qkv_s = h2loc + BT * kOwnMax;                                          // [3*D] q, k_new, v_new of a task
+  float* sbv = qkv_s + 3 * D;                                                   // [kNW][BT]
   int* sbi = reinterpret_cast<int*>(sbv + kNW * BT);                            // [kNW][BT]
   int* s_ids = sbi + kNW * BT;                                                  // [8]
   int* s_pos = s_ids + 8;                                                       // [8]
   uint64_t* full = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(s_pos + 8) + 15) & ~(uintptr_t)15);
   uint64_t* empty = full + kMaxSlots;
-  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(empty + kMaxSlots);        // [L]
+  uint32_t* s_base = reinterpret_cast<uint32_t*>(empty + kMaxSlots);            // [64] counter values at launch
+  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_base + 64);              // [L]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < 64; ++i) s_base[i] = p.ctr_base[i];   // constant indices: no local copy of the params
     for (int s = 0; s < p.n_slots; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], kNW);
@@ -337,308 +609,158 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   }
   {  // layer table -> shared memory (pointer chasing through global memory would sit on every phase)
     const int n_words = p.L * (int)(sizeof(MegaLayer) / 8);
-    const unsigned long long* src = reinterpret_cast<const unsigned long long*>(p.layers);
-    unsigned long long* dst = reinterpret_cast<unsigned long long*>(s_layers);
+    const u64* src = reinterpret_cast<const u64*>(p.layers);
+    u64* dst = reinterpret_cast<u64*>(s_layers);
     for (int i = tid; i < n_words; i += kMegaThreads) dst[i] = src[i];
   }
   __syncthreads();
-  Ring rg{ring_base, full, empty, p.n_slots, 0u};
 
   if (warp == kNW) {
     // =============================== PRODUCER ===============================
     if (lane == 0) {
+      Ring rg{ring_base, full, empty, p.n_slots, 0u};
       for (int step = 0; step < p.n_steps; ++step) {
         for (int li = 0; li < p.L; ++li) {
           const MegaLayer& w = s_layers[li];
-          produce_phase<WT>(rg, w.attn_w, 3 * H, H, cta, G);
-          produce_phase<WT>(rg, w.proj_w, H, H, cta, G);
-          produce_phase<WT>(rg, w.fc_w, F, H, cta, G);
-          produce_phase<WT>(rg, w.mproj_w, H, F, cta, G);
+          produce_phase<WT>(rg, w.attn_w, w.attn_b, 3 * H, H, cta, G);
+          produce_phase<WT>(rg, w.proj_w, w.proj_b, H, H, cta, G);
+          produce_phase<WT>(rg, w.fc_w, w.fc_b, F, H, cta, G);
+          produce_phase<WT>(rg, w.mproj_w, w.mproj_b, H, F, cta, G);
         }
-        if (p.has_head) produce_phase<WT>(rg, p.wte, p.V, H, cta, G);
+        if (p.has_head) produce_phase<WT>(rg, p.wte, nullptr, p.V, H, cta, G);
       }
     }
     return;
   }
 
   // ================================= CONSUMERS =================================
-  unsigned bar_target = 0;
-  // grid barrier, split so that independent work (prefetches) can sit between arrive and wait
-  auto grid_arrive = [&]() {
-    consumer_sync();
-    if (tid == 0) {
-      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.bar) : "memory");
-      bar_target += (unsigned)G;
-    }
-  };
-  auto grid_wait = [&]() {
-    if (tid == 0) {
-      while (ld_acquire(p.bar) < bar_target) {}
-    }
-    consumer_sync();
-  };
-  auto grid_sync = [&]() {
-    grid_arrive();
-    grid_wait();
-  };
-  // optional phase trace (GP_MEGA_TRACE): SM clock of CTA 0 at every phase boundary of the last step
+  // optional phase trace (GP_MEGA_TRACE): every CTA records %globaltimer (ns, one clock for the whole GPU)
   int n_stamp = 0;
   auto stamp = [&](int step) {
-    if (p.trace != nullptr && cta == 0 && tid == 0 && step == p.n_steps - 1 && n_stamp < p.trace_cap)
-      p.trace[n_stamp++] = clock64();
+    if (p.trace != nullptr && tid == 0 && step == p.n_steps - 1 && n_stamp < p.trace_cap)
+      p.trace[(size_t)cta * p.trace_cap + n_stamp++] = (long long)globaltimer();
   };
-  if (tid < 8) s_pos[tid] = (tid < B) ? p.lens[p.slot0 + tid] : 0;
+  if (tid < 8) {
+    s_pos[tid] = (tid < B) ? min(p.lens[p.slot0 + tid], p.max_ctx - 1) : 0;
+    s_ids[tid] = (tid < B && p.has_embed) ? min(max(__ldcg(p.ids + tid), 0), p.V - 1) : 0;
+  }
   if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[p.n_steps] = globaltimer();  // start stamp
   consumer_sync();
 
-  const int sub = lane >> 3, l8 = lane & 7;
-  const int grp = warp * 4 + sub;                    // 0..63: key rows t = grp + 64 j belong to this 8-lane group
-  const unsigned grp_mask = 0xFFu << (sub * 8);
+  Ctx<WT> cx;
+  cx.rg = Ring{ring_base, full, empty, p.n_slots, 0u};
+  cx.xs = xs; cx.red = red; cx.hloc = hloc; cx.h2loc = h2loc; cx.sbv = sbv; cx.sbi = sbi; cx.s_ids = s_ids; cx.s_pos = s_pos;
+  cx.wte = reinterpret_cast<const WT*>(p.wte); cx.wpe = reinterpret_cast<const WT*>(p.wpe);
+  cx.B = B; cx.H = H; cx.V = p.V; cx.n_pos = p.n_pos; cx.G = G; cx.cta = cta; cx.eps = p.eps; cx.logits_out = p.logits_out;
+  int c0, c1;                                        // residual rows this CTA owns (same split as N = H phases)
+  rows_of(cta, G, H, c0, c1);
+  cx.c0 = c0;
+  // counter blocks, one per exchange buffer id (1 qkv, 2 attn, 3 h2, 4 act, 5 h, 6 argmax); their values at
+  // launch are in p.ctr_base; `rounds` = publishes per producer so far in this launch, this one included
+  auto ctr_of = [&](int id) { return p.flags + id * kCtrWords; };
+  auto base_of = [&](int id) { return s_base + id * kSub; };
 
   for (int step = 0; step < p.n_steps; ++step) {
-    const float* hcur = p.hidden_in;  // residual stream feeding the first layer
-    if (p.has_embed) {
-      // ---- embed: h[b,:] = wte[id] + wpe[pos]; every CTA writes its column slice
-      int c0, c1;
-      rows_of(cta, G, H, c0, c1);
-      const WT* wte = reinterpret_cast<const WT*>(p.wte);
-      const WT* wpe = reinterpret_cast<const WT*>(p.wpe);
-      for (int i = tid; i < B * (c1 - c0); i += kConsumers) {
-        const int b = i / (c1 - c0), col = c0 + i % (c1 - c0);
-        int id = (step == 0) ? __ldcg(p.ids + b) : s_ids[b];   // later steps: this CTA's own argmax result
-        id = min(max(id, 0), p.V - 1);
-        const int pos = min(s_pos[b], p.n_pos - 1);
-        p.hbuf[(size_t)b * H + col] = to_f(wte[(size_t)id * H + col]) + to_f(wpe[(size_t)pos * H + col]);
-      }
-      grid_sync();
-      hcur = p.hbuf;
+    const uint32_t ep_step = p.epoch0 + (uint32_t)step * (uint32_t)(p.L + 1) * 8u;
+    // ---- the residual slice this CTA owns: embedding rows (stage 0) or the incoming hidden state
+    for (int i = tid; i < B * (c1 - c0); i += kConsumers) {
+      const int b = i / (c1 - c0), col = c0 + i % (c1 - c0);
+      hloc[b * kOwnMax + (col - c0)] =
+          p.has_embed ? to_f(cx.wte[(size_t)s_ids[b] * H + col]) + to_f(cx.wpe[(size_t)min(s_pos[b], p.n_pos - 1) * H + col])
+                      : __ldcg(p.hidden_in + (size_t)b * H + col);
     }
     stamp(step);
+    uint32_t* pub_ctr = nullptr;   // counter block the next stage has to bump for the phase before it
     for (int li = 0; li < p.L; ++li) {
       const MegaLayer& w = s_layers[li];
       const bool last = (li == p.L - 1);
+      const uint32_t ep = ep_step + (uint32_t)li * 8u;         // +1 qkv, +2 attn, +3 h2, +4 act, +5 h
+      const uint32_t rnd = (uint32_t)(step * p.L + li) + 1u;   // publishes per producer and buffer, this layer included
+      Phase ph;
       // ---- P1: ln_1 + c_attn -> qkv[b, 3H]
-      stage_ln<BT>(xs, red, hcur, H, B, H, w.ln1_g, w.ln1_b, p.eps);
+      ph.src_kind = (li > 0) ? SRC_LL : (p.has_embed ? SRC_EMBED : SRC_PLAIN);
+      ph.src_ll = p.h_ll; ph.src_plain = p.hidden_in; ph.K = H; ph.src_epoch = ep - 8u + 5u;
+      ph.src_ctr = ctr_of(5); ph.src_base = base_of(5); ph.src_rounds = rnd - 1u; ph.src_nprod = G;
+      ph.ln_g = w.ln1_g; ph.ln_b = w.ln1_b; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
+      ph.N = 3 * H; ph.has_bias = 1; ph.mode = EPI_QKV; ph.dst_ll = p.qkv_ll; ph.dst_plain = nullptr; ph.dst_epoch = ep + 1u;
+      stage_x<WT, BT>(cx, ph);
       stamp(step);
-      consume_phase<WT, BT>(
-          rg, xs, 3 * H, H, cta, G, [&](int n) { return (lane < B) ? w.attn_b[n] : 0.f; },
-          [&](int n, const float(&acc)[BT], float pv) {
-            if (lane < B) {
-              float v = 0.f;
-#pragma unroll
-              for (int b = 0; b < BT; ++b) if (lane == b) v = acc[b];
-              p.qkv[(size_t)lane * 3 * H + n] = v + pv;
-            }
-          });
+      run_rows<WT, BT>(cx, ph);
+      pub_ctr = ctr_of(1);
       stamp(step);
-      grid_arrive();
-      // ---- P2: attention for (b, head) tasks.  Old K/V rows do not depend on this step, so the
-      // first two rows of every 8-lane group are fetched while the barrier completes.
-      const bool has_task = cta < B * nh;
-      Raw8<WT> pk0, pk1, pv0, pv1;
-      if (has_task) {
-        const int b = cta / nh, head = cta - b * nh;
-        const size_t base = ((size_t)(p.slot0 + b) * nh + head) * (size_t)p.max_ctx * D;
-        const WT* Kc = reinterpret_cast<const WT*>(w.kc) + base;
-        const WT* Vc = reinterpret_cast<const WT*>(w.vc) + base;
-        const int pos = s_pos[b];
-        if (grp < pos) {
-          pk0.load(Kc + (size_t)grp * D + l8 * 8);
-          pv0.load(Vc + (size_t)grp * D + l8 * 8);
-        }
-        if (grp + 64 < pos) {
-          pk1.load(Kc + (size_t)(grp + 64) * D + l8 * 8);
-          pv1.load(Vc + (size_t)(grp + 64) * D + l8 * 8);
+      // ---- P2: attention for the (b, head) tasks of this CTA
+      if (cta < B * nh) {
+        AttnArgs a;
+        a.kc = w.kc; a.vc = w.vc; a.qkv_ll = p.qkv_ll; a.attn_ll = p.attn_ll; a.ep_qkv = ep + 1u; a.ep_attn = ep + 2u;
+        a.ctr_qkv = ctr_of(1); a.ctr_attn = ctr_of(2); a.base_qkv = base_of(1); a.rounds = rnd;
+        a.nh = nh; a.slot0 = p.slot0; a.max_ctx = p.max_ctx; a.part = part; a.pm = pm; a.pl = pl; a.qkv_s = qkv_s;
+        for (int task = cta; task < B * nh; task += G) {
+          attention_task<WT>(cx, a, task, pub_ctr);
+          pub_ctr = nullptr;
         }
       }
-      grid_wait();
       stamp(step);
-      for (int task = cta; task < B * nh; task += G) {
-        const int b = task / nh, head = task - b * nh;
-        const size_t base = ((size_t)(p.slot0 + b) * nh + head) * (size_t)p.max_ctx * D;
-        WT* Kc = reinterpret_cast<WT*>(w.kc) + base;
-        WT* Vc = reinterpret_cast<WT*>(w.vc) + base;
-        const int pos = min(s_pos[b], p.max_ctx - 1);
-        const float* qrow = p.qkv + (size_t)b * 3 * H + head * D;
-        float qv[8];
-        {
-          const float4 a = __ldcg(reinterpret_cast<const float4*>(qrow + l8 * 8));
-          const float4 c4 = __ldcg(reinterpret_cast<const float4*>(qrow + l8 * 8 + 4));
-          const float sc = 0.125f;  // 64^-0.5
-          qv[0] = a.x * sc; qv[1] = a.y * sc; qv[2] = a.z * sc; qv[3] = a.w * sc;
-          qv[4] = c4.x * sc; qv[5] = c4.y * sc; qv[6] = c4.z * sc; qv[7] = c4.w * sc;
-        }
-        // the new row goes into the cache for later steps (this step reads it from qkv directly)
-        if (tid >= 64 && tid < 64 + 2 * D) {
-          const int i = tid - 64;
-          const float val = __ldcg(qrow + H + i);   // i < 64: k, else v (contiguous thirds: +H, +2H)
-          if (i < D) Kc[(size_t)pos * D + i] = from_f<WT>(val);
-          else Vc[(size_t)pos * D + (i - D)] = from_f<WT>(__ldcg(qrow + 2 * H + (i - D)));
-        }
-        SoftState st;
-        st.m = -INFINITY; st.l = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) st.acc[i] = 0.f;
-        for (int j = 0; grp + 64 * j <= pos; ++j) {
-          const int t = grp + 64 * j;
-          float kk[8], vv[8];
-          if (t == pos) {
-            // storage-rounded like every other cached row, so a step is independent of where the
-            // row is read from
-            const float4 k0 = __ldcg(reinterpret_cast<const float4*>(qrow + H + l8 * 8));
-            const float4 k1 = __ldcg(reinterpret_cast<const float4*>(qrow + H + l8 * 8 + 4));
-            const float4 v0 = __ldcg(reinterpret_cast<const float4*>(qrow + 2 * H + l8 * 8));
-            const float4 v1 = __ldcg(reinterpret_cast<const float4*>(qrow + 2 * H + l8 * 8 + 4));
-            const float kf[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
-            const float vf[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-#pragma unroll
-            for (int i = 0; i < 8; ++i) { kk[i] = to_f(from_f<WT>(kf[i])); vv[i] = to_f(from_f<WT>(vf[i])); }
-          } else if (j == 0 && task == cta) {
-            pk0.get(kk);
-            pv0.get(vv);
-          } else if (j == 1 && task == cta) {
-            pk1.get(kk);
-            pv1.get(vv);
-          } else {
-            load8(Kc + (size_t)t * D + l8 * 8, kk);
-            load8(Vc + (size_t)t * D + l8 * 8, vv);
-          }
-          float dot = 0.f;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) dot = fmaf(qv[i], kk[i], dot);
-          dot += __shfl_xor_sync(grp_mask, dot, 1);
-          dot += __shfl_xor_sync(grp_mask, dot, 2);
-          dot += __shfl_xor_sync(grp_mask, dot, 4);
-          const float mn = fmaxf(st.m, dot);
-          const float c1 = expf(st.m - mn), pe = expf(dot - mn);
-          st.l = st.l * c1 + pe;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) st.acc[i] = st.acc[i] * c1 + pe * vv[i];
-          st.m = mn;
-        }
-        __syncwarp();
-        // merge the four groups of the warp, then the 16 warps through shared memory
-#pragma unroll
-        for (int o = 8; o <= 16; o <<= 1) {
-          const float mo = __shfl_xor_sync(FULL_MASK, st.m, o), lo = __shfl_xor_sync(FULL_MASK, st.l, o);
-          float ao[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) ao[i] = __shfl_xor_sync(FULL_MASK, st.acc[i], o);
-          soft_merge(st, mo, lo, ao);
-        }
-        if (sub == 0) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) part[warp * D + l8 * 8 + i] = st.acc[i];
-          if (l8 == 0) { pm[warp] = st.m; pl[warp] = st.l; }
-        }
-        consumer_sync();
-        if (tid < D) {
-          float M = pm[0];
-#pragma unroll
-          for (int ww = 1; ww < kNW; ++ww) M = fmaxf(M, pm[ww]);
-          float Lsum = 0.f, o = 0.f;
-#pragma unroll
-          for (int ww = 0; ww < kNW; ++ww) {
-            const float c = (pm[ww] == -INFINITY) ? 0.f : expf(pm[ww] - M);
-            Lsum += pl[ww] * c;
-            o += part[ww * D + tid] * c;
-          }
-          p.attn[(size_t)b * H + head * D + tid] = o / Lsum;
-        }
-        consumer_sync();
-      }
+      // ---- P3: attention c_proj + residual -> h2   (CTAs without an attention task publish qkv here)
+      ph.src_kind = SRC_LL; ph.src_ll = p.attn_ll; ph.K = H; ph.src_epoch = ep + 2u;
+      ph.src_ctr = ctr_of(2); ph.src_base = base_of(2); ph.src_rounds = rnd; ph.src_nprod = B * nh;
+      ph.ln_g = nullptr; ph.ln_b = nullptr; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
+      ph.N = H; ph.mode = EPI_PROJ; ph.dst_ll = p.h2_ll; ph.dst_epoch = ep + 3u;
+      stage_x<WT, BT>(cx, ph);
       stamp(step);
-      grid_sync();
-      stamp(step);
-      // ---- P3: attention c_proj + residual -> h2
-      stage_copy<BT>(xs, p.attn, H, B, H);
-      stamp(step);
-      consume_phase<WT, BT>(
-          rg, xs, H, H, cta, G,
-          [&](int n) { return (lane < B) ? w.proj_b[n] + __ldcg(hcur + (size_t)lane * H + n) : 0.f; },
-          [&](int n, const float(&acc)[BT], float pv) {
-            if (lane < B) {
-              float v = 0.f;
-#pragma unroll
-              for (int b = 0; b < BT; ++b) if (lane == b) v = acc[b];
-              p.h2[(size_t)lane * H + n] = v + pv;
-            }
-          });
-      stamp(step);
-      grid_sync();
+      run_rows<WT, BT>(cx, ph);
       stamp(step);
       // ---- P4: ln_2 + c_fc + gelu_new -> act
-      stage_ln<BT>(xs, red, p.h2, H, B, H, w.ln2_g, w.ln2_b, p.eps);
+      ph.src_ll = p.h2_ll; ph.src_epoch = ep + 3u; ph.src_ctr = ctr_of(3); ph.src_base = base_of(3); ph.src_nprod = G;
+      ph.ln_g = w.ln2_g; ph.ln_b = w.ln2_b; ph.pub_ctr = ctr_of(3);
+      ph.N = F; ph.mode = EPI_FC; ph.dst_ll = p.act_ll; ph.dst_epoch = ep + 4u;
+      stage_x<WT, BT>(cx, ph);
       stamp(step);
-      consume_phase<WT, BT>(
-          rg, xs, F, H, cta, G, [&](int n) { return (lane < B) ? w.fc_b[n] : 0.f; },
-          [&](int n, const float(&acc)[BT], float pv) {
-            if (lane < B) {
-              float v = 0.f;
-#pragma unroll
-              for (int b = 0; b < BT; ++b) if (lane == b) v = acc[b];
-              p.act[(size_t)lane * F + n] = gelu_new(v + pv);
-            }
-          });
-      stamp(step);
-      grid_sync();
+      run_rows<WT, BT>(cx, ph);
       stamp(step);
       // ---- P5: mlp c_proj + residual -> h (or the stage output)
-      float* dst = (last && !p.has_head) ? p.hidden_out : p.hbuf;
-      stage_copy<BT>(xs, p.act, F, B, F);
+      ph.src_ll = p.act_ll; ph.K = F; ph.src_epoch = ep + 4u; ph.src_ctr = ctr_of(4); ph.src_base = base_of(4);
+      ph.ln_g = nullptr; ph.ln_b = nullptr; ph.pub_ctr = ctr_of(4);
+      ph.N = H; ph.mode = EPI_PROJ2; ph.dst_ll = p.h_ll; ph.dst_epoch = ep + 5u;
+      ph.dst_plain = (last && !p.has_head) ? p.hidden_out : nullptr;
+      stage_x<WT, BT>(cx, ph);
       stamp(step);
-      consume_phase<WT, BT>(
-          rg, xs, H, F, cta, G,
-          [&](int n) { return (lane < B) ? w.mproj_b[n] + __ldcg(p.h2 + (size_t)lane * H + n) : 0.f; },
-          [&](int n, const float(&acc)[BT], float pv) {
-            if (lane < B) {
-              float v = 0.f;
-#pragma unroll
-              for (int b = 0; b < BT; ++b) if (lane == b) v = acc[b];
-              dst[(size_t)lane * H + n] = v + pv;
-            }
-          });
+      run_rows<WT, BT>(cx, ph);
+      pub_ctr = ctr_of(5);   // bumped even when the rows went to hidden_out: counts stay regular
       stamp(step);
-      grid_sync();
-      stamp(step);
-      hcur = p.hbuf;
     }
     if (p.has_head) {
       // ---- ln_f + lm_head + argmax
-      stage_ln<BT>(xs, red, p.hbuf, H, B, H, p.lnf_g, p.lnf_b, p.eps);
+      const uint32_t ep = ep_step + (uint32_t)p.L * 8u;
+      Phase ph;
+      ph.src_kind = SRC_LL; ph.src_ll = p.h_ll; ph.src_plain = nullptr; ph.K = H; ph.src_epoch = ep - 8u + 5u;
+      ph.src_ctr = ctr_of(5); ph.src_base = base_of(5); ph.src_rounds = (uint32_t)(step * p.L + p.L); ph.src_nprod = G;
+      ph.ln_g = p.lnf_g; ph.ln_b = p.lnf_b; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
+      ph.N = p.V; ph.has_bias = 0; ph.mode = EPI_HEAD; ph.dst_ll = nullptr; ph.dst_plain = nullptr; ph.dst_epoch = 0;
+      stage_x<WT, BT>(cx, ph);
       stamp(step);
-      Best best[BT];
-#pragma unroll
-      for (int b = 0; b < BT; ++b) { best[b].v = -INFINITY; best[b].i = 0x7fffffff; }
-      consume_phase<WT, BT>(
-          rg, xs, p.V, H, cta, G, [&](int) { return 0.f; },
-          [&](int n, const float(&acc)[BT], float) {
-#pragma unroll
-            for (int b = 0; b < BT; ++b) {
-              best_merge(best[b], acc[b], n);
-              if (p.logits_out != nullptr && lane == 0 && b < B) p.logits_out[(size_t)b * p.V + n] = acc[b];
-            }
-          });
-      if (lane == 0) {
-#pragma unroll
-        for (int b = 0; b < BT; ++b) { sbv[warp * BT + b] = best[b].v; sbi[warp * BT + b] = best[b].i; }
-      }
+      run_rows<WT, BT>(cx, ph);
       consumer_sync();
-      if (tid < BT) {
+      // partials are laid out [b][value|index][cta] so that the readers' loads coalesce
+      if (tid < B) {
         Best r{sbv[tid], sbi[tid]};
         for (int ww = 1; ww < kNW; ++ww) best_merge(r, sbv[ww * BT + tid], sbi[ww * BT + tid]);
-        p.part_v[(size_t)cta * kGemvMaxBatch + tid] = r.v;
-        p.part_i[(size_t)cta * kGemvMaxBatch + tid] = r.i;
+        ll_store(p.part_ll + ((size_t)tid * 2 + 0) * kFlagStride + cta, r.v, ep + 6u);
+        ll_store_int(p.part_ll + ((size_t)tid * 2 + 1) * kFlagStride + cta, r.i, ep + 6u);
       }
       stamp(step);
-      grid_sync();
-      stamp(step);
-      // every CTA reduces the G partials (fixed order + index tie-break => deterministic), so
-      // every CTA knows the next token without another exchange
+      // publish, wait for every CTA's partials, then every CTA reduces them itself (index
+      // tie-break => deterministic): every CTA knows the next token without another exchange
+      stage_enter(ctr_of(6), cta, ctr_of(6), base_of(6), (uint32_t)step + 1u, G);
       for (int b = warp; b < B; b += kNW) {
         Best r{-INFINITY, 0x7fffffff};
-        for (int g = lane; g < G; g += 32)
-          best_merge(r, __ldcg(p.part_v + (size_t)g * kGemvMaxBatch + b), __ldcg(p.part_i + (size_t)g * kGemvMaxBatch + b));
+        for (int g0 = 0; g0 < G; g0 += 32) {
+          const int g = g0 + lane;
+          if (g < G) {
+            const float v = __uint_as_float(ll_wait_bits(p.part_ll + ((size_t)b * 2 + 0) * kFlagStride + g, ep + 6u));
+            const int i = (int)ll_wait_bits(p.part_ll + ((size_t)b * 2 + 1) * kFlagStride + g, ep + 6u);
+            best_merge(r, v, i);
+          }
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
           const float ov = __shfl_xor_sync(FULL_MASK, r.v, o);
@@ -646,23 +768,24 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
           best_merge(r, ov, oi);
         }
         if (lane == 0) {
-          s_ids[b] = r.i;
           if (cta == 0) {
             p.ids_out[b] = r.i;
             if (p.seq != nullptr) p.seq[(size_t)b * p.seq_stride + s_pos[b] + 1] = r.i;
           }
+          s_ids[b] = min(max(r.i, 0), p.V - 1);
         }
       }
+      stamp(step);
+    } else if (pub_ctr != nullptr) {
       consumer_sync();
+      if (tid == 0) ctr_bump(pub_ctr, cta);
     }
     // ---- bookkeeping: the cache grew by one position
     if (cta == 0 && tid < B) p.lens[p.slot0 + tid] = s_pos[tid] + 1;
     if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[step] = globaltimer();
     consumer_sync();
-    if (tid < B) s_pos[tid] += 1;
+    if (tid < B) s_pos[tid] = min(s_pos[tid] + 1, p.max_ctx - 1);
     consumer_sync();
-    // no barrier between steps: the argmax partial buffers are next written ~5L barriers from now
-    // and every CTA carries the token id in its own shared memory
   }
 }
 
@@ -680,18 +803,35 @@ int padded(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : 4); }
 
 size_t fixed_smem(int BT, int H, int L) {
   return (size_t)BT * 4 * H * 4 /*xs*/ + kNW * 64 * 4 /*part*/ + 2 * kNW * 4 /*pm,pl*/ + (size_t)2 * BT * kNW * 4 /*red*/ +
-         (size_t)kNW * BT * 8 /*sbv,sbi*/ + 64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + (size_t)L * sizeof(MegaLayer) + 128;
+         (size_t)2 * BT * kOwnMax * 4 /*hloc,h2loc*/ + 3 * 64 * 4 /*qkv_s*/ + (size_t)kNW * BT * 8 /*sbv,sbi*/ +
+         64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + 256 /*ctr base*/ + (size_t)L * sizeof(MegaLayer) + 128;
 }
 
 }  // namespace
 
-bool mega_supported(int B, int H, int nh, int L, int dtype) {
-  if (B < 1 || B > 4 || H % 8 != 0 || nh <= 0 || H / nh != 64 || H % nh != 0 || H > kLnPer * kConsumers) return false;
+bool mega_supported(int B, int H, int nh, int L, int dtype, int num_sms) {
+  if (B < 1 || B > 4 || H % 8 != 0 || nh <= 0 || H % nh != 0 || H / nh != 64) return false;
+  if (H > kLnPer * kConsumers || 4 * H > kCopyPer * kConsumers) return false;
+  if (num_sms < 1 || num_sms > kFlagStride || B * nh > kFlagStride) return false;
+  if ((H + num_sms - 1) / num_sms + 1 > kOwnMax) return false;   // residual rows per CTA
   const size_t fixed = fixed_smem(padded(B), H, L);
   if (fixed + 2 * (size_t)kSlotBytes > 227 * 1024) return false;
   // one row of the widest matrix (K = 4H) must fit a slot
-  return (size_t)4 * H * (dtype == GP_BF16 ? 2 : 4) <= (size_t)kSlotBytes;
+  return (size_t)4 * H * (dtype == GP_BF16 ? 2 : 4) <= (size_t)kSlotData;
 }
+
+uint32_t mega_epochs_per_launch(int L, int n_steps) { return (uint32_t)n_steps * (uint32_t)(L + 1) * 8u + 8u; }
+size_t mega_flag_words() { return (size_t)8 * kCtrWords; }
+// counter values after a launch: what the next launch must pass as ctr_base (host mirror of ctr_bump)
+void mega_advance_counters(uint32_t* base /*[8][8]*/, int L, int n_steps, int B, int nh, int grid, int has_head) {
+  auto add = [&](int id, int n_prod, uint32_t rounds) {
+    for (int j = 0; j < kSub; ++j) base[id * kSub + j] += rounds * (uint32_t)((n_prod - j + kSub - 1) / kSub);
+  };
+  const uint32_t r = (uint32_t)n_steps * (uint32_t)L;
+  add(1, grid, r); add(2, B * nh, r); add(3, grid, r); add(4, grid, r); add(5, grid, r);
+  if (has_head) add(6, grid, (uint32_t)n_steps);
+}
+size_t mega_part_words() { return (size_t)kGemvMaxBatch * 2 * kFlagStride; }
 
 cudaError_t init_mega_attrs() {
   cudaError_t e;
@@ -702,15 +842,15 @@ cudaError_t init_mega_attrs() {
 }
 
 cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_t s) {
-  if (!mega_supported(p.B, p.H, p.nh, p.L, dtype) || p.n_steps < 1 || p.bar == nullptr) return cudaErrorInvalidValue;
+  if (!mega_supported(p.B, p.H, p.nh, p.L, dtype, num_sms) || p.n_steps < 1 || p.epoch0 == 0 || p.flags == nullptr)
+    return cudaErrorInvalidValue;
   const int BT = padded(p.B);
   const size_t fixed = fixed_smem(BT, p.H, p.L);
   int n_slots = (int)((227 * 1024 - fixed) / kSlotBytes);
   if (n_slots > kMaxSlots) n_slots = kMaxSlots;
+  if (const char* env = getenv("GP_MEGA_SLOTS")) { int v = atoi(env); if (v >= 2 && v < n_slots) n_slots = v; }
   p.n_slots = n_slots;
   const size_t smem = fixed + (size_t)n_slots * kSlotBytes;
-  cudaError_t e = cudaMemsetAsync(p.bar, 0, sizeof(unsigned), s);
-  if (e != cudaSuccess) return e;
   const int grid = num_sms;
   if (dtype == GP_BF16) {
     if (BT == 1) return launch_t<bf16, 1>(p, grid, smem, s);
