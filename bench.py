@@ -35,6 +35,9 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "gpt2-124m-b1-p32-n128"
 METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
+# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu --set full
+# capture (profiles/), per launch; None until a capture of the current kernel exists
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 31882981888  # profiles/r01_ncu_full_summary.txt: 31.869943 GB read + 13.04 MB written
 
 
 def synthetic_prompts(B, P, vocab, seed=7):
@@ -110,25 +113,32 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------
-def cpu_reference_tokens_per_s(preset, seed, B, P, n_tokens, full_path_probe=False):
+_REF_WEIGHTS = {}
+
+
+def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_probe=False):
     """The reference's path on the host cores: full recompute of Shard A then Shard B per token
-    (server.py:169-206) via the oracle port, compute only (no HTTP/JSON).  Returns
-    (tokens/s, p50 s/token, info)."""
+    (server.py:169-206) via the oracle port, compute only (no HTTP/JSON).  The reference's cost per
+    token grows with the sequence, so `n_samples` steps evenly spread over the n_new-token run are
+    timed (each one token at its true sequence length) and averaged.  Returns (tokens/s, p50 s/token, info)."""
     from oracle import gpt2_oracle as O
     dims = O.PRESETS[preset]
-    w = O.init_weights(dims, seed, "hf")
-    ids = synthetic_prompts(B, P, dims.vocab_size).long()
+    key = (preset, seed)
+    if key not in _REF_WEIGHTS:
+        _REF_WEIGHTS[key] = O.init_weights(dims, seed, "hf")
+    w = _REF_WEIGHTS[key]
     split = O.split_layers(dims.n_layer, 2)[0][1]
     lat = []
+    steps = sorted(set(int(round(i * (n_new - 1) / max(1, n_samples - 1))) for i in range(n_samples)))
     with torch.no_grad():
-        for _ in range(n_tokens):
+        for t in steps:
+            ids = synthetic_prompts(B, P + t, dims.vocab_size, seed=7 + t).long()
             t0 = time.perf_counter()
             hidden = O.shard_a_forward(w, dims, ids, split)
             logits = O.shard_b_forward(w, dims, hidden, split)
-            nxt = O.greedy_select(logits[:, -1])
-            ids = torch.cat([ids, nxt.unsqueeze(1)], dim=1)
+            O.greedy_select(logits[:, -1])
             lat.append(time.perf_counter() - t0)
-    info = {}
+    info = {"sampled_steps": steps}
     if full_path_probe:
         # one token of the reference's real wire format: hidden and ALL-position logits as JSON
         t0 = time.perf_counter()
@@ -138,8 +148,7 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_tokens, full_path_probe=Fal
         _ = json.loads(l_json)["logits"][0][-1]
         info["json_overhead_s_per_token"] = round(time.perf_counter() - t0, 3)
         info["json_T"] = int(hidden2.shape[1])
-    total = sum(lat)
-    return B * n_tokens / total, statistics.median(lat), info
+    return B * len(lat) / sum(lat), statistics.median(lat), info
 
 
 def run_reference(args):
@@ -151,12 +160,12 @@ def run_reference(args):
     cores = torch.get_num_threads()
     sample = min(n_new, 8)
     for _ in range(args.warmup):
-        cpu_reference_tokens_per_s(preset, seed, B, P, 2)
+        cpu_reference_tokens_per_s(preset, seed, B, P, n_new, 2)
     vals, lats = [], []
     t_all = time.perf_counter()
     info = {}
     for i in range(args.steps):
-        v, p50, inf = cpu_reference_tokens_per_s(preset, seed, B, P, sample, full_path_probe=(i == 0))
+        v, p50, inf = cpu_reference_tokens_per_s(preset, seed, B, P, n_new, sample, full_path_probe=(i == 0))
         info.update(inf)
         vals.append(v)
         lats.append(p50)
@@ -169,7 +178,8 @@ def run_reference(args):
         "config": {"workload": args.workload, "model": preset, "batch": B, "prompt": P, "new_tokens": n_new},
         "p50_token_ms": round(1000 * statistics.median(lats), 3),
         "cpu_baseline": {"value": round(value, 3), "unit": "tokens/s", "cores": cores, "kind": "port",
-                         "sample": f"first {sample} of {n_new} new tokens per step, full recompute of both shards "
+                         "sample": f"{sample} of the {n_new} decode steps per bench step, evenly spread over the run, "
+                                   f"each one token at its true sequence length; full recompute of both shards "
                                    f"per token (server.py:169-181), compute only (no HTTP/JSON); {info}"},
         "e2e": {"value": round(value, 3), "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -204,10 +214,11 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     # --- device-timed steps (value)
-    dev_ms, step_tok_ms, launches = [], [], 0
+    dev_ms, step_tok_ms, launches, decode_ms = [], [], 0, []
     for _ in range(args.steps):
         out, tm = runner.generate(prompts, n_new, timings=True)
         dev_ms.append(tm["prefill_ms"] + tm["decode_ms"])
+        decode_ms.append(tm["decode_ms"])
         step_tok_ms += tm["step_ms"]
         launches += tm["launches"]
     runner.barrier()
@@ -230,28 +241,45 @@ def run_b200(args):
     e2e = tokens_per_step * args.steps / e2e_s
     p50_tok_ms = statistics.median(step_tok_ms) if step_tok_ms else None
 
-    # roofline of the decode step (HBM-bound): algorithmic bytes per step / measured step time
+    # roofline of the dominant kernel.  world == 1: decode_mega_kernel, ONE launch per request that runs
+    # all n_new-1 decode steps; its duration is the CUDA-event time between the end of the prefill and the
+    # end of the loop on the engine's stream (gp_generate's own events), its algorithmic bytes are
+    # (n_new-1) x the per-step figure of SURVEY.md 8(d) at the mean context of the run.
+    # world > 1: the same kernel runs one step per launch on every stage; per-stage bytes / per-stage time.
     peak, peak_kind = measured_peaks()
+    esz = 2 if dtype == L.GP_BF16 else 4
     t_ctx = P + n_new // 2
-    bytes_step = algorithmic_bytes_per_step(dims, B, t_ctx, world, 2 if dtype == L.GP_BF16 else 4)
+    bytes_step = algorithmic_bytes_per_step(dims, B, t_ctx, world, esz)
     roof = None
-    if p50_tok_ms:
-        per_stage_bytes = bytes_step / world
-        achieved = per_stage_bytes / (p50_tok_ms / 1000.0 / world) / 1e9 if world > 1 else bytes_step / (p50_tok_ms / 1000.0) / 1e9
-        roof = {"bound": "hbm", "kernel": "decode step (all launches of one token; dominated by gemv_kernel + lmhead_argmax_kernel)",
-                "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": None,
-                "algorithmic_bytes_per_launch": int(bytes_step)}
+    decode_ms_mean = statistics.mean(decode_ms) if decode_ms else None
+    if decode_ms_mean and n_new > 1:
+        if world == 1:
+            bytes_launch = bytes_step * (n_new - 1)
+            achieved = bytes_launch / (decode_ms_mean / 1000.0) / 1e9
+            kern = "decode_mega_kernel<bf16,1> (persistent, %d decode steps per launch)" % (n_new - 1)
+        else:
+            bytes_launch = bytes_step / world
+            achieved = bytes_launch / (p50_tok_ms / 1000.0 / n_streams) / 1e9 if p50_tok_ms else 0.0
+            kern = "decode_mega_kernel<bf16,1> (one step of one stage per launch)"
+        roof = {"bound": "hbm", "kernel": kern, "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH,
+                "algorithmic_bytes_per_launch": int(bytes_launch),
+                "note": "batch-1 decode of a 124M model is latency-bound (about 60 dependent phases per token); see DESIGN.md"}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
         sample = 16
-        v, p50, info = cpu_reference_tokens_per_s(preset, seed, B, P, sample)
+        v, p50, info = cpu_reference_tokens_per_s(preset, seed, B, P, n_new, sample, full_path_probe=True)
         cpu = {"value": round(v, 3), "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
-               "sample": f"first {sample} of {n_new} new tokens of the same prompt, full recompute per token, "
-                         f"compute only (no HTTP/JSON), p50 {1000 * p50:.1f} ms/token"}
+               "sample": f"{sample} of the {n_new} decode steps evenly spread over the run, each one token at its true "
+                         f"sequence length, full recompute per token, compute only (no HTTP/JSON), p50 "
+                         f"{1000 * p50:.1f} ms/token; the reference's JSON wire format would add "
+                         f"{info.get('json_overhead_s_per_token')} s per token at T={info.get('json_T')}"}
 
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(dev_total_ms / args.steps, 4), "higher_is_better": True,
@@ -285,6 +313,12 @@ def main():
         run_reference(args)
     else:
         run_b200(args)
+    try:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
 
 
 if __name__ == "__main__":

@@ -208,6 +208,10 @@ template <typename WT> struct Ctx {
   float *xs, *red, *hloc, *h2loc, *sbv; int* sbi; int *s_ids, *s_pos;
   const WT *wte, *wpe;
   int B, H, V, n_pos, G, cta, c0; float eps; float* logits_out;
+  long long* trace; int trace_cap; int n_stamp; bool tracing;   // debug: per-CTA clock64 stamps (thread 0)
+  __device__ __forceinline__ void stamp() {
+    if (tracing && threadIdx.x == 0 && n_stamp < trace_cap) trace[n_stamp++] = clock64();
+  }
 };
 
 template <typename WT>
@@ -245,6 +249,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
   if (ph.ln_g == nullptr) {
     stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
                 ph.src_nprod);
+    cx.stamp();
 #pragma unroll
     for (int b = 0; b < BT; ++b) {
       if (b >= B) {
@@ -270,6 +275,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
           }
       }
     }
+    cx.stamp();
     consumer_sync();
     return;
   }
@@ -282,6 +288,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
   }
   stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
               ph.src_nprod);
+  cx.stamp();
   unsigned pending = 0;
 #pragma unroll
   for (int i = 0; i < kLnPer; ++i) {
@@ -301,6 +308,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
           if (fetch_x(cx, ph, b, tid + i * kConsumers, v[b][i])) pending &= ~(1u << (b * kLnPer + i));
         }
   }
+  cx.stamp();
   float* redA = cx.red;             // [BT][kNW]
   float* redB = cx.red + BT * kNW;  // [BT][kNW]
 #pragma unroll
@@ -374,6 +382,7 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
     const uint8_t* slot = rg.slots + (size_t)s * kSlotBytes;
     if (lane == 0) mbar_wait(&rg.full[s], phs);   // one waiter per warp
     __syncwarp();
+    if (r == r0) cx.stamp();
     for (int rr = warp; rr < n; rr += kNW) {
       const WT* wrow = reinterpret_cast<const WT*>(slot + (size_t)rr * rowbytes);
       float acc[BT];
@@ -489,6 +498,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
     pv1.load(Vc + (size_t)(grp + kGroups) * D + l8 * 8);
   }
   stage_enter(pub_ctr, cx.cta, a.ctr_qkv, a.base_qkv, a.rounds, cx.G);
+  cx.stamp();
   // q, k_new, v_new of this head: 192 values, one per thread, into shared memory
   if (tid < 3 * D) {
     const int which = tid / D, i = tid - which * D;
@@ -503,6 +513,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
     }
   }
   consumer_sync();
+  cx.stamp();
   float qv[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) qv[i] = a.qkv_s[l8 * 8 + i];
@@ -540,6 +551,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
     st.m = mn;
   }
   __syncwarp();
+  cx.stamp();
   // merge the four groups of the warp, then the 15 warps through shared memory
 #pragma unroll
   for (int o = 8; o <= 16; o <<= 1) {
@@ -635,10 +647,12 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
 
   // ================================= CONSUMERS =================================
   // optional phase trace (GP_MEGA_TRACE): every CTA records %globaltimer (ns, one clock for the whole GPU)
-  int n_stamp = 0;
+  Ctx<WT> cx;
+  cx.trace = p.trace ? p.trace + (size_t)cta * p.trace_cap : nullptr; cx.trace_cap = p.trace_cap; cx.n_stamp = 0;
+  cx.tracing = false;
   auto stamp = [&](int step) {
-    if (p.trace != nullptr && tid == 0 && step == p.n_steps - 1 && n_stamp < p.trace_cap)
-      p.trace[(size_t)cta * p.trace_cap + n_stamp++] = (long long)globaltimer();
+    cx.tracing = (p.trace != nullptr && step == p.n_steps - 1);
+    cx.stamp();
   };
   if (tid < 8) {
     s_pos[tid] = (tid < B) ? min(p.lens[p.slot0 + tid], p.max_ctx - 1) : 0;
@@ -647,7 +661,6 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[p.n_steps] = globaltimer();  // start stamp
   consumer_sync();
 
-  Ctx<WT> cx;
   cx.rg = Ring{ring_base, full, empty, p.n_slots, 0u};
   cx.xs = xs; cx.red = red; cx.hloc = hloc; cx.h2loc = h2loc; cx.sbv = sbv; cx.sbi = sbi; cx.s_ids = s_ids; cx.s_pos = s_pos;
   cx.wte = reinterpret_cast<const WT*>(p.wte); cx.wpe = reinterpret_cast<const WT*>(p.wpe);
