@@ -277,9 +277,6 @@ def run_b200(args):
                          f"{1000 * p50:.1f} ms/token; the reference's JSON wire format would add "
                          f"{info.get('json_overhead_s_per_token')} s per token at T={info.get('json_T')}"}
 
-    if world > 1:
-        import torch.distributed as dist
-        dist.barrier()
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(dev_total_ms / args.steps, 4), "higher_is_better": True,

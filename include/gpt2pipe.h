@@ -131,6 +131,26 @@ int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, in
 int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t P, int32_t n_new,
                 int32_t* out_ids_host, float* timings_ms_host);
 
+/* ---- stage boundary on the device (replaces the HTTP/JSON hops of server.py:172-181).
+ * One process per GPU.  Every stage owns an "inbox" in its HBM; the stage before it writes the
+ * hidden state of each decode step straight into that inbox over NVLink (the last stage writes
+ * the next token ids into stage 0's inbox), every fp32 / int32 value travelling in one 64-bit
+ * word together with the round number, so the receiving kernel polls its own memory and no
+ * host, NCCL call or fence is involved per token.
+ *   gp_comm_export : creates the inbox and returns its 64-byte cudaIpcMemHandle_t
+ *   gp_comm_connect: maps the inbox of the stage this one feeds ((rank+1) % stages)
+ *   gp_pipeline_decode: ONE persistent launch per stage runs n_rounds decode steps of n_streams
+ *     micro-batches (B sequences each, KV slots [m*B,(m+1)*B)); call it on every stage at the same
+ *     time.  comm_epoch0 must be the same on all stages and larger than any used before
+ *     (previous comm_epoch0 + n_rounds).  Stage 0: first_ids int32 [n_streams*B] (tokens the
+ *     prefill produced) -> tokens_out int32 [n_streams*B, n_rounds].  Returns GP_ECUDA if the
+ *     kernel has not finished after timeout_ms (a peer is missing). */
+int gp_comm_export(gp_engine* e, void* handle_host);
+int gp_comm_connect(gp_engine* e, const void* peer_handle_host);
+int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds, int32_t n_streams, int32_t B,
+                       uint32_t comm_epoch0, int32_t* tokens_out, int32_t timeout_ms, float* ms_host,
+                       void* stream);
+
 /* Number of kernel launches the last gp_stage_prefill / gp_stage_decode / gp_generate
  * issued (graph replays count the kernels inside the graph). */
 int64_t gp_last_launch_count(const gp_engine* e);

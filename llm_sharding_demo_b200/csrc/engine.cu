@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <map>
 #include <set>
 #include <string>
@@ -64,6 +65,10 @@ struct gp_engine {
   unsigned long long* part_ll = nullptr;
   uint32_t* mega_flags = nullptr;
   uint32_t mega_ctr[64] = {0};   // host mirror of the device "published" counters
+  // pipeline stage boundary: this stage's inbox (peers write into it) and the mapped inbox of the peer it feeds
+  unsigned char* inbox = nullptr;       // [1024 B ids words][64*H hidden words]
+  unsigned char* peer_inbox = nullptr;  // next stage's inbox (stage 0's for the last stage), cudaIpcOpenMemHandle
+  bool peer_is_ipc = false;
   uint32_t mega_epoch = 8;
   unsigned long long* step_clock = nullptr;
   bool mega_uploaded = false;
@@ -173,8 +178,14 @@ int upload_mega_layers(gp_engine* e) {
 }
 
 // one launch = n_steps cached decode steps of this stage (n_steps > 1 only for single-stage engines)
+struct PipeArgs {
+  int n_streams = 1; uint32_t comm_epoch0 = 0; int32_t* tok_out = nullptr; int tok_stride = 0; bool on = false;
+};
+size_t inbox_bytes(const gp_engine* e) { return 1024 + (size_t)64 * e->H * 8; }
+
 int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B, int slot0, float* hidden_out,
-                float* logits, int32_t* next_ids, int32_t* seq, int n_steps, bool clock, cudaStream_t s) {
+                float* logits, int32_t* next_ids, int32_t* seq, int n_steps, bool clock, cudaStream_t s,
+                const PipeArgs& pipe = PipeArgs()) {
   int r = upload_mega_layers(e);
   if (r != GP_OK) return r;
   const gp_config& c = e->cfg;
@@ -185,7 +196,15 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   p.hidden_out = hidden_out; p.lens = e->lens; p.qkv_ll = e->qkv_ll; p.attn_ll = e->attn_ll; p.h2_ll = e->h2_ll;
   p.act_ll = e->act_ll; p.h_ll = e->h_ll; p.part_ll = e->part_ll; p.flags = e->mega_flags; p.ids_out = next_ids ? next_ids : e->mailbox;
   p.seq = seq; p.seq_stride = e->seq_stride; p.logits_out = logits; p.n_steps = n_steps;
-  const uint32_t span = mega_epochs_per_launch(e->L, n_steps);
+  p.n_streams = pipe.n_streams;
+  if (pipe.on) {
+    p.comm_epoch0 = pipe.comm_epoch0; p.tok_out = pipe.tok_out; p.tok_stride = pipe.tok_stride;
+    if (c.has_embed) p.inbox_ids = reinterpret_cast<const unsigned long long*>(e->inbox);
+    else p.inbox_hid = reinterpret_cast<const unsigned long long*>(e->inbox + 1024);
+    if (c.has_head) p.peer_ids = reinterpret_cast<unsigned long long*>(e->peer_inbox);
+    else p.peer_hid = reinterpret_cast<unsigned long long*>(e->peer_inbox + 1024);
+  }
+  const uint32_t span = mega_epochs_per_launch(e->L, n_steps * pipe.n_streams);
   if (e->mega_epoch > 0xFFFFFFFFu - span - 8u) {
     // epoch counter about to wrap: start over on zeroed exchange buffers
     const size_t MBx = c.max_batch;
@@ -199,7 +218,7 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   p.epoch0 = e->mega_epoch;
   e->mega_epoch += span;
   memcpy(p.ctr_base, e->mega_ctr, sizeof(p.ctr_base));
-  mega_advance_counters(e->mega_ctr, e->L, n_steps, B, e->nh, e->num_sms, c.has_head);
+  mega_advance_counters(e->mega_ctr, e->L, n_steps * pipe.n_streams, B, e->nh, e->num_sms, c.has_head);
   p.step_clock = clock ? e->step_clock : nullptr;
   const char* trace_path = getenv("GP_MEGA_TRACE");
   const bool trace = trace_path != nullptr && n_steps > 1;
@@ -474,7 +493,7 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRY(alloc((void**)&e->h_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->h_ll, 0, MB * H * 8, e->stream));
   TRY(alloc((void**)&e->part_ll, mega_part_words() * 8)); TRYCK(cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, e->stream));
   TRY(alloc((void**)&e->mega_flags, mega_flag_words() * 4)); TRYCK(cudaMemsetAsync(e->mega_flags, 0, mega_flag_words() * 4, e->stream));
-  TRY(alloc((void**)&e->step_clock, (size_t)(cfg->n_positions + 2) * sizeof(unsigned long long)));
+  TRY(alloc((void**)&e->step_clock, (size_t)(cfg->n_positions + 2) * 64 * sizeof(unsigned long long)));
   TRYCK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
   if (e->num_sms > 1024) e->num_sms = 1024;
   TRYCK(init_mega_attrs());
@@ -494,6 +513,8 @@ int gp_engine_destroy(gp_engine* e) {
   for (void* p : e->allocs) cudaFree(p);
   if (e->stage) cudaFree(e->stage);
   if (e->trace) cudaFree(e->trace);
+  if (e->peer_inbox && e->peer_is_ipc) cudaIpcCloseMemHandle(e->peer_inbox);
+  if (e->inbox) cudaFree(e->inbox);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return GP_OK;
@@ -701,6 +722,81 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
       }
     }
   }
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------- pipeline stage boundary
+int gp_comm_export(gp_engine* e, void* handle_host) {
+  if (!e || !handle_host) { set_err(e, "gp_comm_export: NULL argument"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(e->cfg.device));
+  if (!e->inbox) {
+    CK(e, cudaMalloc((void**)&e->inbox, inbox_bytes(e)));
+    CK(e, cudaMemset(e->inbox, 0, inbox_bytes(e)));
+    CK(e, cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t h;
+  CK(e, cudaIpcGetMemHandle(&h, e->inbox));
+  memcpy(handle_host, &h, sizeof h);
+  return GP_OK;
+}
+
+int gp_comm_connect(gp_engine* e, const void* peer_handle_host) {
+  if (!e || !peer_handle_host) { set_err(e, "gp_comm_connect: NULL argument"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(e->cfg.device));
+  if (e->peer_inbox && e->peer_is_ipc) { cudaIpcCloseMemHandle(e->peer_inbox); e->peer_inbox = nullptr; }
+  cudaIpcMemHandle_t h;
+  memcpy(&h, peer_handle_host, sizeof h);
+  void* ptr = nullptr;
+  CK(e, cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  e->peer_inbox = reinterpret_cast<unsigned char*>(ptr);
+  e->peer_is_ipc = true;
+  return GP_OK;
+}
+
+int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds, int32_t n_streams, int32_t B,
+                       uint32_t comm_epoch0, int32_t* tokens_out, int32_t timeout_ms, float* ms_host, void* stream) {
+  if (!e) return GP_EINVAL;
+  const gp_config& c = e->cfg;
+  if (c.has_embed && c.has_head) { set_err(e, "gp_pipeline_decode is for multi-stage pipelines; use gp_generate on a single stage"); return GP_EINVAL; }
+  if (n_rounds < 1 || n_streams < 1 || B < 1 || n_streams * B > 64 || n_streams * B > c.max_batch || comm_epoch0 == 0) {
+    set_err(e, "gp_pipeline_decode: bad n_rounds/n_streams/B (%d,%d,%d) for max_batch %d", n_rounds, n_streams, B, c.max_batch);
+    return GP_EINVAL;
+  }
+  if (!e->inbox || !e->peer_inbox) { set_err(e, "gp_pipeline_decode: stage boundary not connected (gp_comm_export / gp_comm_connect)"); return GP_ESTATE; }
+  if (c.has_embed && (!first_ids || !tokens_out)) { set_err(e, "gp_pipeline_decode: stage 0 needs first_ids and tokens_out"); return GP_EINVAL; }
+  if (!use_mega(e, B)) { set_err(e, "gp_pipeline_decode: shape outside the persistent kernel's envelope (B<=4, head_dim 64)"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(c.device));
+  int r = check_ready(e);
+  if (r != GP_OK) return r;
+  cudaStream_t s = (cudaStream_t)stream;
+  e->launches = 0;
+  while ((int)e->events.size() < 2) {
+    cudaEvent_t ev;
+    CK(e, cudaEventCreate(&ev));
+    e->events.push_back(ev);
+  }
+  PipeArgs pa;
+  pa.on = true; pa.n_streams = n_streams; pa.comm_epoch0 = comm_epoch0; pa.tok_out = tokens_out; pa.tok_stride = n_rounds;
+  CK(e, cudaEventRecord(e->events[0], s));
+  r = decode_mega(e, first_ids, nullptr, B, 0, nullptr, nullptr, nullptr, nullptr, n_rounds, false, s, pa);
+  if (r != GP_OK) return r;
+  CK(e, cudaEventRecord(e->events[1], s));
+  // host watchdog: the kernel waits on other GPUs; if a peer never shows up report it instead of hanging forever
+  const double t0 = (double)clock() / CLOCKS_PER_SEC;
+  struct timespec ts0; clock_gettime(CLOCK_MONOTONIC, &ts0);
+  for (;;) {
+    cudaError_t q = cudaEventQuery(e->events[1]);
+    if (q == cudaSuccess) break;
+    if (q != cudaErrorNotReady) { CK(e, q); }
+    struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
+    const double el = (ts.tv_sec - ts0.tv_sec) * 1e3 + (ts.tv_nsec - ts0.tv_nsec) * 1e-6;
+    if (timeout_ms > 0 && el > timeout_ms) {
+      set_err(e, "gp_pipeline_decode: no progress after %d ms (a peer stage is missing); the kernel is still spinning - terminate the process", timeout_ms);
+      return GP_ECUDA;
+    }
+  }
+  (void)t0;
+  if (ms_host) CK(e, cudaEventElapsedTime(ms_host, e->events[0], e->events[1]));
   return GP_OK;
 }
 

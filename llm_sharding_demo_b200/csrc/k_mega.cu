@@ -98,6 +98,18 @@ __device__ __forceinline__ u64 ll_load(const u64* p) {
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
   return w;
 }
+// system scope: words another GPU writes into this GPU's inbox over NVLink (and our writes into a peer's)
+__device__ __forceinline__ void ll_store_sys(u64* p, uint32_t bits, uint32_t epoch) {
+  const u64 w = ((u64)epoch << 32) | (u64)bits;
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ uint32_t ll_wait_sys(const u64* p, uint32_t epoch) {
+  u64 w;
+  do {
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+  } while ((uint32_t)(w >> 32) != epoch);
+  return (uint32_t)w;
+}
 __device__ __forceinline__ uint32_t ll_wait_bits(const u64* p, uint32_t epoch) {
   u64 w = ll_load(p);
   while ((uint32_t)(w >> 32) != epoch) w = ll_load(p);
@@ -201,6 +213,8 @@ struct Phase {
   // ---- rows
   int N; int has_bias; int mode;
   u64* dst_ll; float* dst_plain; uint32_t dst_epoch;
+  int dst_sys;                                       // dst_ll is a peer GPU's inbox: system-scope stores
+  const u64* sentinel; uint32_t sentinel_epoch;      // inbox input: one word thread 0 watches before all poll
 };
 
 template <typename WT> struct Ctx {
@@ -217,7 +231,9 @@ template <typename WT> struct Ctx {
 template <typename WT>
 __device__ __forceinline__ bool fetch_x(const Ctx<WT>& cx, const Phase& ph, int b, int k, float& v) {
   if (ph.src_kind == SRC_LL) {
-    const u64 w = ll_load(ph.src_ll + (size_t)b * ph.K + k);
+    u64 w;
+    if (ph.sentinel != nullptr) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(ph.src_ll + (size_t)b * ph.K + k) : "memory");
+    else w = ll_load(ph.src_ll + (size_t)b * ph.K + k);
     v = __uint_as_float((uint32_t)w);
     return (uint32_t)(w >> 32) == ph.src_epoch;
   }
@@ -231,10 +247,12 @@ __device__ __forceinline__ bool fetch_x(const Ctx<WT>& cx, const Phase& ph, int 
 
 // barrier (previous phase fully done in this CTA) -> publish it -> wait for this phase's producers
 __device__ __forceinline__ void stage_enter(uint32_t* pub_ctr, int pub_idx, const uint32_t* ctr, const uint32_t* base,
-                                         uint32_t rounds, int n_prod) {
+                                         uint32_t rounds, int n_prod, const u64* sentinel = nullptr,
+                                         uint32_t sentinel_epoch = 0) {
   consumer_sync();
   if (threadIdx.x == 0 && pub_ctr != nullptr) ctr_bump(pub_ctr, pub_idx);
   gate_ctr(ctr, base, rounds, n_prod);
+  if (sentinel != nullptr && threadIdx.x == 0) ll_wait_sys(sentinel, sentinel_epoch);   // previous pipeline stage
   consumer_sync();
 }
 
@@ -248,7 +266,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
   float* xs = cx.xs;
   if (ph.ln_g == nullptr) {
     stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
-                ph.src_nprod);
+                ph.src_nprod, ph.sentinel, ph.sentinel_epoch);
     cx.stamp();
 #pragma unroll
     for (int b = 0; b < BT; ++b) {
@@ -287,7 +305,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
     bb[i] = (k < K) ? ph.ln_b[k] : 0.f;
   }
   stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
-              ph.src_nprod);
+              ph.src_nprod, ph.sentinel, ph.sentinel_epoch);
   cx.stamp();
   unsigned pending = 0;
 #pragma unroll
@@ -422,6 +440,7 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
         else if (ph.mode == EPI_FC) v = gelu_new(v);
         else if (ph.mode == EPI_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
         if (ph.dst_plain != nullptr) ph.dst_plain[(size_t)lane * ph.N + row] = v;
+        else if (ph.dst_sys) ll_store_sys(ph.dst_ll + (size_t)lane * ph.N + row, __float_as_uint(v), ph.dst_epoch);
         else ll_store(ph.dst_ll + (size_t)lane * ph.N + row, v, ph.dst_epoch);
       }
     }
@@ -607,7 +626,8 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   uint64_t* full = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(s_pos + 8) + 15) & ~(uintptr_t)15);
   uint64_t* empty = full + kMaxSlots;
   uint32_t* s_base = reinterpret_cast<uint32_t*>(empty + kMaxSlots);            // [64] counter values at launch
-  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_base + 64);              // [L]
+  int* s_pos0 = reinterpret_cast<int*>(s_base + 64);                            // [64] cache lengths at launch
+  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_pos0 + 64);              // [L]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
@@ -631,7 +651,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
     // =============================== PRODUCER ===============================
     if (lane == 0) {
       Ring rg{ring_base, full, empty, p.n_slots, 0u};
-      for (int step = 0; step < p.n_steps; ++step) {
+      for (int step = 0; step < p.n_steps * p.n_streams; ++step) {
         for (int li = 0; li < p.L; ++li) {
           const MegaLayer& w = s_layers[li];
           produce_phase<WT>(rg, w.attn_w, w.attn_b, 3 * H, H, cta, G);
@@ -650,15 +670,14 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   Ctx<WT> cx;
   cx.trace = p.trace ? p.trace + (size_t)cta * p.trace_cap : nullptr; cx.trace_cap = p.trace_cap; cx.n_stamp = 0;
   cx.tracing = false;
+  const int n_items = p.n_steps * p.n_streams;   // item = (round, stream); one decode step of B sequences each
   auto stamp = [&](int step) {
-    cx.tracing = (p.trace != nullptr && step == p.n_steps - 1);
+    cx.tracing = (p.trace != nullptr && step == n_items - 1);
     cx.stamp();
   };
-  if (tid < 8) {
-    s_pos[tid] = (tid < B) ? min(p.lens[p.slot0 + tid], p.max_ctx - 1) : 0;
-    s_ids[tid] = (tid < B && p.has_embed) ? min(max(__ldcg(p.ids + tid), 0), p.V - 1) : 0;
-  }
-  if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[p.n_steps] = globaltimer();  // start stamp
+  if (tid < 64) s_pos0[tid] = (tid < p.n_streams * B) ? p.lens[p.slot0 + tid] : 0;
+  if (tid < 8) { s_pos[tid] = 0; s_ids[tid] = 0; }
+  if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[n_items] = globaltimer();  // start stamp
   consumer_sync();
 
   cx.rg = Ring{ring_base, full, empty, p.n_slots, 0u};
@@ -673,14 +692,36 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   auto ctr_of = [&](int id) { return p.flags + id * kCtrWords; };
   auto base_of = [&](int id) { return s_base + id * kSub; };
 
-  for (int step = 0; step < p.n_steps; ++step) {
+  for (int step = 0; step < n_items; ++step) {
+    const int round = step / p.n_streams, strm = step - round * p.n_streams;
+    const int slot_base = p.slot0 + strm * B;
+    const uint32_t cep = p.comm_epoch0 + (uint32_t)round;   // epoch of this item's words on the stage boundary
     const uint32_t ep_step = p.epoch0 + (uint32_t)step * (uint32_t)(p.L + 1) * 8u;
+    const u64* in_hid = p.inbox_hid ? p.inbox_hid + (size_t)strm * B * H : nullptr;
+    // ---- position and (stage 0) token of every sequence of this item
+    if (tid < B) {
+      s_pos[tid] = min(s_pos0[strm * B + tid] + round, p.max_ctx - 1);
+      if (p.has_embed) {
+        int id = s_ids[tid];   // single-stage loop: this CTA's own argmax of the previous step
+        if (p.inbox_ids != nullptr && round > 0) {
+          // pipeline: the token the last stage produced for this stream in the previous round
+          id = (int)ll_wait_sys(p.inbox_ids + strm * B + tid, cep - 1u);
+          if (cta == 0 && p.tok_out != nullptr) p.tok_out[(size_t)(strm * B + tid) * p.tok_stride + (round - 1)] = id;
+        } else if (round == 0) {
+          id = __ldcg(p.ids + strm * B + tid);
+        }
+        s_ids[tid] = min(max(id, 0), p.V - 1);
+      }
+    }
+    consumer_sync();
     // ---- the residual slice this CTA owns: embedding rows (stage 0) or the incoming hidden state
     for (int i = tid; i < B * (c1 - c0); i += kConsumers) {
       const int b = i / (c1 - c0), col = c0 + i % (c1 - c0);
-      hloc[b * kOwnMax + (col - c0)] =
-          p.has_embed ? to_f(cx.wte[(size_t)s_ids[b] * H + col]) + to_f(cx.wpe[(size_t)min(s_pos[b], p.n_pos - 1) * H + col])
-                      : __ldcg(p.hidden_in + (size_t)b * H + col);
+      float hv;
+      if (p.has_embed) hv = to_f(cx.wte[(size_t)s_ids[b] * H + col]) + to_f(cx.wpe[(size_t)min(s_pos[b], p.n_pos - 1) * H + col]);
+      else if (in_hid != nullptr) hv = __uint_as_float(ll_wait_sys(in_hid + (size_t)b * H + col, cep));
+      else hv = __ldcg(p.hidden_in + (size_t)b * H + col);
+      hloc[b * kOwnMax + (col - c0)] = hv;
     }
     stamp(step);
     uint32_t* pub_ctr = nullptr;   // counter block the next stage has to bump for the phase before it
@@ -689,11 +730,18 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       const bool last = (li == p.L - 1);
       const uint32_t ep = ep_step + (uint32_t)li * 8u;         // +1 qkv, +2 attn, +3 h2, +4 act, +5 h
       const uint32_t rnd = (uint32_t)(step * p.L + li) + 1u;   // publishes per producer and buffer, this layer included
+      (void)last;
       Phase ph;
       // ---- P1: ln_1 + c_attn -> qkv[b, 3H]
-      ph.src_kind = (li > 0) ? SRC_LL : (p.has_embed ? SRC_EMBED : SRC_PLAIN);
+      ph.src_kind = (li > 0) ? SRC_LL : (p.has_embed ? SRC_EMBED : (in_hid ? SRC_LL : SRC_PLAIN));
       ph.src_ll = p.h_ll; ph.src_plain = p.hidden_in; ph.K = H; ph.src_epoch = ep - 8u + 5u;
       ph.src_ctr = ctr_of(5); ph.src_base = base_of(5); ph.src_rounds = rnd - 1u; ph.src_nprod = G;
+      ph.dst_sys = 0; ph.sentinel = nullptr; ph.sentinel_epoch = 0;
+      if (li == 0 && !p.has_embed && in_hid != nullptr) {
+        // input = what the previous pipeline stage wrote into this GPU's inbox
+        ph.src_ll = in_hid; ph.src_epoch = cep; ph.src_ctr = nullptr;
+        ph.sentinel = in_hid + (H - 1); ph.sentinel_epoch = cep;
+      }
       ph.ln_g = w.ln1_g; ph.ln_b = w.ln1_b; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
       ph.N = 3 * H; ph.has_bias = 1; ph.mode = EPI_QKV; ph.dst_ll = p.qkv_ll; ph.dst_plain = nullptr; ph.dst_epoch = ep + 1u;
       stage_x<WT, BT>(cx, ph);
@@ -701,12 +749,13 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       run_rows<WT, BT>(cx, ph);
       pub_ctr = ctr_of(1);
       stamp(step);
+      ph.sentinel = nullptr;
       // ---- P2: attention for the (b, head) tasks of this CTA
       if (cta < B * nh) {
         AttnArgs a;
         a.kc = w.kc; a.vc = w.vc; a.qkv_ll = p.qkv_ll; a.attn_ll = p.attn_ll; a.ep_qkv = ep + 1u; a.ep_attn = ep + 2u;
         a.ctr_qkv = ctr_of(1); a.ctr_attn = ctr_of(2); a.base_qkv = base_of(1); a.rounds = rnd;
-        a.nh = nh; a.slot0 = p.slot0; a.max_ctx = p.max_ctx; a.part = part; a.pm = pm; a.pl = pl; a.qkv_s = qkv_s;
+        a.nh = nh; a.slot0 = slot_base; a.max_ctx = p.max_ctx; a.part = part; a.pm = pm; a.pl = pl; a.qkv_s = qkv_s;
         for (int task = cta; task < B * nh; task += G) {
           attention_task<WT>(cx, a, task, pub_ctr);
           pub_ctr = nullptr;
@@ -734,7 +783,13 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       ph.src_ll = p.act_ll; ph.K = F; ph.src_epoch = ep + 4u; ph.src_ctr = ctr_of(4); ph.src_base = base_of(4);
       ph.ln_g = nullptr; ph.ln_b = nullptr; ph.pub_ctr = ctr_of(4);
       ph.N = H; ph.mode = EPI_PROJ2; ph.dst_ll = p.h_ll; ph.dst_epoch = ep + 5u;
-      ph.dst_plain = (last && !p.has_head) ? p.hidden_out : nullptr;
+      if (last && !p.has_head) {
+        if (p.peer_hid != nullptr) {   // straight into the next stage's inbox over NVLink
+          ph.dst_ll = p.peer_hid + (size_t)strm * B * H; ph.dst_epoch = cep; ph.dst_sys = 1;
+        } else {
+          ph.dst_plain = p.hidden_out;
+        }
+      }
       stage_x<WT, BT>(cx, ph);
       stamp(step);
       run_rows<WT, BT>(cx, ph);
@@ -749,6 +804,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       ph.src_ctr = ctr_of(5); ph.src_base = base_of(5); ph.src_rounds = (uint32_t)(step * p.L + p.L); ph.src_nprod = G;
       ph.ln_g = p.lnf_g; ph.ln_b = p.lnf_b; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
       ph.N = p.V; ph.has_bias = 0; ph.mode = EPI_HEAD; ph.dst_ll = nullptr; ph.dst_plain = nullptr; ph.dst_epoch = 0;
+      ph.dst_sys = 0; ph.sentinel = nullptr; ph.sentinel_epoch = 0;
       stage_x<WT, BT>(cx, ph);
       stamp(step);
       run_rows<WT, BT>(cx, ph);
@@ -782,8 +838,10 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
         }
         if (lane == 0) {
           if (cta == 0) {
-            p.ids_out[b] = r.i;
-            if (p.seq != nullptr) p.seq[(size_t)b * p.seq_stride + s_pos[b] + 1] = r.i;
+            p.ids_out[strm * B + b] = r.i;
+            if (p.seq != nullptr) p.seq[(size_t)(strm * B + b) * p.seq_stride + s_pos[b] + 1] = r.i;
+            // pipeline: the token goes straight into stage 0's inbox
+            if (p.peer_ids != nullptr) ll_store_sys(p.peer_ids + strm * B + b, (uint32_t)r.i, cep);
           }
           s_ids[b] = min(max(r.i, 0), p.V - 1);
         }
@@ -794,11 +852,14 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       if (tid == 0) ctr_bump(pub_ctr, cta);
     }
     // ---- bookkeeping: the cache grew by one position
-    if (cta == 0 && tid < B) p.lens[p.slot0 + tid] = s_pos[tid] + 1;
+    if (cta == 0 && tid < B) p.lens[slot_base + tid] = s_pos[tid] + 1;
     if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[step] = globaltimer();
     consumer_sync();
-    if (tid < B) s_pos[tid] = min(s_pos[tid] + 1, p.max_ctx - 1);
-    consumer_sync();
+  }
+  // pipeline, stage 0: the tokens of the last round never come back as inputs; collect them here
+  if (p.has_embed && p.inbox_ids != nullptr && p.tok_out != nullptr && cta == 0 && tid < p.n_streams * B) {
+    const int id = (int)ll_wait_sys(p.inbox_ids + tid, p.comm_epoch0 + (uint32_t)p.n_steps - 1u);
+    p.tok_out[(size_t)tid * p.tok_stride + (p.n_steps - 1)] = id;
   }
 }
 
@@ -817,7 +878,7 @@ int padded(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : 4); }
 size_t fixed_smem(int BT, int H, int L) {
   return (size_t)BT * 4 * H * 4 /*xs*/ + kNW * 64 * 4 /*part*/ + 2 * kNW * 4 /*pm,pl*/ + (size_t)2 * BT * kNW * 4 /*red*/ +
          (size_t)2 * BT * kOwnMax * 4 /*hloc,h2loc*/ + 3 * 64 * 4 /*qkv_s*/ + (size_t)kNW * BT * 8 /*sbv,sbi*/ +
-         64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + 256 /*ctr base*/ + (size_t)L * sizeof(MegaLayer) + 128;
+         64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + 256 /*ctr base*/ + 256 /*pos0*/ + (size_t)L * sizeof(MegaLayer) + 128;
 }
 
 }  // namespace
@@ -855,7 +916,8 @@ cudaError_t init_mega_attrs() {
 }
 
 cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_t s) {
-  if (!mega_supported(p.B, p.H, p.nh, p.L, dtype, num_sms) || p.n_steps < 1 || p.epoch0 == 0 || p.flags == nullptr)
+  if (!mega_supported(p.B, p.H, p.nh, p.L, dtype, num_sms) || p.n_steps < 1 || p.epoch0 == 0 || p.flags == nullptr ||
+      p.n_streams < 1 || p.n_streams * p.B > 64)
     return cudaErrorInvalidValue;
   const int BT = padded(p.B);
   const size_t fixed = fixed_smem(BT, p.H, p.L);

@@ -97,8 +97,16 @@ struct MegaParams {
   uint32_t ctr_base[64] = {0};                               // their values when this launch starts
   uint32_t epoch0 = 0;                                       // first epoch of this launch (> every earlier one)
   int32_t* ids_out = nullptr; int32_t* seq = nullptr; int seq_stride = 0; float* logits_out = nullptr;
-  int n_steps = 1;
-  unsigned long long* step_clock = nullptr;                  // [n_steps+1] globaltimer ns: end of each step, then start
+  int n_steps = 1;                                           // decode steps (rounds) per launch
+  int n_streams = 1;                                         // sequences groups per round: item (round, stream) uses slots slot0 + stream*B ..
+  // pipeline mode: the stage boundary as peer-memory writes + flag-in-data words
+  const unsigned long long* inbox_hid = nullptr;             // local [n_streams][B][H]: hidden from the previous stage
+  const unsigned long long* inbox_ids = nullptr;             // local [n_streams][B]: tokens from the last stage (stage 0)
+  unsigned long long* peer_hid = nullptr;                    // next stage's inbox_hid (mapped peer memory)
+  unsigned long long* peer_ids = nullptr;                    // stage 0's inbox_ids (mapped peer memory; last stage)
+  uint32_t comm_epoch0 = 0;                                  // epoch of round 0 on the stage boundary
+  int32_t* tok_out = nullptr; int tok_stride = 0;            // stage 0: tokens [n_streams*B][n_steps]
+  unsigned long long* step_clock = nullptr;                  // [items+1] globaltimer ns: end of each item, then start
   int n_slots = 0;                                           // filled by the launcher
   long long* trace = nullptr; int trace_cap = 0;             // debug: clock64 of CTA 0 per phase boundary
 };

@@ -161,5 +161,27 @@ class StageEngine:
             return out, {"prefill_ms": tm[0], "decode_ms": tm[1], "step_ms": list(tm)[2:2 + max(n_new - 1, 0)]}
         return out
 
+    # ---- device-side stage boundary (multi-GPU pipelines)
+    def comm_export(self) -> bytes:
+        buf = (C.c_ubyte * 64)()
+        check(self.lib.gp_comm_export(self._h, buf), self._h)
+        return bytes(buf)
+
+    def comm_connect(self, peer_handle: bytes):
+        buf = (C.c_ubyte * 64).from_buffer_copy(peer_handle)
+        check(self.lib.gp_comm_connect(self._h, buf), self._h)
+
+    def pipeline_decode(self, first_ids, n_rounds: int, n_streams: int, B: int, comm_epoch0: int,
+                        timeout_ms: int = 20000):
+        """One persistent launch: n_rounds decode steps of n_streams micro-batches on this stage.
+        Stage 0 passes `first_ids` (int32 [n_streams*B], device) and gets int32 [n_streams*B, n_rounds]."""
+        tokens = None
+        if self.has_embed:
+            tokens = torch.empty((n_streams * B, n_rounds), dtype=torch.int32, device=self.device)
+        ms = C.c_float(0.0)
+        check(self.lib.gp_pipeline_decode(self._h, _ptr(first_ids), n_rounds, n_streams, B, comm_epoch0, _ptr(tokens),
+                                          timeout_ms, C.byref(ms), _stream_ptr(self.device)), self._h)
+        return tokens, float(ms.value)
+
     def last_launch_count(self) -> int:
         return int(self.lib.gp_last_launch_count(self._h))

@@ -70,7 +70,7 @@ def run_ticks(rank: int, n_stages: int, n_streams: int, n_rounds: int, exchange,
 class PipelineRunner:
     def __init__(self, dims: GPT2Dims, seed: int = 0, dtype: int = GP_BF16, batch_per_stream: int = 1,
                  max_ctx: Optional[int] = None, rank: int = 0, world: int = 1, device: int = 0, recipe: str = "hf",
-                 weights=None, flags: int = 0):
+                 weights=None, flags: int = 0, transport: str = "p2p"):
         from .engine import StageEngine
         self.dims, self.rank, self.world, self.B = dims, rank, world, batch_per_stream
         self.n_streams = world
@@ -89,8 +89,16 @@ class PipelineRunner:
             if not dist.is_initialized():
                 dist.init_process_group("nccl", device_id=self.device)
             self.dist = dist
+            self.transport = transport
+            self.comm_epoch = 1
+            if transport == "p2p":
+                handles = [None] * world
+                dist.all_gather_object(handles, self.engine.comm_export())
+                self.engine.comm_connect(handles[(rank + 1) % world])
+                dist.barrier()
         else:
             self.dist = None
+            self.transport = "none"
 
     # ---- small collectives for the bench harness
     def barrier(self):
@@ -166,9 +174,20 @@ class PipelineRunner:
                 e_prefill.record()
             return out["next_ids"] if self.last else out["hidden"]
 
-        run_ticks(self.rank, S, M, n_new, exchange, compute, on_ids)
+        p2p = self.transport == "p2p" and n_new > 1
+        run_ticks(self.rank, S, M, min(n_new, 1) if p2p else n_new, exchange, compute, on_ids)
         if n_new <= 0:
             e_prefill.record()
+        kernel_ms = None
+        if p2p:
+            # decode: one persistent launch per stage; the stage boundary is peer-memory writes
+            rounds = n_new - 1
+            first = seq[:, P].contiguous() if self.first else None
+            tokens, kernel_ms = eng.pipeline_decode(first, rounds, M, B, self.comm_epoch)
+            self.comm_epoch += rounds
+            state["launches"] += eng.last_launch_count()
+            if self.first:
+                seq[:, P + 1:] = tokens
         e_end.record()
         torch.cuda.synchronize(dev)
         result = seq.cpu() if self.first else None
@@ -176,8 +195,11 @@ class PipelineRunner:
             return result
         tm = {"prefill_ms": e_start.elapsed_time(e_prefill), "decode_ms": e_prefill.elapsed_time(e_end),
               "step_ms": [], "launches": state["launches"]}
+        if kernel_ms is not None:
+            # every round advances all streams by one token; the persistent kernel has no per-round events
+            tm["step_ms"] = [kernel_ms / (n_new - 1)] * (n_new - 1)
         se = state["step_events"]
-        if self.last and len(se) > 1:
+        if kernel_ms is None and self.last and len(se) > 1:
             # one entry per round: time for ALL streams to advance one token
             tm["step_ms"] = [se[i - 1].elapsed_time(se[i]) for i in range(1, len(se))]
         gathered = [None] * S
