@@ -256,6 +256,37 @@ __device__ __forceinline__ void stage_enter(uint32_t* pub_ctr, int pub_idx, cons
   consumer_sync();
 }
 
+// One row of a flag-in-data buffer -> shared memory.  All PER loads of a thread are issued
+// back to back (addresses clamped instead of predicated, so no branch separates them) and only
+// then checked; words whose epoch is still old are re-read, again as one batch.
+template <int PER>
+__device__ __forceinline__ void copy_ll(float* xrow, const u64* src, int k0, int K, uint32_t epoch) {
+  const int tid = threadIdx.x;
+  u64 w[PER];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) w[i] = ll_load(src + min(k0 + tid + i * kConsumers, K - 1));
+  unsigned pending = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int k = k0 + tid + i * kConsumers;
+    if (k < K) {
+      if ((uint32_t)(w[i] >> 32) == epoch) xrow[k] = __uint_as_float((uint32_t)w[i]);
+      else pending |= 1u << i;
+    }
+  }
+  while (pending) {   // rare: the counters said "published" before the last words became visible
+#pragma unroll 1
+    for (int i = 0; i < PER; ++i)
+      if (pending & (1u << i)) {
+        const u64 v = ll_load(src + k0 + tid + i * kConsumers);
+        if ((uint32_t)(v >> 32) == epoch) {
+          xrow[k0 + tid + i * kConsumers] = __uint_as_float((uint32_t)v);
+          pending &= ~(1u << i);
+        }
+      }
+  }
+}
+
 // Collect x[B,K] into shared memory; elements not yet visible are re-read until they are.
 // LayerNorm variant (K = H <= 1920): the row lives in registers; mean and the two-pass biased
 // variance ([hf] modeling_gpt2.py:252,254,505) each cost one shared-memory exchange.  Fully
@@ -265,32 +296,22 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
   const int tid = threadIdx.x, w = tid >> 5, l = tid & 31, K = ph.K, B = cx.B;
   float* xs = cx.xs;
   if (ph.ln_g == nullptr) {
-    stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
-                ph.src_nprod, ph.sentinel, ph.sentinel_epoch);
+    // plain copy: always from a flag-in-data buffer (attention output, GELU output)
+    stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, ph.sentinel,
+                ph.sentinel_epoch);
     cx.stamp();
+    const int per = (K + kConsumers - 1) / kConsumers;
 #pragma unroll
     for (int b = 0; b < BT; ++b) {
       if (b >= B) {
         for (int k = tid; k < K; k += kConsumers) xs[b * K + k] = 0.f;
         continue;
       }
-      unsigned pending = 0;
-#pragma unroll
-      for (int i = 0; i < kCopyPer; ++i) {
-        const int k = tid + i * kConsumers;
-        if (k < K) {
-          float v;
-          if (fetch_x(cx, ph, b, k, v)) xs[b * K + k] = v;
-          else pending |= 1u << i;
-        }
-      }
-      while (pending) {
-#pragma unroll
-        for (int i = 0; i < kCopyPer; ++i)
-          if (pending & (1u << i)) {
-            float v;
-            if (fetch_x(cx, ph, b, tid + i * kConsumers, v)) { xs[b * K + tid + i * kConsumers] = v; pending &= ~(1u << i); }
-          }
+      const u64* src = ph.src_ll + (size_t)b * K;
+      if (per <= 2) {
+        copy_ll<2>(xs + b * K, src, 0, K, ph.src_epoch);
+      } else {
+        for (int k0 = 0; k0 < K; k0 += 8 * kConsumers) copy_ll<8>(xs + b * K, src, k0, K, ph.src_epoch);
       }
     }
     cx.stamp();
@@ -309,14 +330,14 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
   cx.stamp();
   unsigned pending = 0;
 #pragma unroll
-  for (int i = 0; i < kLnPer; ++i) {
-    const int k = tid + i * kConsumers;
+  for (int i = 0; i < kLnPer; ++i)
 #pragma unroll
     for (int b = 0; b < BT; ++b) {
-      v[b][i] = 0.f;
-      if (b < B && k < K && !fetch_x(cx, ph, b, k, v[b][i])) pending |= 1u << (b * kLnPer + i);
+      const bool ok = fetch_x(cx, ph, min(b, B - 1), min(tid + i * kConsumers, K - 1), v[b][i]);
+      const bool live = b < B && tid + i * kConsumers < K;
+      if (!live) v[b][i] = 0.f;
+      else if (!ok) pending |= 1u << (b * kLnPer + i);
     }
-  }
   while (pending) {
 #pragma unroll
     for (int b = 0; b < BT; ++b)
@@ -479,7 +500,7 @@ struct SoftState {
 __device__ __forceinline__ void soft_merge(SoftState& a, float mo, float lo, const float (&ao)[8]) {
   const float mn = fmaxf(a.m, mo);
   if (mn == -INFINITY) return;
-  const float c1 = expf(a.m - mn), c2 = expf(mo - mn);
+  const float c1 = __expf(a.m - mn), c2 = __expf(mo - mn);
   a.l = a.l * c1 + lo * c2;
 #pragma unroll
   for (int i = 0; i < 8; ++i) a.acc[i] = a.acc[i] * c1 + ao[i] * c2;
@@ -563,7 +584,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
     dot += __shfl_xor_sync(grp_mask, dot, 2);
     dot += __shfl_xor_sync(grp_mask, dot, 4);
     const float mn = fmaxf(st.m, dot);
-    const float c1 = expf(st.m - mn), pe = expf(dot - mn);
+    const float c1 = __expf(st.m - mn), pe = __expf(dot - mn);
     st.l = st.l * c1 + pe;
 #pragma unroll
     for (int i = 0; i < 8; ++i) st.acc[i] = st.acc[i] * c1 + pe * vv[i];
@@ -593,7 +614,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
     float Lsum = 0.f, o = 0.f;
 #pragma unroll
     for (int ww = 0; ww < kNW; ++ww) {
-      const float c = (a.pm[ww] == -INFINITY) ? 0.f : expf(a.pm[ww] - M);
+      const float c = (a.pm[ww] == -INFINITY) ? 0.f : __expf(a.pm[ww] - M);
       Lsum += a.pl[ww] * c;
       o += a.part[ww * D + tid] * c;
     }
