@@ -47,6 +47,9 @@ struct gp_engine {
   float* attn_f = nullptr;  // [max_batch, H]    decode attention output (GEMV path)
   float* act_f = nullptr;   // [max_batch, 4H]   decode GELU output (GEMV path)
   float* hlast = nullptr;   // [max_batch, H]
+  float* splitk = nullptr;  // split-K partial tiles of the tcgen05 GEMM (decode-sized M)
+  size_t splitk_floats = 0;
+  float* logits_ws = nullptr;  // [max_batch, V] logits of the GEMM-path lm_head
   void* lm_scratch = nullptr;
   float* stage = nullptr;
   size_t stage_floats = 0;
@@ -122,8 +125,11 @@ bool bf(const gp_engine* e) { return e->cfg.dtype == GP_BF16; }
 // GEMM dispatch: tcgen05 when the shape allows and the storage type is bf16, else SIMT tiles
 cudaError_t gemm(gp_engine* e, const void* A, int lda, const void* Wt, const float* bias, const float* residual,
                  int ldr, void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s) {
-  if (bf(e) && !(e->cfg.flags & GP_FLAG_NO_TCGEN05) && gemm_tc_supported(M, N, K) && lda == K)
-    return launch_gemm_tc(A, lda, Wt, bias, residual, ldr, out, ldo, M, N, K, flags, s);
+  if (bf(e) && !(e->cfg.flags & GP_FLAG_NO_TCGEN05) && gemm_tc_supported(M, N, K) && lda == K) {
+    float* part = (M <= 256) ? e->splitk : nullptr;
+    if (part && gemm_tc_splits(M, N, K, e->splitk_floats) > 1) ++e->launches;   // the split-K epilogue kernel
+    return launch_gemm_tc(A, lda, Wt, bias, residual, ldr, out, ldo, M, N, K, flags, s, part, e->splitk_floats);
+  }
   return launch_gemm_simt(A, lda, Wt, bias, residual, ldr, out, ldo, M, N, K, flags, e->cfg.dtype, s);
 }
 
@@ -314,7 +320,9 @@ int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
 
   if (use_mega(e, B)) return decode_mega(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, seq, 1, false, s);
 
-  const bool use_gemv = gemv_supported(B, F);
+  // GEMV kernels: fp32 mode and odd shapes; in bf16 mode more than 4 rows go to the tcgen05 GEMMs
+  const bool tc_ok = bf(e) && !(c.flags & GP_FLAG_NO_TCGEN05) && gemm_tc_supported(B, H, H);
+  const bool use_gemv = gemv_supported(B, F) && !(tc_ok && B > 4);
   const bool obf = bf(e);
   const uint32_t oflag = obf ? GP_OUT_BF16 : 0u;
 
@@ -364,7 +372,14 @@ int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
       LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, e->h, H, dst, H, B, H, F, 0u, s));
     }
   }
-  if (c.has_head) {
+  if (c.has_head && !use_gemv && e->logits_ws != nullptr && gemm_tc_supported(B, e->V, H)) {
+    // batched decode: ln_f -> tcgen05 GEMM over the tied head -> per-row argmax (+ bookkeeping)
+    float* lg = logits ? logits : e->logits_ws;
+    LAUNCH(e, launch_layernorm(e->h, H, e->lnf_g, e->lnf_b, e->xa, true, B, H, c.ln_eps, s));
+    LAUNCH(e, gemm(e, e->xa, H, e->wte, nullptr, nullptr, 0, lg, e->V, B, e->V, H, 0u, s));
+    LAUNCH(e, launch_argmax_rows(lg, e->V, B, e->V, next_ids ? next_ids : e->mailbox, e->lens, slot0, seq,
+                                 e->seq_stride, s));
+  } else if (c.has_head) {
     // the last CTA of the (last) lm_head launch advances the cache lengths and appends to seq
     r = run_lm_head(e, e->h, H, B, slot0, logits, next_ids, e->lens, seq, s);
     if (r != GP_OK) return r;
@@ -482,6 +497,12 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRY(alloc((void**)&e->attn_f, MB * H * 4));
   TRY(alloc((void**)&e->act_f, MB * F * 4));
   TRY(alloc((void**)&e->hlast, MB * H * 4));
+  if (cfg->dtype == GP_BF16 && !(cfg->flags & GP_FLAG_NO_TCGEN05)) {
+    e->splitk_floats = (size_t)8 * 256 * (size_t)(F > V ? F : (cfg->has_head ? V : F));
+    if (e->splitk_floats > ((size_t)48 << 20)) e->splitk_floats = (size_t)48 << 20;   // 192 MB cap
+    TRY(alloc((void**)&e->splitk, e->splitk_floats * 4));
+    if (cfg->has_head) TRY(alloc((void**)&e->logits_ws, MB * V * 4));
+  }
   TRY(alloc((void**)&e->seq, MB * (size_t)e->seq_stride * sizeof(int32_t)));
   TRY(alloc((void**)&e->prompt, MB * (size_t)cfg->n_positions * sizeof(int32_t)));
   TRY(alloc((void**)&e->mailbox, MB * sizeof(int32_t)));

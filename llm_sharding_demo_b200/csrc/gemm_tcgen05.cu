@@ -116,7 +116,7 @@ template <int BM, typename OT>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
                const float* __restrict__ bias, const float* residual, int ldr, OT* out, int ldo, int M, int N, int K,
-               uint32_t flags) {
+               uint32_t flags, float* __restrict__ partial) {
   using C = Cfg<BM>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -129,7 +129,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * kBlockN, m0 = blockIdx.y * BM;
-  const int nk = (K + kBlockK - 1) / kBlockK;
+  // split-K: gridDim.z CTAs share one output tile; CTA z takes k-blocks [kb0, kb1) and, when
+  // gridDim.z > 1, stores its raw fp32 partial tile to partial[z][m][n] for splitk_epilogue_kernel
+  const int nk_all = (K + kBlockK - 1) / kBlockK;
+  const int kb0 = (int)(((long long)blockIdx.z * nk_all) / gridDim.z);
+  const int kb1 = (int)(((long long)(blockIdx.z + 1) * nk_all) / gridDim.z);
+  const int nk = kb1 - kb0;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
@@ -159,8 +164,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         const uint32_t ph = (kb / C::kStages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_expect_tx(&full[s], C::kStageBytes);
-        tma_load_2d(sW + s * kWBytes, &tmW, kb * kBlockK, n0, &full[s]);
-        tma_load_2d(sA + s * C::kABytes, &tmA, kb * kBlockK, m0, &full[s]);
+        tma_load_2d(sW + s * kWBytes, &tmW, (kb0 + kb) * kBlockK, n0, &full[s]);
+        tma_load_2d(sA + s * C::kABytes, &tmA, (kb0 + kb) * kBlockK, m0, &full[s]);
       }
     }
   } else if (warp == 1) {
@@ -189,8 +194,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     tc_fence_after();
     const int n = n0 + q * 32 + lane;
     const bool n_ok = n < N;
-    const float bv = (bias != nullptr && n_ok) ? bias[n] : 0.f;
-    const bool gelu = flags & GP_EPI_GELU;
+    const bool split = gridDim.z > 1;
+    const float bv = (!split && bias != nullptr && n_ok) ? bias[n] : 0.f;
+    const bool gelu = !split && (flags & GP_EPI_GELU);
+    float* pz = split ? partial + (size_t)blockIdx.z * M * N : nullptr;
 #pragma unroll 1
     for (int c0 = 0; c0 < BM; c0 += 16) {
       if (m0 + c0 >= M) break;  // warp-uniform
@@ -201,9 +208,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         const int m = m0 + c0 + j;
         if (n_ok && m < M) {
           float v = __uint_as_float(r[j]) + bv;
-          if (gelu) v = gelu_new(v);
-          if (residual != nullptr) v += residual[(size_t)m * ldr + n];
-          store1(out + (size_t)m * ldo + n, v);
+          if (split) {
+            pz[(size_t)m * N + n] = v;
+          } else {
+            if (gelu) v = gelu_new(v);
+            if (residual != nullptr) v += residual[(size_t)m * ldr + n];
+            store1(out + (size_t)m * ldo + n, v);
+          }
         }
       }
     }
@@ -213,6 +224,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::kTmemCols)
                  : "memory");
+  }
+}
+
+// out[m,n] = epi(sum_z partial[z][m][n] + bias[n]) (+ residual[m,n]); fixed summation order => deterministic
+template <typename OT>
+__global__ void __launch_bounds__(256)
+splitk_epilogue_kernel(const float* __restrict__ partial, int S, const float* __restrict__ bias, const float* residual,
+                       int ldr, OT* out, int ldo, int M, int N, uint32_t flags) {
+  const size_t MN = (size_t)M * N;
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < MN; i += (size_t)gridDim.x * 256) {
+    const int m = (int)(i / N), n = (int)(i - (size_t)m * N);
+    float v = 0.f;
+    for (int z = 0; z < S; ++z) v += partial[(size_t)z * MN + i];
+    if (bias) v += bias[n];
+    if (flags & GP_EPI_GELU) v = gelu_new(v);
+    if (residual) v += residual[(size_t)m * ldr + n];
+    store1(out + (size_t)m * ldo + n, v);
   }
 }
 
@@ -263,10 +291,17 @@ cudaError_t tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtens
 
 template <int BM, typename OT>
 cudaError_t launch_t(const CUtensorMap& tw, const CUtensorMap& ta, const float* bias, const float* residual, int ldr,
-                     void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s) {
-  dim3 grid((N + kBlockN - 1) / kBlockN, (M + BM - 1) / BM);
+                     void* out, int ldo, int M, int N, int K, uint32_t flags, int splits, float* partial,
+                     cudaStream_t s) {
+  dim3 grid((N + kBlockN - 1) / kBlockN, (M + BM - 1) / BM, splits);
   gemm_tc_kernel<BM, OT><<<grid, kThreads, Cfg<BM>::kSmemBytes, s>>>(tw, ta, bias, residual, ldr, (OT*)out, ldo, M, N,
-                                                                    K, flags);
+                                                                    K, flags, partial);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess || splits <= 1) return e;
+  size_t mn = (size_t)M * N;
+  int g = (int)((mn + 255) / 256);
+  if (g > 148 * 8) g = 148 * 8;
+  splitk_epilogue_kernel<OT><<<g, 256, 0, s>>>(partial, splits, bias, residual, ldr, (OT*)out, ldo, M, N, flags);
   return cudaGetLastError();
 }
 
@@ -291,8 +326,22 @@ cudaError_t init_gemm_tc() {
   return cudaSuccess;
 }
 
+int gemm_tc_splits(int M, int N, int K, size_t partial_floats) {
+  // few output tiles (decode-sized M, narrow N): split K so that ~all SMs stream weights
+  const int BM = (M <= 32) ? 32 : 128;
+  const int tiles = ((N + kBlockN - 1) / kBlockN) * ((M + BM - 1) / BM);
+  const int nk = (K + kBlockK - 1) / kBlockK;
+  int s = 148 / tiles;
+  if (s > 8) s = 8;
+  if (s > nk / 2) s = nk / 2;   // at least two k-blocks per CTA
+  if (s < 2) return 1;
+  while (s > 1 && (size_t)s * M * N > partial_floats) --s;
+  return s;
+}
+
 cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* bias, const float* residual, int ldr,
-                           void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s) {
+                           void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s, float* partial,
+                           size_t partial_floats) {
   if (!gemm_tc_supported(M, N, K) || lda != K) return cudaErrorInvalidValue;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Wt) & 15)) return cudaErrorInvalidValue;
   const int BM = (M <= 32) ? 32 : 128;
@@ -301,11 +350,12 @@ cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* 
   if ((e = tensor_map(Wt, N, K, kBlockN, &tw)) != cudaSuccess) return e;
   if ((e = tensor_map(A, M, K, BM, &ta)) != cudaSuccess) return e;
   const bool obf = flags & GP_OUT_BF16;
+  const int splits = partial ? gemm_tc_splits(M, N, K, partial_floats) : 1;
   if (BM == 32)
-    return obf ? launch_t<32, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s)
-               : launch_t<32, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s);
-  return obf ? launch_t<128, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s)
-             : launch_t<128, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, s);
+    return obf ? launch_t<32, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s)
+               : launch_t<32, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s);
+  return obf ? launch_t<128, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s)
+             : launch_t<128, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s);
 }
 
 }  // namespace gp

@@ -230,6 +230,41 @@ convert_kernel(const float* __restrict__ src, WT* __restrict__ dst, size_t n) {
     dst[i] = from_f<WT>(src[i]);
 }
 
+// greedy selection on materialised logits (batched decode through the GEMM path): one CTA per
+// sequence, lowest index wins ties; optionally appends to seq and advances the cache length
+__global__ void __launch_bounds__(512)
+argmax_rows_kernel(const float* __restrict__ logits, int ldl, int V, int32_t* __restrict__ ids_out, int32_t* lens,
+                   int slot0, int32_t* seq, int seq_stride) {
+  __shared__ float sv[16];
+  __shared__ int si[16];
+  const int b = blockIdx.x;
+  const float* row = logits + (size_t)b * ldl;
+  float bv = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < V; i += 512) {
+    const float v = row[i];
+    if (v > bv) { bv = v; bi = i; }   // ascending i per thread: first maximum kept
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(FULL_MASK, bv, o);
+    const int oi = __shfl_xor_sync(FULL_MASK, bi, o);
+    if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 16; ++w)
+      if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
+    ids_out[b] = bi;
+    if (lens != nullptr) {
+      const int old_len = lens[slot0 + b];
+      if (seq != nullptr) seq[(size_t)b * seq_stride + old_len + 1] = bi;
+      lens[slot0 + b] = old_len + 1;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 gather_last_kernel(const float* __restrict__ src, float* __restrict__ dst, int T, int H) {
   const int b = blockIdx.x;
@@ -325,6 +360,12 @@ cudaError_t launch_convert(const float* src, void* dst, int R, int C, bool trans
     if (dtype == GP_BF16) convert_kernel<bf16><<<grid, 256, 0, s>>>(src, (bf16*)dst, n);
     else convert_kernel<float><<<grid, 256, 0, s>>>(src, (float*)dst, n);
   }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_argmax_rows(const float* logits, int ldl, int B, int V, int32_t* ids_out, int32_t* lens, int slot0,
+                               int32_t* seq, int seq_stride, cudaStream_t s) {
+  argmax_rows_kernel<<<B, 512, 0, s>>>(logits, ldl, V, ids_out, lens, slot0, seq, seq_stride);
   return cudaGetLastError();
 }
 

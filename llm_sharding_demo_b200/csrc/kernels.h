@@ -124,7 +124,14 @@ void record_error(const char* msg);
 // ---- tcgen05 GEMM (gemm_tcgen05.cu)
 bool gemm_tc_supported(int M, int N, int K);
 cudaError_t init_gemm_tc();
+// `partial` (optional, `partial_floats` fp32 of scratch) enables deterministic split-K for
+// decode-sized problems; gemm_tc_splits tells how many kernels the call will launch (1 or 2)
+int gemm_tc_splits(int M, int N, int K, size_t partial_floats);
 cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* bias, const float* residual,
-                           int ldr, void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s);
+                           int ldr, void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s,
+                           float* partial = nullptr, size_t partial_floats = 0);
+// per-row argmax of fp32 logits [B,V] (lowest index wins ties) + the decode bookkeeping of the lm_head kernel
+cudaError_t launch_argmax_rows(const float* logits, int ldl, int B, int V, int32_t* ids_out, int32_t* lens, int slot0,
+                               int32_t* seq, int seq_stride, cudaStream_t s);
 
 }  // namespace gp
