@@ -30,8 +30,10 @@ if ROOT not in sys.path:
 import torch  # noqa: E402
 
 WORKLOADS = {
-    # name: (preset, B per stream, P, n_new, weight seed)
-    "gpt2-124m-b1-p32-n128": ("gpt2", 1, 32, 128, 1234),
+    # name: (preset, B per stream, P, n_new, weight seed).  N GPUs = N stages x N streams of B sequences.
+    "gpt2-124m-b1-p32-n128": ("gpt2", 1, 32, 128, 1234),          # BASELINE.json configs[1] (the metric's config)
+    "gpt2-medium-b8-p512-n128": ("gpt2-medium", 2, 512, 128, 1234),  # configs[2]: 4 stages x 4 streams x 2 = batch 8
+    "gpt2-xl-b32-p896-n128": ("gpt2-xl", 4, 896, 128, 1234),      # configs[3]: 8 stages x 8 streams x 4 = batch 32, ctx 1024
 }
 DEFAULT_WORKLOAD = "gpt2-124m-b1-p32-n128"
 METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
@@ -130,6 +132,9 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_p
     split = O.split_layers(dims.n_layer, 2)[0][1]
     lat = []
     steps = sorted(set(int(round(i * (n_new - 1) / max(1, n_samples - 1))) for i in range(n_samples)))
+    # bound the CPU work: at most 2048 token positions per timed forward (the per-sequence cost is what is
+    # measured; the reference has no batching on /forward anyway, server.py:137)
+    B_full, B = B, max(1, min(B, 2048 // (P + n_new)))
     with torch.no_grad():
         for t in steps:
             ids = synthetic_prompts(B, P + t, dims.vocab_size, seed=7 + t).long()
@@ -138,10 +143,12 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_p
             logits = O.shard_b_forward(w, dims, hidden, split)
             O.greedy_select(logits[:, -1])
             lat.append(time.perf_counter() - t0)
-    info = {"sampled_steps": steps}
-    if full_path_probe:
-        # one token of the reference's real wire format: hidden and ALL-position logits as JSON
+    info = {"sampled_steps": steps, "sequences_timed": B, "sequences_in_workload": B_full}
+    if full_path_probe and hidden.shape[1] <= 200:
+        # one token of the reference's real wire format: hidden and ALL-position logits as JSON (one sequence;
+        # skipped for long sequences, where it alone would take minutes)
         t0 = time.perf_counter()
+        hidden, logits = hidden[:1], logits[:1]
         h_json = json.dumps({"hidden_states": hidden.tolist()})
         hidden2 = torch.tensor(json.loads(h_json)["hidden_states"], dtype=torch.float32)
         l_json = json.dumps({"logits": logits.tolist()})

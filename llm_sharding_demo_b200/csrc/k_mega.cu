@@ -561,21 +561,21 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
   st.m = -INFINITY; st.l = 0.f;
 #pragma unroll
   for (int i = 0; i < 8; ++i) st.acc[i] = 0.f;
-  for (int j = 0; grp + kGroups * j <= pos; ++j) {
-    const int t = grp + kGroups * j;
+  // software pipeline over this group's rows t = grp, grp+60, ...: two register buffers; a row's K/V
+  // chunk is consumed and the buffer immediately refilled with the row two steps ahead
+  auto step = [&](int t, Raw8<WT>& kb, Raw8<WT>& vb) {
     float kk[8], vv[8];
     if (t == pos) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) { kk[i] = a.qkv_s[D + l8 * 8 + i]; vv[i] = a.qkv_s[2 * D + l8 * 8 + i]; }
-    } else if (j == 0) {
-      pk0.get(kk);
-      pv0.get(vv);
-    } else if (j == 1) {
-      pk1.get(kk);
-      pv1.get(vv);
     } else {
-      load8(Kc + (size_t)t * D + l8 * 8, kk);
-      load8(Vc + (size_t)t * D + l8 * 8, vv);
+      kb.get(kk);
+      vb.get(vv);
+    }
+    const int t2 = t + 2 * kGroups;
+    if (t2 < pos) {
+      kb.load(Kc + (size_t)t2 * D + l8 * 8);
+      vb.load(Vc + (size_t)t2 * D + l8 * 8);
     }
     float dot = 0.f;
 #pragma unroll
@@ -589,6 +589,10 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
 #pragma unroll
     for (int i = 0; i < 8; ++i) st.acc[i] = st.acc[i] * c1 + pe * vv[i];
     st.m = mn;
+  };
+  for (int t = grp; t <= pos; t += 2 * kGroups) {
+    step(t, pk0, pv0);
+    if (t + kGroups <= pos) step(t + kGroups, pk1, pv1);
   }
   __syncwarp();
   cx.stamp();
