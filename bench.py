@@ -263,15 +263,23 @@ def run_b200(args):
         if world == 1:
             bytes_launch = bytes_step * (n_new - 1)
             achieved = bytes_launch / (decode_ms_mean / 1000.0) / 1e9
-            kern = "decode_mega_kernel<bf16,1> (persistent, %d decode steps per launch)" % (n_new - 1)
+            kern = ("decode_mega_kernel (persistent, %d decode steps per launch)" % (n_new - 1)) if B <= 4 else \
+                "decode step (tcgen05 GEMMs + attention kernels in a CUDA graph)"
         else:
-            bytes_launch = bytes_step / world
-            achieved = bytes_launch / (p50_tok_ms / 1000.0 / n_streams) / 1e9 if p50_tok_ms else 0.0
-            kern = "decode_mega_kernel<bf16,1> (one step of one stage per launch)"
+            # one persistent launch per stage for the whole request: every round each stage streams its
+            # share of the weights once per stream plus its share of the KV cache
+            H_, L_, V_ = dims.n_embd, dims.n_layer, dims.vocab_size
+            w_bytes = esz * (L_ * (12 * H_ * H_ + 13 * H_) + V_ * H_ + 2 * H_)
+            kv_bytes = bytes_step - w_bytes
+            bytes_round_all = n_streams * (w_bytes + kv_bytes)           # all stages together, per round
+            bytes_launch = bytes_round_all * (n_new - 1) / world           # per stage launch
+            achieved = bytes_launch / (decode_ms_mean / 1000.0) / 1e9
+            kern = "decode_mega_kernel (one persistent launch per stage, %d rounds x %d streams)" % (n_new - 1, n_streams)
         roof = {"bound": "hbm", "kernel": kern, "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind,
-                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH,
+                "unit": "GB/s", "frac": round(achieved / peak, 4),
+                "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH if (world == 1 and args.workload == DEFAULT_WORKLOAD) else None,
                 "algorithmic_bytes_per_launch": int(bytes_launch),
-                "note": "batch-1 decode of a 124M model is latency-bound (about 60 dependent phases per token); see DESIGN.md"}
+                "note": "per-GPU figure; small-batch decode is latency-bound (dependent phases), see DESIGN.md"}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:

@@ -422,47 +422,66 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
     if (lane == 0) mbar_wait(&rg.full[s], phs);   // one waiter per warp
     __syncwarp();
     if (r == r0) cx.stamp();
-    for (int rr = warp; rr < n; rr += kNW) {
-      const WT* wrow = reinterpret_cast<const WT*>(slot + (size_t)rr * rowbytes);
-      float acc[BT];
+    // Row blocking: a warp takes RB = BT consecutive rows, so each x chunk it pulls from shared
+    // memory is used RB times - the x traffic per weight row stays that of batch 1.
+    constexpr int RB = (BT >= 4) ? 2 : BT;   // 4 x 4 accumulators + 32 x registers spill at 128 regs/thread
+    for (int g0 = warp * RB; g0 < n; g0 += kNW * RB) {
+      float acc[RB][BT];
 #pragma unroll
-      for (int b = 0; b < BT; ++b) acc[b] = 0.f;
-#pragma unroll 4
+      for (int rI = 0; rI < RB; ++rI)
+#pragma unroll
+        for (int b = 0; b < BT; ++b) acc[rI][b] = 0.f;
+#pragma unroll 2
       for (int k0 = lane * 8; k0 < K; k0 += 256) {
-        float w[8];
-        lds8(wrow + k0, w);
+        float4 x0[BT], x1[BT];
 #pragma unroll
         for (int b = 0; b < BT; ++b) {
-          const float4 x0 = *reinterpret_cast<const float4*>(xs + b * K + k0);
-          const float4 x1 = *reinterpret_cast<const float4*>(xs + b * K + k0 + 4);
-          acc[b] = fmaf(w[0], x0.x, acc[b]); acc[b] = fmaf(w[1], x0.y, acc[b]);
-          acc[b] = fmaf(w[2], x0.z, acc[b]); acc[b] = fmaf(w[3], x0.w, acc[b]);
-          acc[b] = fmaf(w[4], x1.x, acc[b]); acc[b] = fmaf(w[5], x1.y, acc[b]);
-          acc[b] = fmaf(w[6], x1.z, acc[b]); acc[b] = fmaf(w[7], x1.w, acc[b]);
+          x0[b] = *reinterpret_cast<const float4*>(xs + b * K + k0);
+          x1[b] = *reinterpret_cast<const float4*>(xs + b * K + k0 + 4);
+        }
+#pragma unroll
+        for (int rI = 0; rI < RB; ++rI) {
+          if (g0 + rI < n) {   // warp-uniform
+            float w[8];
+            lds8(reinterpret_cast<const WT*>(slot + (size_t)(g0 + rI) * rowbytes) + k0, w);
+#pragma unroll
+            for (int b = 0; b < BT; ++b) {
+              float t = acc[rI][b];
+              t = fmaf(w[0], x0[b].x, t); t = fmaf(w[1], x0[b].y, t); t = fmaf(w[2], x0[b].z, t); t = fmaf(w[3], x0[b].w, t);
+              t = fmaf(w[4], x1[b].x, t); t = fmaf(w[5], x1[b].y, t); t = fmaf(w[6], x1[b].z, t); t = fmaf(w[7], x1[b].w, t);
+              acc[rI][b] = t;
+            }
+          }
         }
       }
-      const float bv = ph.has_bias ? reinterpret_cast<const float*>(slot + kSlotData)[(r & 3) + rr] : 0.f;
-      const int row = r + rr;
 #pragma unroll
-      for (int b = 0; b < BT; ++b) acc[b] = warp_sum(acc[b]);
-      if (ph.mode == EPI_HEAD) {
+      for (int rI = 0; rI < RB; ++rI) {
+        const int rr = g0 + rI;
+        if (rr >= n) break;
+        const float bv = ph.has_bias ? reinterpret_cast<const float*>(slot + kSlotData)[(r & 3) + rr] : 0.f;
+        const int row = r + rr;
+        float sum[BT];
 #pragma unroll
-        for (int b = 0; b < BT; ++b) {
-          best_merge(best[b], acc[b], row);
-          if (cx.logits_out != nullptr && lane == 0 && b < B) cx.logits_out[(size_t)b * cx.V + row] = acc[b];
+        for (int b = 0; b < BT; ++b) sum[b] = warp_sum(acc[rI][b]);
+        if (ph.mode == EPI_HEAD) {
+#pragma unroll
+          for (int b = 0; b < BT; ++b) {
+            best_merge(best[b], sum[b], row);
+            if (cx.logits_out != nullptr && lane == 0 && b < B) cx.logits_out[(size_t)b * cx.V + row] = sum[b];
+          }
+        } else if (lane < B) {
+          float v = 0.f;
+#pragma unroll
+          for (int b = 0; b < BT; ++b) if (lane == b) v = sum[b];
+          v += bv;
+          const int own = lane * kOwnMax + (row - cx.c0);
+          if (ph.mode == EPI_PROJ) { v += cx.hloc[own]; cx.h2loc[own] = v; }
+          else if (ph.mode == EPI_FC) v = gelu_new(v);
+          else if (ph.mode == EPI_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
+          if (ph.dst_plain != nullptr) ph.dst_plain[(size_t)lane * ph.N + row] = v;
+          else if (ph.dst_sys) ll_store_sys(ph.dst_ll + (size_t)lane * ph.N + row, __float_as_uint(v), ph.dst_epoch);
+          else ll_store(ph.dst_ll + (size_t)lane * ph.N + row, v, ph.dst_epoch);
         }
-      } else if (lane < B) {
-        float v = 0.f;
-#pragma unroll
-        for (int b = 0; b < BT; ++b) if (lane == b) v = acc[b];
-        v += bv;
-        const int own = lane * kOwnMax + (row - cx.c0);
-        if (ph.mode == EPI_PROJ) { v += cx.hloc[own]; cx.h2loc[own] = v; }
-        else if (ph.mode == EPI_FC) v = gelu_new(v);
-        else if (ph.mode == EPI_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
-        if (ph.dst_plain != nullptr) ph.dst_plain[(size_t)lane * ph.N + row] = v;
-        else if (ph.dst_sys) ll_store_sys(ph.dst_ll + (size_t)lane * ph.N + row, __float_as_uint(v), ph.dst_epoch);
-        else ll_store(ph.dst_ll + (size_t)lane * ph.N + row, v, ph.dst_epoch);
       }
     }
     __syncwarp();
