@@ -6,10 +6,12 @@
 // Small M (batched decode, short prompts) therefore costs a narrow UMMA_N instead of a mostly
 // empty 128-row tile, and the epilogue's global accesses are coalesced along n.
 //
-// Pipeline: warp 0 = TMA producer (cp.async.bulk.tensor, SWIZZLE_128B tiles, mbarrier
-// complete_tx), warp 1 = TMEM allocator + single-thread tcgen05.mma issuer (tcgen05.commit
-// releases smem stages and finally signals the epilogue), warps 2..5 = epilogue (tcgen05.ld
-// 32x32b, bias / gelu_new / residual, coalesced stores).
+// Persistent, warp-specialised: warp 0 = TMA producer (cp.async.bulk.tensor, SWIZZLE_128B tiles,
+// mbarrier complete_tx), warp 1 = TMEM allocator + single-thread tcgen05.mma issuer
+// (tcgen05.commit releases smem stages and signals the epilogue), warps 2..9 = epilogue
+// (8 warps, tcgen05.ld 32x32b, bias / gelu_new / residual, stores coalesced along n).  The accumulator is
+// double-buffered in TMEM so the epilogue of one tile overlaps the main loop of the next; token
+// tiles are 32, 128 or 256 wide (UMMA_N), decode-sized problems are split along K.
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -26,14 +28,16 @@ namespace {
 constexpr int kBlockN = 128;  // weight rows per CTA  (UMMA M)
 constexpr int kBlockK = 64;   // bf16 elements per k-block = 128 bytes = one swizzle row
 constexpr int kUmmaK = 16;
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;        // two per TMEM lane quarter, each takes half of the columns
+constexpr int kThreads = 64 + kEpiWarps * 32;
 constexpr int kWBytes = kBlockN * kBlockK * 2;  // 16 KB
 
 template <int BM> struct Cfg {
   static constexpr int kABytes = BM * kBlockK * 2;
   static constexpr int kStageBytes = kWBytes + kABytes;
-  static constexpr int kStages = (BM <= 32) ? 8 : (BM <= 64 ? 7 : 6);
-  static constexpr int kTmemCols = BM < 32 ? 32 : BM;
+  static constexpr int kStages = (BM <= 32) ? 8 : (BM <= 128 ? 6 : 4);
+  static constexpr int kAccCols = BM < 32 ? 32 : BM;   // TMEM columns of one accumulator stage
+  static constexpr int kTmemCols = 2 * kAccCols;       // two stages: epilogue of tile i overlaps main loop of tile i+1
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -112,11 +116,13 @@ __host__ __device__ constexpr uint32_t make_idesc(int umma_m, int umma_n) {
 
 template <typename OT> __device__ __forceinline__ void store1(OT* p, float v) { *p = from_f<OT>(v); }
 
+// Persistent: CTA c processes work items c, c + gridDim.x, ...; an item is (output tile, k-split).
+// Items are ordered m-tile fastest, so CTAs running at the same time share a weight tile in L2.
 template <int BM, typename OT>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
                const float* __restrict__ bias, const float* residual, int ldr, OT* out, int ldo, int M, int N, int K,
-               uint32_t flags, float* __restrict__ partial) {
+               uint32_t flags, float* __restrict__ partial, int splits) {
   using C = Cfg<BM>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -124,17 +130,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
   uint8_t* sA = smem + C::kStages * kWBytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
   uint64_t* empty = full + C::kStages;
-  uint64_t* tmem_full = empty + C::kStages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tfull = empty + C::kStages;     // [2] accumulator stage complete (MMA -> epilogue)
+  uint64_t* tempty = tfull + 2;             // [2] accumulator stage drained  (epilogue -> MMA)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * kBlockN, m0 = blockIdx.y * BM;
-  // split-K: gridDim.z CTAs share one output tile; CTA z takes k-blocks [kb0, kb1) and, when
-  // gridDim.z > 1, stores its raw fp32 partial tile to partial[z][m][n] for splitk_epilogue_kernel
+  const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + kBlockN - 1) / kBlockN;
+  const int n_items = m_tiles * n_tiles * splits;
   const int nk_all = (K + kBlockK - 1) / kBlockK;
-  const int kb0 = (int)(((long long)blockIdx.z * nk_all) / gridDim.z);
-  const int kb1 = (int)(((long long)(blockIdx.z + 1) * nk_all) / gridDim.z);
-  const int nk = kb1 - kb0;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
@@ -143,7 +146,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull[s], 1);
+      mbar_init(&tempty[s], kEpiWarps);   // one arrival per epilogue warp
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -157,65 +163,103 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // item -> (tile coordinates, k-block range)
+  auto decode = [&](int w, int& m0, int& n0, int& z, int& kb0, int& nk) {
+    z = w % splits;
+    const int tile = w / splits;
+    m0 = (tile % m_tiles) * BM;
+    n0 = (tile / m_tiles) * kBlockN;
+    kb0 = (int)(((long long)z * nk_all) / splits);
+    nk = (int)(((long long)(z + 1) * nk_all) / splits) - kb0;
+  };
+
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < nk; ++kb) {
-        const int s = kb % C::kStages;
-        const uint32_t ph = (kb / C::kStages) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        mbar_expect_tx(&full[s], C::kStageBytes);
-        tma_load_2d(sW + s * kWBytes, &tmW, (kb0 + kb) * kBlockK, n0, &full[s]);
-        tma_load_2d(sA + s * C::kABytes, &tmA, (kb0 + kb) * kBlockK, m0, &full[s]);
+      uint32_t it = 0;   // smem stage counter across items
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+        int m0, n0, z, kb0, nk;
+        decode(w, m0, n0, z, kb0, nk);
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % C::kStages;
+          const uint32_t ph = (it / C::kStages) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_expect_tx(&full[s], C::kStageBytes);
+          tma_load_2d(sW + s * kWBytes, &tmW, (kb0 + kb) * kBlockK, n0, &full[s]);
+          tma_load_2d(sA + s * C::kABytes, &tmA, (kb0 + kb) * kBlockK, m0, &full[s]);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(kBlockN, BM < 16 ? 16 : BM);
-      for (int kb = 0; kb < nk; ++kb) {
-        const int s = kb % C::kStages;
-        const uint32_t ph = (kb / C::kStages) & 1;
-        mbar_wait(&full[s], ph);
+      uint32_t it = 0, item = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+        int m0, n0, z, kb0, nk;
+        decode(w, m0, n0, z, kb0, nk);
+        const uint32_t as = item & 1;
+        mbar_wait(&tempty[as], ((item >> 1) & 1) ^ 1);   // epilogue has drained this accumulator stage
         tc_fence_after();
-        const uint64_t adesc = make_desc(smem_u32(sW + s * kWBytes));
-        const uint64_t bdesc = make_desc(smem_u32(sA + s * C::kABytes));
+        const uint32_t tmem_d = tmem_base + as * C::kAccCols;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % C::kStages;
+          const uint32_t ph = (it / C::kStages) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint64_t adesc = make_desc(smem_u32(sW + s * kWBytes));
+          const uint64_t bdesc = make_desc(smem_u32(sA + s * C::kABytes));
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          // advance 16 elements = 32 bytes inside the 128-byte swizzle row: +2 in the >>4 address field
-          tc_mma_bf16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // advance 16 elements = 32 bytes inside the 128-byte swizzle row: +2 in the >>4 address field
+            tc_mma_bf16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          }
+          tc_commit(&empty[s]);  // frees the smem stage once these MMAs have read it
         }
-        tc_commit(&empty[s]);  // frees the stage once these MMAs have read it
+        tc_commit(&tfull[as]);   // accumulator complete
       }
-      tc_commit(tmem_full);    // accumulator complete
     }
   } else {
-    // epilogue: warp w may touch TMEM lanes [32*(w%4), 32*(w%4)+32)
+    // epilogue: warp w may touch TMEM lanes [32*(w%4), 32*(w%4)+32); warps 2..5 take the even
+    // 16-column chunks of their quarter, warps 6..9 the odd ones
     const int q = warp & 3;
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    const int n = n0 + q * 32 + lane;
-    const bool n_ok = n < N;
-    const bool split = gridDim.z > 1;
-    const float bv = (!split && bias != nullptr && n_ok) ? bias[n] : 0.f;
+    const int chunk0 = (warp - 2) >> 2;   // 0 or 1
+    const bool split = splits > 1;
     const bool gelu = !split && (flags & GP_EPI_GELU);
-    float* pz = split ? partial + (size_t)blockIdx.z * M * N : nullptr;
+    uint32_t item = 0;
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+      int m0, n0, z, kb0, nk;
+      decode(w, m0, n0, z, kb0, nk);
+      const uint32_t as = item & 1;
+      mbar_wait(&tfull[as], (item >> 1) & 1);
+      tc_fence_after();
+      const int n = n0 + q * 32 + lane;
+      const bool n_ok = n < N;
+      const float bv = (!split && bias != nullptr && n_ok) ? bias[n] : 0.f;
+      float* pz = split ? partial + (size_t)z * M * N : nullptr;
+      const uint32_t tcol = tmem_base + as * C::kAccCols + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-    for (int c0 = 0; c0 < BM; c0 += 16) {
-      if (m0 + c0 >= M) break;  // warp-uniform
-      uint32_t r[16];
-      tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+      for (int c0 = chunk0 * 16; c0 < BM; c0 += 32) {
+        if (m0 + c0 >= M) break;  // warp-uniform
+        uint32_t r[16];
+        tc_ld16(tcol + (uint32_t)c0, r);
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int m = m0 + c0 + j;
-        if (n_ok && m < M) {
-          float v = __uint_as_float(r[j]) + bv;
-          if (split) {
-            pz[(size_t)m * N + n] = v;
-          } else {
-            if (gelu) v = gelu_new(v);
-            if (residual != nullptr) v += residual[(size_t)m * ldr + n];
-            store1(out + (size_t)m * ldo + n, v);
+        for (int j = 0; j < 16; ++j) {
+          const int m = m0 + c0 + j;
+          if (n_ok && m < M) {
+            float v = __uint_as_float(r[j]) + bv;
+            if (split) {
+              pz[(size_t)m * N + n] = v;
+            } else {
+              if (gelu) v = gelu_new(v);
+              if (residual != nullptr) v += residual[(size_t)m * ldr + n];
+              store1(out + (size_t)m * ldo + n, v);
+            }
           }
         }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tempty[as])) : "memory");
       }
     }
   }
@@ -249,6 +293,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
+int g_num_sms = 148;
 std::mutex g_mu;
 std::map<std::tuple<const void*, int, int, int>, CUtensorMap> g_maps;
 
@@ -293,9 +338,10 @@ template <int BM, typename OT>
 cudaError_t launch_t(const CUtensorMap& tw, const CUtensorMap& ta, const float* bias, const float* residual, int ldr,
                      void* out, int ldo, int M, int N, int K, uint32_t flags, int splits, float* partial,
                      cudaStream_t s) {
-  dim3 grid((N + kBlockN - 1) / kBlockN, (M + BM - 1) / BM, splits);
+  const int items = ((N + kBlockN - 1) / kBlockN) * ((M + BM - 1) / BM) * splits;
+  const int grid = items < g_num_sms ? items : g_num_sms;
   gemm_tc_kernel<BM, OT><<<grid, kThreads, Cfg<BM>::kSmemBytes, s>>>(tw, ta, bias, residual, ldr, (OT*)out, ldo, M, N,
-                                                                    K, flags, partial);
+                                                                    K, flags, partial, splits);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess || splits <= 1) return e;
   size_t mn = (size_t)M * N;
@@ -319,6 +365,11 @@ bool gemm_tc_supported(int M, int N, int K) {
 cudaError_t init_gemm_tc() {
   cudaError_t e;
   if ((e = get_encode()) != cudaSuccess) return e;
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0)
+    g_num_sms = sms;
+  if ((e = set_attr<256, float>()) != cudaSuccess) return e;
+  if ((e = set_attr<256, bf16>()) != cudaSuccess) return e;
   if ((e = set_attr<32, float>()) != cudaSuccess) return e;
   if ((e = set_attr<32, bf16>()) != cudaSuccess) return e;
   if ((e = set_attr<128, float>()) != cudaSuccess) return e;
@@ -328,7 +379,7 @@ cudaError_t init_gemm_tc() {
 
 int gemm_tc_splits(int M, int N, int K, size_t partial_floats) {
   // few output tiles (decode-sized M, narrow N): split K so that ~all SMs stream weights
-  const int BM = (M <= 32) ? 32 : 128;
+  const int BM = (M <= 32) ? 32 : (M < 512 ? 128 : 256);
   const int tiles = ((N + kBlockN - 1) / kBlockN) * ((M + BM - 1) / BM);
   const int nk = (K + kBlockK - 1) / kBlockK;
   int s = 148 / tiles;
@@ -344,7 +395,7 @@ cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* 
                            size_t partial_floats) {
   if (!gemm_tc_supported(M, N, K) || lda != K) return cudaErrorInvalidValue;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Wt) & 15)) return cudaErrorInvalidValue;
-  const int BM = (M <= 32) ? 32 : 128;
+  const int BM = (M <= 32) ? 32 : (M < 512 ? 128 : 256);
   CUtensorMap tw, ta;
   cudaError_t e;
   if ((e = tensor_map(Wt, N, K, kBlockN, &tw)) != cudaSuccess) return e;
@@ -354,8 +405,11 @@ cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* 
   if (BM == 32)
     return obf ? launch_t<32, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s)
                : launch_t<32, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s);
-  return obf ? launch_t<128, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s)
-             : launch_t<128, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s);
+  if (BM == 128)
+    return obf ? launch_t<128, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s)
+               : launch_t<128, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s);
+  return obf ? launch_t<256, bf16>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s)
+             : launch_t<256, float>(tw, ta, bias, residual, ldr, out, ldo, M, N, K, flags, splits, partial, s);
 }
 
 }  // namespace gp

@@ -422,16 +422,18 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
     if (lane == 0) mbar_wait(&rg.full[s], phs);   // one waiter per warp
     __syncwarp();
     if (r == r0) cx.stamp();
-    // Row blocking: a warp takes RB = BT consecutive rows, so each x chunk it pulls from shared
-    // memory is used RB times - the x traffic per weight row stays that of batch 1.
-    constexpr int RB = (BT >= 4) ? 2 : BT;   // 4 x 4 accumulators + 32 x registers spill at 128 regs/thread
-    for (int g0 = warp * RB; g0 < n; g0 += kNW * RB) {
+    // A chunk has at most 24 rows for 15 warps: warp w owns rows w and w+15 and walks them together,
+    // so every x chunk it pulls from shared memory is used for both.
+    constexpr int RB = (BT == 1) ? 1 : 2;   // at batch 1 the x traffic is small: one row at a time, deeper unroll
+    static_assert(kMaxRows <= 2 * kNW, "a warp owns at most two rows of a chunk");
+    for (int g0 = warp; g0 < n; g0 += kNW * RB) {
       float acc[RB][BT];
 #pragma unroll
       for (int rI = 0; rI < RB; ++rI)
 #pragma unroll
         for (int b = 0; b < BT; ++b) acc[rI][b] = 0.f;
-#pragma unroll 2
+      constexpr int kUnrollK = (BT == 1) ? 4 : (BT == 2 ? 2 : 1);
+#pragma unroll kUnrollK
       for (int k0 = lane * 8; k0 < K; k0 += 256) {
         float4 x0[BT], x1[BT];
 #pragma unroll
@@ -441,9 +443,9 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
         }
 #pragma unroll
         for (int rI = 0; rI < RB; ++rI) {
-          if (g0 + rI < n) {   // warp-uniform
+          if (g0 + rI * kNW < n) {   // warp-uniform
             float w[8];
-            lds8(reinterpret_cast<const WT*>(slot + (size_t)(g0 + rI) * rowbytes) + k0, w);
+            lds8(reinterpret_cast<const WT*>(slot + (size_t)(g0 + rI * kNW) * rowbytes) + k0, w);
 #pragma unroll
             for (int b = 0; b < BT; ++b) {
               float t = acc[rI][b];
@@ -456,7 +458,7 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
       }
 #pragma unroll
       for (int rI = 0; rI < RB; ++rI) {
-        const int rr = g0 + rI;
+        const int rr = g0 + rI * kNW;
         if (rr >= n) break;
         const float bv = ph.has_bias ? reinterpret_cast<const float*>(slot + kSlotData)[(r & 3) + rr] : 0.f;
         const int row = r + rr;
