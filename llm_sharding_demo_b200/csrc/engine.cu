@@ -228,7 +228,7 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   p.step_clock = clock ? e->step_clock : nullptr;
   const char* trace_path = getenv("GP_MEGA_TRACE");
   const bool trace = trace_path != nullptr && n_steps > 1;
-  const int kTraceCap = 256;
+  const int kTraceCap = 512;
   if (trace) {  // debug aid: per-CTA %globaltimer at every phase boundary of the last step -> raw int64 file
     if (!e->trace) CK(e, cudaMalloc((void**)&e->trace, (size_t)e->num_sms * kTraceCap * sizeof(long long)));
     CK(e, cudaMemsetAsync(e->trace, 0, (size_t)e->num_sms * kTraceCap * sizeof(long long), s));

@@ -143,17 +143,22 @@ __device__ __forceinline__ uint32_t flag_load(const uint32_t* p) {
 // poll one counter each until it reaches its target.  The counters only throttle polling;
 // correctness rests on the per-element epochs, so no fence is needed on either side.
 constexpr int kSub = 8;
+constexpr uint32_t kGateSlack = 1;     // see gate_ctr
 constexpr int kCtrWords = kSub * 32;   // words per exchange buffer id
 __device__ __forceinline__ void ctr_bump(uint32_t* ctr, int producer) {
   asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(ctr + (producer % kSub) * 32) : "memory");
 }
 // target_j = base_j + n_j where n_j = number of producers i < n with i % kSub == j
-__device__ __forceinline__ void gate_ctr(const uint32_t* ctr, const uint32_t* base, uint32_t rounds, int n) {
+// `slack`: open the gate when each counter is within `slack` of its target, i.e. while up to kSub * slack
+// producers are still missing; the readers then spin on exactly the words of those producers (few
+// threads, little traffic) and see them one L2 round trip earlier than via counter + re-read.
+__device__ __forceinline__ void gate_ctr(const uint32_t* ctr, const uint32_t* base, uint32_t rounds, int n,
+                                         uint32_t slack = 0) {
   if ((threadIdx.x >> 5) != 0 || ctr == nullptr) return;
   const int lane = threadIdx.x & 31;
   if (lane < kSub) {
     const uint32_t per_round = (uint32_t)((n - lane + kSub - 1) / kSub);
-    const uint32_t target = base[lane] + rounds * per_round;
+    const uint32_t target = base[lane] + rounds * per_round - (per_round > 4u * slack ? slack : 0u);
     while ((int32_t)(flag_load(ctr + lane * 32) - target) < 0) {}
   }
   __syncwarp();
@@ -173,7 +178,21 @@ struct Ring {
   uint64_t* full;
   uint64_t* empty;
   int n_slots;
-  uint32_t it;  // chunks issued (producer) / consumed (each consumer warp) so far
+  int slot;       // next slot to fill (producer) / to read (each consumer warp)
+  uint32_t par;   // its phase parity: flips every time `slot` wraps
+  __device__ __forceinline__ void advance() {
+    if (++slot == n_slots) { slot = 0; par ^= 1u; }
+  }
+};
+
+// What a CTA needs to know about one kind of phase (0 qkv, 2 proj, 3 fc, 4 proj2, 5 head; 1 = attention
+// has no matrix).  Computed once per launch into shared memory: the divisions behind it would otherwise
+// sit on the dependent path of every one of the ~60 phases of a step.
+struct KindInfo {
+  int r0, r1;   // rows of the [N,K] matrix this CTA owns
+  int rps;      // rows per ring slot
+  int K, N;
+  int pad[3];
 };
 
 // CTA `cta` of G owns rows [r0, r1) of an N-row matrix.  32-bit arithmetic on purpose (64-bit division
@@ -189,36 +208,35 @@ __device__ __forceinline__ int rows_per_slot(int rowbytes) {
 
 // ---- producer: stream this CTA's rows [r0,r1) of W[N,K] (+ their biases) through the ring
 template <typename WT>
-__device__ __forceinline__ void produce_phase(Ring& rg, const void* W, const float* bias, int N, int K, int cta, int G) {
-  int r0, r1;
-  rows_of(cta, G, N, r0, r1);
-  const int rowbytes = K * (int)sizeof(WT);
-  const int rps = rows_per_slot(rowbytes);
+__device__ __forceinline__ void produce_phase(Ring& rg, const void* W, const float* bias, const KindInfo& ki) {
+  const int rowbytes = ki.K * (int)sizeof(WT);
+  const int rps = ki.rps, r1 = ki.r1;
   const uint8_t* base = reinterpret_cast<const uint8_t*>(W);
-  for (int r = r0; r < r1; r += rps) {
+  for (int r = ki.r0; r < r1; r += rps) {
     const int n = min(rps, r1 - r);
-    const int s = rg.it % rg.n_slots;
-    const uint32_t ph = (rg.it / rg.n_slots) & 1;
+    const int s = rg.slot;
     uint8_t* slot = rg.slots + (size_t)s * kSlotBytes;
-    mbar_wait(&rg.empty[s], ph ^ 1);
+    mbar_wait(&rg.empty[s], rg.par ^ 1u);
     // bias window: 16-byte aligned superset [r & ~3, (r + n + 3) & ~3) of the chunk's rows
     const int b0 = r & ~3, b1 = (r + n + 3) & ~3;
     const uint32_t bias_bytes = bias ? (uint32_t)(b1 - b0) * 4u : 0u;
     mbar_expect_tx(&rg.full[s], (uint32_t)(n * rowbytes) + bias_bytes);
     bulk_g2s(slot, base + (size_t)r * rowbytes, (uint32_t)(n * rowbytes), &rg.full[s]);
     if (bias) bulk_g2s(slot + kSlotData, bias + b0, bias_bytes, &rg.full[s]);
-    ++rg.it;
+    rg.advance();
   }
 }
 
 // ======================================================================================
-// Consumer side.  The whole step is ~60 phases that differ only in parameters, so every phase
-// runs through the SAME three non-inlined routines (stage, rows, attention): the hot loop must
-// fit the instruction cache - a fully inlined version was 120 KB of SASS and ran every phase on
-// cold instruction fetches, 5-10x slower than the arithmetic warrants.
+// Consumer side.  A step is ~60 phases that differ only in parameters; each of the five phases of a
+// layer gets its own inlined, constant-propagated copy of the stage / rows routines (~120 KB of SASS
+// in all).  Both alternatives were measured and lost: calling shared routines puts the parameter block
+// on the local-memory stack (with the 227 KB shared-memory carve-out there is no L1 behind it: 2.5x
+// slower), and ONE generic inlined copy driven by run-time parameters (64 KB) costs more per phase in
+// selects and branches than it saves in instruction fetches (ncu: 2.5 % "no instruction" stalls).
 // ======================================================================================
 enum { SRC_LL = 0, SRC_PLAIN = 1, SRC_EMBED = 2 };
-enum { EPI_QKV = 0, EPI_PROJ = 1, EPI_FC = 2, EPI_PROJ2 = 3, EPI_HEAD = 4 };
+enum { EPI_QKV = 0, KIND_ATTN = 1, EPI_PROJ = 2, EPI_FC = 3, EPI_PROJ2 = 4, EPI_HEAD = 5 };   // = kind of the phase
 
 struct Phase {
   // ---- input vector x[B,K]
@@ -240,8 +258,10 @@ template <typename WT> struct Ctx {
   const WT *wte, *wpe;
   int B, H, V, n_pos, G, cta, c0; float eps; float* logits_out;
   long long* trace; int trace_cap; int n_stamp; bool tracing;   // debug: per-CTA clock64 stamps (thread 0)
-  __device__ __forceinline__ void stamp() {
-    if (tracing && threadIdx.x == 0 && n_stamp < trace_cap) trace[n_stamp++] = clock64();
+  // tag = kind * 8 + event (kind of the phase, 7 = step boundary), kept in the top byte
+  __device__ __forceinline__ void stamp(int tag) {
+    if (tracing && threadIdx.x == 0 && n_stamp < trace_cap)
+      trace[n_stamp++] = (long long)(((u64)clock64() & 0x00FFFFFFFFFFFFFFull) | ((u64)tag << 56));
   }
 };
 
@@ -268,7 +288,7 @@ __device__ __forceinline__ void stage_enter(uint32_t* pub_ctr, int pub_idx, cons
                                          uint32_t sentinel_epoch = 0) {
   consumer_sync();
   if (threadIdx.x == 0 && pub_ctr != nullptr) ctr_bump(pub_ctr, pub_idx);
-  gate_ctr(ctr, base, rounds, n_prod);
+  gate_ctr(ctr, base, rounds, n_prod, kGateSlack);
   if (sentinel != nullptr && threadIdx.x == 0) ll_wait_sys(sentinel, sentinel_epoch);   // previous pipeline stage
   consumer_sync();
 }
@@ -316,7 +336,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
     // plain copy: always from a flag-in-data buffer (attention output, GELU output)
     stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, ph.sentinel,
                 ph.sentinel_epoch);
-    cx.stamp();
+    cx.stamp(ph.mode * 8 + 0);
     const int per = (K + kConsumers - 1) / kConsumers;
 #pragma unroll
     for (int b = 0; b < BT; ++b) {
@@ -327,20 +347,29 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
       const u64* src = ph.src_ll + (size_t)b * K;
       if (per <= 2) {
         copy_ll<2>(xs + b * K, src, 0, K, ph.src_epoch);
+      } else if (per <= 7) {
+        copy_ll<7>(xs + b * K, src, 0, K, ph.src_epoch);    // K = 4 * 768: 6.4 words per thread
       } else {
         for (int k0 = 0; k0 < K; k0 += 8 * kConsumers) copy_ll<8>(xs + b * K, src, k0, K, ph.src_epoch);
       }
     }
-    cx.stamp();
+    cx.stamp(ph.mode * 8 + 1);
     consumer_sync();
     return;
   }
+  // element i of a thread is k = tid + 480 i; `i * 480 < K` is uniform over the CTA, so slots a narrow
+  // model never uses (i >= 2 at H = 768) cost one branch instead of their loads and arithmetic
   float v[BT][kLnPer], gg[kLnPer], bb[kLnPer];
 #pragma unroll
   for (int i = 0; i < kLnPer; ++i) {
     const int k = tid + i * kConsumers;
-    gg[i] = (k < K) ? ph.ln_g[k] : 0.f;
-    bb[i] = (k < K) ? ph.ln_b[k] : 0.f;
+    gg[i] = 0.f; bb[i] = 0.f;
+#pragma unroll
+    for (int b = 0; b < BT; ++b) v[b][i] = 0.f;
+    if (i * kConsumers < K) {
+      gg[i] = (k < K) ? ph.ln_g[k] : 0.f;
+      bb[i] = (k < K) ? ph.ln_b[k] : 0.f;
+    }
   }
   // Speculative first read: the CTA that arrives last (the one everybody else waits for) finds all of
   // its input already published, so it skips the counter poll and one barrier; only CTAs that arrive
@@ -353,19 +382,22 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
     stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
                 ph.src_nprod, ph.sentinel, ph.sentinel_epoch);
   }
-  cx.stamp();
+  cx.stamp(ph.mode * 8 + 0);
   unsigned pending = 0;
 #pragma unroll
-  for (int i = 0; i < kLnPer; ++i)
+  for (int i = 0; i < kLnPer; ++i) {
+    if (i * kConsumers < K) {
 #pragma unroll
-    for (int b = 0; b < BT; ++b) {
-      const bool ok = fetch_x(cx, ph, min(b, B - 1), min(tid + i * kConsumers, K - 1), v[b][i]);
-      const bool live = b < B && tid + i * kConsumers < K;
-      if (!live) v[b][i] = 0.f;
-      else if (!ok) pending |= 1u << (b * kLnPer + i);
+      for (int b = 0; b < BT; ++b) {
+        const bool ok = fetch_x(cx, ph, min(b, B - 1), min(tid + i * kConsumers, K - 1), v[b][i]);
+        const bool live = b < B && tid + i * kConsumers < K;
+        if (!live) v[b][i] = 0.f;
+        else if (!ok) pending |= 1u << (b * kLnPer + i);
+      }
     }
+  }
   if (spec && !consumer_all(pending == 0)) {
-    gate_ctr(ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod);
+    gate_ctr(ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, kGateSlack);
     consumer_sync();
   }
   while (pending) {
@@ -377,7 +409,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
           if (fetch_x(cx, ph, b, tid + i * kConsumers, v[b][i])) pending &= ~(1u << (b * kLnPer + i));
         }
   }
-  cx.stamp();
+  cx.stamp(ph.mode * 8 + 1);
   float* redA = cx.red;             // [BT][kNW]
   float* redB = cx.red + BT * kNW;  // [BT][kNW]
 #pragma unroll
@@ -399,9 +431,11 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
     float q = 0.f;
 #pragma unroll
     for (int i = 0; i < kLnPer; ++i) {
-      const int k = tid + i * kConsumers;
-      const float dlt = (k < K) ? v[b][i] - mean[b] : 0.f;
-      q += dlt * dlt;
+      if (i * kConsumers < K) {
+        const int k = tid + i * kConsumers;
+        const float dlt = (k < K) ? v[b][i] - mean[b] : 0.f;
+        q += dlt * dlt;
+      }
     }
     q = warp_sum(q);
     if (l == 0) redB[b * kNW + w] = q;
@@ -416,7 +450,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
 #pragma unroll
     for (int i = 0; i < kLnPer; ++i) {
       const int k = tid + i * kConsumers;
-      if (k < K) xs[b * K + k] = (b < B) ? (v[b][i] - mean[b]) * rstd * gg[i] + bb[i] : 0.f;
+      if (i * kConsumers < K && k < K) xs[b * K + k] = (b < B) ? (v[b][i] - mean[b]) * rstd * gg[i] + bb[i] : 0.f;
     }
   }
   consumer_sync();
@@ -430,33 +464,30 @@ __device__ __forceinline__ void best_merge(Best& a, float v, int i) {
   if (v > a.v || (v == a.v && i < a.i)) { a.v = v; a.i = i; }
 }
 
-// Every warp walks the same chunk sequence; warp w owns rows w, w+15 of each chunk.
+// Every warp walks the same chunk sequence.  Rows are dealt round-robin over the CTA's whole row range
+// (row j of the range belongs to warp j % 15), not per chunk: with 21-row chunks a per-chunk deal gives
+// six warps twice the work of the other nine in every chunk, and the warps only meet at the ring.
 template <typename WT, int BT>
-__device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
+__device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph, const KindInfo& ki) {
   Ring& rg = cx.rg;
-  int r0, r1;
-  rows_of(cx.cta, cx.G, ph.N, r0, r1);
+  const int r0 = ki.r0, r1 = ki.r1, rps = ki.rps;
   const int K = ph.K, B = cx.B;
   const int rowbytes = K * (int)sizeof(WT);
-  const int rps = rows_per_slot(rowbytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float* xs = cx.xs;
   Best best[BT];
 #pragma unroll
   for (int b = 0; b < BT; ++b) { best[b].v = -INFINITY; best[b].i = 0x7fffffff; }
+  int first = warp;   // index in the chunk of this warp's first row
   for (int r = r0; r < r1; r += rps) {
     const int n = min(rps, r1 - r);
-    const int s = rg.it % rg.n_slots;
-    const uint32_t phs = (rg.it / rg.n_slots) & 1;
+    const int s = rg.slot;
     const uint8_t* slot = rg.slots + (size_t)s * kSlotBytes;
-    if (lane == 0) mbar_wait(&rg.full[s], phs);   // one waiter per warp
+    if (lane == 0) mbar_wait(&rg.full[s], rg.par);   // one waiter per warp
     __syncwarp();
-    if (r == r0) cx.stamp();
-    // A chunk has at most 24 rows for 15 warps: warp w owns rows w and w+15 and walks them together,
-    // so every x chunk it pulls from shared memory is used for both.
+    if (r == r0) cx.stamp(ph.mode * 8 + 3);
     constexpr int RB = (BT == 1) ? 1 : 2;   // at batch 1 the x traffic is small: one row at a time, deeper unroll
-    static_assert(kMaxRows <= 2 * kNW, "a warp owns at most two rows of a chunk");
-    for (int g0 = warp; g0 < n; g0 += kNW * RB) {
+    for (int g0 = first; g0 < n; g0 += kNW * RB) {
       float acc[RB][BT];
 #pragma unroll
       for (int rI = 0; rI < RB; ++rI)
@@ -518,7 +549,10 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph) {
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&rg.empty[s]);
-    ++rg.it;
+    rg.advance();
+    // (row index in the range) % 15 == warp: the next chunk starts n rows further on
+    first -= n % kNW;
+    if (first < 0) first += kNW;
   }
   if (ph.mode == EPI_HEAD && lane == 0) {
 #pragma unroll
@@ -591,7 +625,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
   // publish this CTA's own qkv rows; no gate on the other 147 producers: a task needs only the 192
   // words of its head, which 192 threads of 12 CTAs can poll directly without loading L2
   stage_enter(pub_ctr, cx.cta, nullptr, a.base_qkv, a.rounds, cx.G);
-  cx.stamp();
+  cx.stamp(KIND_ATTN * 8 + 0);
   // q, k_new, v_new of this head: 192 values, one per thread, into shared memory
   if (tid < 3 * D) {
     const int which = tid / D, i = tid - which * D;
@@ -606,7 +640,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
     }
   }
   consumer_sync();
-  cx.stamp();
+  cx.stamp(KIND_ATTN * 8 + 1);
   float qv[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) qv[i] = a.qkv_s[l8 * 8 + i];
@@ -648,7 +682,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
     if (t + kGroups <= pos) step(t + kGroups, pk1, pv1);
   }
   __syncwarp();
-  cx.stamp();
+  cx.stamp(KIND_ATTN * 8 + 2);
   // merge the four groups of the warp, then the 15 warps through shared memory
 #pragma unroll
   for (int o = 8; o <= 16; o <<= 1) {
@@ -705,7 +739,8 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   uint64_t* empty = full + kMaxSlots;
   uint32_t* s_base = reinterpret_cast<uint32_t*>(empty + kMaxSlots);            // [64] counter values at launch
   int* s_pos0 = reinterpret_cast<int*>(s_base + 64);                            // [64] cache lengths at launch
-  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_pos0 + 64);              // [L]
+  KindInfo* s_kind = reinterpret_cast<KindInfo*>(s_pos0 + 64);                  // [8] (6 used)
+  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_kind + 8);               // [L]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
@@ -716,6 +751,16 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       mbar_init(&empty[s], kNW);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (tid >= 32 && tid < 38) {
+    const int kind = tid - 32;
+    KindInfo ki;
+    ki.N = (kind == EPI_QKV) ? 3 * H : (kind == EPI_FC) ? F : (kind == EPI_HEAD) ? p.V : H;
+    ki.K = (kind == EPI_PROJ2) ? F : H;
+    rows_of(cta, G, ki.N, ki.r0, ki.r1);
+    ki.rps = rows_per_slot(ki.K * (int)sizeof(WT));
+    ki.pad[0] = ki.pad[1] = ki.pad[2] = 0;
+    s_kind[kind] = ki;
   }
   {  // layer table -> shared memory (pointer chasing through global memory would sit on every phase)
     const int n_words = p.L * (int)(sizeof(MegaLayer) / 8);
@@ -728,16 +773,19 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   if (warp == kNW) {
     // =============================== PRODUCER ===============================
     if (lane == 0) {
-      Ring rg{ring_base, full, empty, p.n_slots, 0u};
+      Ring rg{ring_base, full, empty, p.n_slots, 0, 0u};
       for (int step = 0; step < p.n_steps * p.n_streams; ++step) {
         for (int li = 0; li < p.L; ++li) {
           const MegaLayer& w = s_layers[li];
-          produce_phase<WT>(rg, w.attn_w, w.attn_b, 3 * H, H, cta, G);
-          produce_phase<WT>(rg, w.proj_w, w.proj_b, H, H, cta, G);
-          produce_phase<WT>(rg, w.fc_w, w.fc_b, F, H, cta, G);
-          produce_phase<WT>(rg, w.mproj_w, w.mproj_b, H, F, cta, G);
+#pragma unroll 1
+          for (int kind = 0; kind < 5; ++kind) {
+            if (kind == KIND_ATTN) continue;
+            const void* W = (kind == EPI_QKV) ? w.attn_w : (kind == EPI_PROJ) ? w.proj_w : (kind == EPI_FC) ? w.fc_w : w.mproj_w;
+            const float* bias = (kind == EPI_QKV) ? w.attn_b : (kind == EPI_PROJ) ? w.proj_b : (kind == EPI_FC) ? w.fc_b : w.mproj_b;
+            produce_phase<WT>(rg, W, bias, s_kind[kind]);
+          }
         }
-        if (p.has_head) produce_phase<WT>(rg, p.wte, nullptr, p.V, H, cta, G);
+        if (p.has_head) produce_phase<WT>(rg, p.wte, nullptr, s_kind[EPI_HEAD]);
       }
     }
     return;
@@ -749,16 +797,12 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   cx.trace = p.trace ? p.trace + (size_t)cta * p.trace_cap : nullptr; cx.trace_cap = p.trace_cap; cx.n_stamp = 0;
   cx.tracing = false;
   const int n_items = p.n_steps * p.n_streams;   // item = (round, stream); one decode step of B sequences each
-  auto stamp = [&](int step) {
-    cx.tracing = (p.trace != nullptr && step == n_items - 1);
-    cx.stamp();
-  };
   if (tid < 64) s_pos0[tid] = (tid < p.n_streams * B) ? p.lens[p.slot0 + tid] : 0;
   if (tid < 8) { s_pos[tid] = 0; s_ids[tid] = 0; }
   if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[n_items] = globaltimer();  // start stamp
   consumer_sync();
 
-  cx.rg = Ring{ring_base, full, empty, p.n_slots, 0u};
+  cx.rg = Ring{ring_base, full, empty, p.n_slots, 0, 0u};
   cx.xs = xs; cx.red = red; cx.hloc = hloc; cx.h2loc = h2loc; cx.sbv = sbv; cx.sbi = sbi; cx.s_ids = s_ids; cx.s_pos = s_pos;
   cx.wte = reinterpret_cast<const WT*>(p.wte); cx.wpe = reinterpret_cast<const WT*>(p.wpe);
   cx.B = B; cx.H = H; cx.V = p.V; cx.n_pos = p.n_pos; cx.G = G; cx.cta = cta; cx.eps = p.eps; cx.logits_out = p.logits_out;
@@ -801,7 +845,8 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       else hv = __ldcg(p.hidden_in + (size_t)b * H + col);
       hloc[b * kOwnMax + (col - c0)] = hv;
     }
-    stamp(step);
+    cx.tracing = (p.trace != nullptr && step == n_items - 1);
+    cx.stamp(7 * 8 + 0);
     uint32_t* pub_ctr = nullptr;   // counter block the next stage has to bump for the phase before it
     for (int li = 0; li < p.L; ++li) {
       const MegaLayer& w = s_layers[li];
@@ -823,10 +868,10 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       ph.ln_g = w.ln1_g; ph.ln_b = w.ln1_b; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
       ph.N = 3 * H; ph.has_bias = 1; ph.mode = EPI_QKV; ph.dst_ll = p.qkv_ll; ph.dst_plain = nullptr; ph.dst_epoch = ep + 1u;
       stage_x<WT, BT>(cx, ph);
-      stamp(step);
-      run_rows<WT, BT>(cx, ph);
+      cx.stamp(ph.mode * 8 + 2);
+      run_rows<WT, BT>(cx, ph, s_kind[EPI_QKV]);
       pub_ctr = ctr_of(1);
-      stamp(step);
+      cx.stamp(ph.mode * 8 + 4);
       ph.sentinel = nullptr;
       // ---- P2: attention for the (b, head) tasks of this CTA
       if (cta < B * nh) {
@@ -839,24 +884,24 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
           pub_ctr = nullptr;
         }
       }
-      stamp(step);
+      cx.stamp(KIND_ATTN * 8 + 3);
       // ---- P3: attention c_proj + residual -> h2   (CTAs without an attention task publish qkv here)
       ph.src_kind = SRC_LL; ph.src_ll = p.attn_ll; ph.K = H; ph.src_epoch = ep + 2u;
       ph.src_ctr = ctr_of(2); ph.src_base = base_of(2); ph.src_rounds = rnd; ph.src_nprod = B * nh;
       ph.ln_g = nullptr; ph.ln_b = nullptr; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
       ph.N = H; ph.mode = EPI_PROJ; ph.dst_ll = p.h2_ll; ph.dst_epoch = ep + 3u;
       stage_x<WT, BT>(cx, ph);
-      stamp(step);
-      run_rows<WT, BT>(cx, ph);
-      stamp(step);
+      cx.stamp(ph.mode * 8 + 2);
+      run_rows<WT, BT>(cx, ph, s_kind[EPI_PROJ]);
+      cx.stamp(ph.mode * 8 + 4);
       // ---- P4: ln_2 + c_fc + gelu_new -> act
       ph.src_ll = p.h2_ll; ph.src_epoch = ep + 3u; ph.src_ctr = ctr_of(3); ph.src_base = base_of(3); ph.src_nprod = G;
       ph.ln_g = w.ln2_g; ph.ln_b = w.ln2_b; ph.pub_ctr = ctr_of(3);
       ph.N = F; ph.mode = EPI_FC; ph.dst_ll = p.act_ll; ph.dst_epoch = ep + 4u;
       stage_x<WT, BT>(cx, ph);
-      stamp(step);
-      run_rows<WT, BT>(cx, ph);
-      stamp(step);
+      cx.stamp(ph.mode * 8 + 2);
+      run_rows<WT, BT>(cx, ph, s_kind[EPI_FC]);
+      cx.stamp(ph.mode * 8 + 4);
       // ---- P5: mlp c_proj + residual -> h (or the stage output)
       ph.src_ll = p.act_ll; ph.K = F; ph.src_epoch = ep + 4u; ph.src_ctr = ctr_of(4); ph.src_base = base_of(4);
       ph.ln_g = nullptr; ph.ln_b = nullptr; ph.pub_ctr = ctr_of(4);
@@ -869,10 +914,10 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
         }
       }
       stage_x<WT, BT>(cx, ph);
-      stamp(step);
-      run_rows<WT, BT>(cx, ph);
+      cx.stamp(ph.mode * 8 + 2);
+      run_rows<WT, BT>(cx, ph, s_kind[EPI_PROJ2]);
       pub_ctr = ctr_of(5);   // bumped even when the rows went to hidden_out: counts stay regular
-      stamp(step);
+      cx.stamp(ph.mode * 8 + 4);
     }
     if (p.has_head) {
       // ---- ln_f + lm_head + argmax
@@ -884,8 +929,8 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       ph.N = p.V; ph.has_bias = 0; ph.mode = EPI_HEAD; ph.dst_ll = nullptr; ph.dst_plain = nullptr; ph.dst_epoch = 0;
       ph.dst_sys = 0; ph.sentinel = nullptr; ph.sentinel_epoch = 0;
       stage_x<WT, BT>(cx, ph);
-      stamp(step);
-      run_rows<WT, BT>(cx, ph);
+      cx.stamp(ph.mode * 8 + 2);
+      run_rows<WT, BT>(cx, ph, s_kind[EPI_HEAD]);
       consumer_sync();
       // partials are laid out [b][value|index][cta] so that the readers' loads coalesce
       if (tid < B) {
@@ -894,7 +939,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
         ll_store(p.part_ll + ((size_t)tid * 2 + 0) * kFlagStride + cta, r.v, ep + 6u);
         ll_store_int(p.part_ll + ((size_t)tid * 2 + 1) * kFlagStride + cta, r.i, ep + 6u);
       }
-      stamp(step);
+      cx.stamp(7 * 8 + 2);
       // publish, wait for every CTA's partials, then every CTA reduces them itself (index
       // tie-break => deterministic): every CTA knows the next token without another exchange
       stage_enter(ctr_of(6), cta, ctr_of(6), base_of(6), (uint32_t)step + 1u, G);
@@ -924,7 +969,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
           s_ids[b] = min(max(r.i, 0), p.V - 1);
         }
       }
-      stamp(step);
+      cx.stamp(7 * 8 + 1);
     } else if (pub_ctr != nullptr) {
       consumer_sync();
       if (tid == 0) ctr_bump(pub_ctr, cta);
@@ -956,7 +1001,8 @@ int padded(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : 4); }
 size_t fixed_smem(int BT, int H, int L) {
   return (size_t)BT * 4 * H * 4 /*xs*/ + kNW * 64 * 4 /*part*/ + 2 * kNW * 4 /*pm,pl*/ + (size_t)2 * BT * kNW * 4 /*red*/ +
          (size_t)2 * BT * kOwnMax * 4 /*hloc,h2loc*/ + 3 * 64 * 4 /*qkv_s*/ + (size_t)kNW * BT * 8 /*sbv,sbi*/ +
-         64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + 256 /*ctr base*/ + 256 /*pos0*/ + (size_t)L * sizeof(MegaLayer) + 128;
+         64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + 256 /*ctr base*/ + 256 /*pos0*/ + 8 * sizeof(KindInfo) +
+         (size_t)L * sizeof(MegaLayer) + 128;
 }
 
 }  // namespace
