@@ -173,6 +173,16 @@ __device__ __forceinline__ void lds8(const float* p, float (&v)[8]) {
   v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
 
+// four consecutive weights of a row (8 bytes of bf16 / 16 bytes of fp32)
+__device__ __forceinline__ void lds4(const bf16* p, float (&v)[4]) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  v[0] = bf16lo(u.x); v[1] = bf16hi(u.x); v[2] = bf16lo(u.y); v[3] = bf16hi(u.y);
+}
+__device__ __forceinline__ void lds4(const float* p, float (&v)[4]) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+
 struct Ring {
   uint8_t* slots;
   uint64_t* full;
@@ -464,6 +474,89 @@ __device__ __forceinline__ void best_merge(Best& a, float v, int i) {
   if (v > a.v || (v == a.v && i < a.i)) { a.v = v; a.i = i; }
 }
 
+// This warp's rows of one chunk.  RB = 2: the warp owns two rows (first, first + 15) and walks them together
+// - their loads and FMA chains interleave and every x vector pulled from shared memory serves both.
+// Shared-memory bandwidth is what bounds this loop (15 warps x (1.5 KB of weights + 3 KB of x) per row), so the
+// element-to-lane mapping is the conflict-free one: of every 256-element block a lane takes elements
+// [4 lane, 4 lane + 4) and [128 + 4 lane, 128 + 4 lane + 4) - a quarter-warp then reads 128 contiguous bytes
+// of x per float4 load (8 consecutive floats per lane would be a 2-way bank conflict on every x load).
+template <typename WT, int BT, int RB>
+__device__ __forceinline__ void chunk_rows(Ctx<WT>& cx, const Phase& ph, const uint8_t* slot, int first, int r,
+                                           Best (&best)[BT]) {
+  const int K = ph.K, B = cx.B;
+  const int rowbytes = K * (int)sizeof(WT);
+  const int lane = threadIdx.x & 31;
+  const float* xs = cx.xs;
+  float acc[RB][BT];
+#pragma unroll
+  for (int rI = 0; rI < RB; ++rI)
+#pragma unroll
+    for (int b = 0; b < BT; ++b) acc[rI][b] = 0.f;
+  const WT* wrow[RB];
+#pragma unroll
+  for (int rI = 0; rI < RB; ++rI) wrow[rI] = reinterpret_cast<const WT*>(slot + (size_t)(first + rI * kNW) * rowbytes);
+  constexpr int kUnrollK = (BT * RB == 1) ? 3 : (BT * RB == 2 ? 2 : 1);   // K = 768: exactly 3 trips
+#pragma unroll kUnrollK
+  for (int k0 = lane * 4; k0 < K; k0 += 256) {
+    // K is a multiple of 8 only: in the last block the upper half may lie beyond the row (x counts as 0)
+    const bool hi = k0 + 128 < K;
+    float4 x0[BT], x1[BT];
+#pragma unroll
+    for (int b = 0; b < BT; ++b) {
+      x0[b] = *reinterpret_cast<const float4*>(xs + b * K + k0);
+      x1[b] = hi ? *reinterpret_cast<const float4*>(xs + b * K + k0 + 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int rI = 0; rI < RB; ++rI) {
+      float w0[4], w1[4];
+      lds4(wrow[rI] + k0, w0);
+      lds4(wrow[rI] + (hi ? k0 + 128 : k0), w1);
+#pragma unroll
+      for (int b = 0; b < BT; ++b) {
+        float t = acc[rI][b];
+        t = fmaf(w0[0], x0[b].x, t); t = fmaf(w0[1], x0[b].y, t); t = fmaf(w0[2], x0[b].z, t); t = fmaf(w0[3], x0[b].w, t);
+        t = fmaf(w1[0], x1[b].x, t); t = fmaf(w1[1], x1[b].y, t); t = fmaf(w1[2], x1[b].z, t); t = fmaf(w1[3], x1[b].w, t);
+        acc[rI][b] = t;
+      }
+    }
+  }
+  cx.stamp(ph.mode * 8 + 5);
+  // the RB * BT butterflies are independent: one shuffle level of all of them at a time
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int rI = 0; rI < RB; ++rI)
+#pragma unroll
+      for (int b = 0; b < BT; ++b) acc[rI][b] += __shfl_xor_sync(FULL_MASK, acc[rI][b], o);
+  cx.stamp(ph.mode * 8 + 6);
+#pragma unroll
+  for (int rI = 0; rI < RB; ++rI) {
+    const int rr = first + rI * kNW;
+    const float bv = ph.has_bias ? reinterpret_cast<const float*>(slot + kSlotData)[(r & 3) + rr] : 0.f;
+    const int row = r + rr;
+    if (ph.mode == EPI_HEAD) {
+#pragma unroll
+      for (int b = 0; b < BT; ++b) {
+        best_merge(best[b], acc[rI][b], row);
+        if (cx.logits_out != nullptr && lane == 0 && b < B) cx.logits_out[(size_t)b * cx.V + row] = acc[rI][b];
+      }
+    } else if (lane < B) {
+      float v = 0.f;
+#pragma unroll
+      for (int b = 0; b < BT; ++b) if (lane == b) v = acc[rI][b];
+      v += bv;
+      const int own = lane * kOwnMax + (row - cx.c0);
+      if (ph.mode == EPI_PROJ) { v += cx.hloc[own]; cx.h2loc[own] = v; }
+      else if (ph.mode == EPI_FC) v = gelu_new(v);
+      else if (ph.mode == EPI_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
+      if (ph.dst_plain != nullptr) ph.dst_plain[(size_t)lane * ph.N + row] = v;
+      else if (ph.dst_sys) ll_store_sys(ph.dst_ll + (size_t)lane * ph.N + row, __float_as_uint(v), ph.dst_epoch);
+      else ll_store(ph.dst_ll + (size_t)lane * ph.N + row, v, ph.dst_epoch);
+    }
+  }
+  cx.stamp(ph.mode * 8 + 7);
+}
+
 // Every warp walks the same chunk sequence.  Rows are dealt round-robin over the CTA's whole row range
 // (row j of the range belongs to warp j % 15), not per chunk: with 21-row chunks a per-chunk deal gives
 // six warps twice the work of the other nine in every chunk, and the warps only meet at the ring.
@@ -471,10 +564,7 @@ template <typename WT, int BT>
 __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph, const KindInfo& ki) {
   Ring& rg = cx.rg;
   const int r0 = ki.r0, r1 = ki.r1, rps = ki.rps;
-  const int K = ph.K, B = cx.B;
-  const int rowbytes = K * (int)sizeof(WT);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const float* xs = cx.xs;
   Best best[BT];
 #pragma unroll
   for (int b = 0; b < BT; ++b) { best[b].v = -INFINITY; best[b].i = 0x7fffffff; }
@@ -486,67 +576,10 @@ __device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph, const Kin
     if (lane == 0) mbar_wait(&rg.full[s], rg.par);   // one waiter per warp
     __syncwarp();
     if (r == r0) cx.stamp(ph.mode * 8 + 3);
-    constexpr int RB = (BT == 1) ? 1 : 2;   // at batch 1 the x traffic is small: one row at a time, deeper unroll
-    for (int g0 = first; g0 < n; g0 += kNW * RB) {
-      float acc[RB][BT];
-#pragma unroll
-      for (int rI = 0; rI < RB; ++rI)
-#pragma unroll
-        for (int b = 0; b < BT; ++b) acc[rI][b] = 0.f;
-      constexpr int kUnrollK = (BT == 1) ? 4 : (BT == 2 ? 2 : 1);
-#pragma unroll kUnrollK
-      for (int k0 = lane * 8; k0 < K; k0 += 256) {
-        float4 x0[BT], x1[BT];
-#pragma unroll
-        for (int b = 0; b < BT; ++b) {
-          x0[b] = *reinterpret_cast<const float4*>(xs + b * K + k0);
-          x1[b] = *reinterpret_cast<const float4*>(xs + b * K + k0 + 4);
-        }
-#pragma unroll
-        for (int rI = 0; rI < RB; ++rI) {
-          if (g0 + rI * kNW < n) {   // warp-uniform
-            float w[8];
-            lds8(reinterpret_cast<const WT*>(slot + (size_t)(g0 + rI * kNW) * rowbytes) + k0, w);
-#pragma unroll
-            for (int b = 0; b < BT; ++b) {
-              float t = acc[rI][b];
-              t = fmaf(w[0], x0[b].x, t); t = fmaf(w[1], x0[b].y, t); t = fmaf(w[2], x0[b].z, t); t = fmaf(w[3], x0[b].w, t);
-              t = fmaf(w[4], x1[b].x, t); t = fmaf(w[5], x1[b].y, t); t = fmaf(w[6], x1[b].z, t); t = fmaf(w[7], x1[b].w, t);
-              acc[rI][b] = t;
-            }
-          }
-        }
-      }
-#pragma unroll
-      for (int rI = 0; rI < RB; ++rI) {
-        const int rr = g0 + rI * kNW;
-        if (rr >= n) break;
-        const float bv = ph.has_bias ? reinterpret_cast<const float*>(slot + kSlotData)[(r & 3) + rr] : 0.f;
-        const int row = r + rr;
-        float sum[BT];
-#pragma unroll
-        for (int b = 0; b < BT; ++b) sum[b] = warp_sum(acc[rI][b]);
-        if (ph.mode == EPI_HEAD) {
-#pragma unroll
-          for (int b = 0; b < BT; ++b) {
-            best_merge(best[b], sum[b], row);
-            if (cx.logits_out != nullptr && lane == 0 && b < B) cx.logits_out[(size_t)b * cx.V + row] = sum[b];
-          }
-        } else if (lane < B) {
-          float v = 0.f;
-#pragma unroll
-          for (int b = 0; b < BT; ++b) if (lane == b) v = sum[b];
-          v += bv;
-          const int own = lane * kOwnMax + (row - cx.c0);
-          if (ph.mode == EPI_PROJ) { v += cx.hloc[own]; cx.h2loc[own] = v; }
-          else if (ph.mode == EPI_FC) v = gelu_new(v);
-          else if (ph.mode == EPI_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
-          if (ph.dst_plain != nullptr) ph.dst_plain[(size_t)lane * ph.N + row] = v;
-          else if (ph.dst_sys) ll_store_sys(ph.dst_ll + (size_t)lane * ph.N + row, __float_as_uint(v), ph.dst_epoch);
-          else ll_store(ph.dst_ll + (size_t)lane * ph.N + row, v, ph.dst_epoch);
-        }
-      }
-    }
+    // a chunk holds at most 24 rows: a warp owns none, one or two of them
+    static_assert(kMaxRows <= 2 * kNW, "a warp owns at most two rows of a chunk");
+    if (first + kNW < n) chunk_rows<WT, BT, 2>(cx, ph, slot, first, r, best);
+    else if (first < n) chunk_rows<WT, BT, 1>(cx, ph, slot, first, r, best);
     __syncwarp();
     if (lane == 0) mbar_arrive(&rg.empty[s]);
     rg.advance();
@@ -945,12 +978,27 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       stage_enter(ctr_of(6), cta, ctr_of(6), base_of(6), (uint32_t)step + 1u, G);
       for (int b = warp; b < B; b += kNW) {
         Best r{-INFINITY, 0x7fffffff};
-        for (int g0 = 0; g0 < G; g0 += 32) {
-          const int g = g0 + lane;
-          if (g < G) {
-            const float v = __uint_as_float(ll_wait_bits(p.part_ll + ((size_t)b * 2 + 0) * kFlagStride + g, ep + 6u));
-            const int i = (int)ll_wait_bits(p.part_ll + ((size_t)b * 2 + 1) * kFlagStride + g, ep + 6u);
-            best_merge(r, v, i);
+        // the loads of a lane go out in batches of 2 x 4 before the first one is checked (they were 10
+        // serial round trips); 148 CTAs need two batches
+        const u64* pv = p.part_ll + ((size_t)b * 2 + 0) * kFlagStride;
+        const u64* pi = p.part_ll + ((size_t)b * 2 + 1) * kFlagStride;
+#pragma unroll 1
+        for (int j0 = 0; j0 < G; j0 += 128) {
+          u64 wv[4], wi[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int g = min(j0 + j * 32 + lane, G - 1);
+            wv[j] = ll_load(pv + g);
+            wi[j] = ll_load(pi + g);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int g = j0 + j * 32 + lane;
+            if (g < G) {
+              if ((uint32_t)(wv[j] >> 32) != ep + 6u) wv[j] = ll_wait_bits(pv + g, ep + 6u);
+              if ((uint32_t)(wi[j] >> 32) != ep + 6u) wi[j] = ll_wait_bits(pi + g, ep + 6u);
+              best_merge(r, __uint_as_float((uint32_t)wv[j]), (int)(uint32_t)wi[j]);
+            }
           }
         }
 #pragma unroll

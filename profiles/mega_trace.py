@@ -13,7 +13,7 @@ raw = np.fromfile(sys.argv[1], dtype=np.uint64).reshape(-1, CAP)
 mhz = float(sys.argv[2]) if len(sys.argv) > 2 else 1965.0
 n_attn = int(sys.argv[3]) if len(sys.argv) > 3 else 12
 PH = {0: "qkv", 1: "attn", 2: "proj", 3: "fc", 4: "proj2", 5: "head", 7: "step"}
-EV = {0: "enter", 1: "x-ok", 2: "staged", 3: "w-full", 4: "rows-done"}
+EV = {0: "enter", 1: "x-ok", 2: "staged", 3: "w-full", 4: "rows-done", 5: "dot", 6: "reduced", 7: "stored"}
 
 
 def name(tag):
