@@ -131,6 +131,18 @@ int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, in
 int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t P, int32_t n_new,
                 int32_t* out_ids_host, float* timings_ms_host);
 
+/* Token selection.  Default: greedy.  temperature > 0 and top_k >= 1 switch the engine
+ * to the reference coordinator's sampler (server.py:187-205, temperature 0.6 / top_k 40 there):
+ * logits / temperature -> top-k (ties: lower token id first) -> softmax over the k values -> one
+ * multinomial draw.  The reference draws from torch's unseeded global generator; here the draw is
+ * a pure function of (seed, KV slot of the sequence, position of the new token) - Philox4x32-10,
+ * key = seed, counter = (position, slot, 0, 0) - so a request is reproducible and independent of
+ * batch composition.  Applies to gp_stage_prefill / gp_stage_decode / gp_generate on a stage with
+ * the lm_head; sampled decode steps run the per-op kernels (the persistent kernel fuses the greedy
+ * argmax), and gp_pipeline_decode refuses while the sampler is on.  temperature <= 0 or
+ * top_k <= 0 restores greedy.  top_k <= 64. */
+int gp_set_sampler(gp_engine* e, float temperature, int32_t top_k, uint64_t seed);
+
 /* ---- stage boundary on the device (replaces the HTTP/JSON hops of server.py:172-181).
  * One process per GPU.  Every stage owns an "inbox" in its HBM; the stage before it writes the
  * hidden state of each decode step straight into that inbox over NVLink (the last stage writes
@@ -194,6 +206,11 @@ int gp_op_attn_decode(const float* q, const void* kcache, const void* vcache, co
  * [hf] modeling_gpt2.py:185-191); out `dtype` [B,T,H]. */
 int gp_op_attn_prefill(const void* qkv, void* out, int32_t B, int32_t T, int32_t nh, int32_t d,
                        int32_t dtype, void* stream);
+
+/* A10 (server.py:187-205), sampled: one token per row of logits fp32 [B,V] (row stride V) ->
+ * ids_out int32 [B].  Row b draws with counter (position, row0 + b); see gp_set_sampler. */
+int gp_op_sample_topk(const float* logits, int32_t B, int32_t V, float temperature, int32_t top_k,
+                      uint64_t seed, int32_t row0, int32_t position, int32_t* ids_out, void* stream);
 
 /* K8+K9: ln_f, tied lm_head and greedy argmax fused (server.py:101-102,187-205 with greedy
  * selection); lowest index wins ties.  x fp32 [B,H]; wte `dtype` [V,H]; ids_out int32 [B];

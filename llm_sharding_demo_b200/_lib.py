@@ -45,6 +45,7 @@ SIGNATURES = {
     "gp_stage_prefill": (C.c_int, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _P, _P]),
     "gp_stage_decode": (C.c_int, [_P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "gp_generate": (C.c_int, [_P, _P, _I, _I, _I, _P, _P]),
+    "gp_set_sampler": (C.c_int, [_P, _F, _I, C.c_uint64]),
     "gp_last_launch_count": (C.c_int64, [_P]),
     "gp_comm_export": (C.c_int, [_P, _P]),
     "gp_comm_connect": (C.c_int, [_P, _P]),
@@ -56,6 +57,7 @@ SIGNATURES = {
     "gp_op_attn_decode": (C.c_int, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "gp_op_attn_prefill": (C.c_int, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "gp_lmhead_scratch_bytes": (C.c_int64, [_I, _I]),
+    "gp_op_sample_topk": (C.c_int, [_P, _I, _I, _F, _I, C.c_uint64, _I, _I, _P, _P]),
     "gp_op_lmhead_argmax": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _I, _P]),
     "gp_op_lmhead_argmax_static": (C.c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _I, _P]),
 }

@@ -49,7 +49,7 @@ struct gp_engine {
   float* hlast = nullptr;   // [max_batch, H]
   float* splitk = nullptr;  // split-K partial tiles of the tcgen05 GEMM (decode-sized M)
   size_t splitk_floats = 0;
-  float* logits_ws = nullptr;  // [max_batch, V] logits of the GEMM-path lm_head
+  float* logits_ws = nullptr;  // [max_batch, V] logits of the GEMM-path lm_head / input of the sampling kernel
   void* lm_scratch = nullptr;
   float* stage = nullptr;
   size_t stage_floats = 0;
@@ -59,7 +59,12 @@ struct gp_engine {
   int32_t* mailbox = nullptr;  // [max_batch] next token ids
   int seq_stride = 0;
   cudaStream_t stream = nullptr;
-  std::map<int, cudaGraphExec_t> decode_graphs;  // keyed by batch
+  std::map<int, cudaGraphExec_t> decode_graphs;  // keyed by batch (+ kSampledKey when the sampler is on)
+  // token selection: greedy (default) or the reference's temperature / top-k / multinomial (gp_set_sampler)
+  bool sampler_on = false;
+  float sampler_temperature = 1.f;
+  int sampler_top_k = 0;
+  uint64_t sampler_seed = 0;
   std::map<int, int64_t> decode_graph_launches;
   std::vector<cudaEvent_t> events;
   // persistent decode kernel
@@ -134,6 +139,8 @@ cudaError_t gemm(gp_engine* e, const void* A, int lda, const void* Wt, const flo
 }
 
 // ln_f + lm_head + argmax over rows x[B,H] in chunks of kGemvMaxBatch
+constexpr int kSampledKey = 1 << 20;
+
 int run_lm_head(gp_engine* e, const float* x, int ldx, int B, int slot0, float* logits, int32_t* next_ids,
                 int32_t* lens, int32_t* seq, cudaStream_t s) {
   for (int c = 0; c < B; c += kGemvMaxBatch) {
@@ -153,6 +160,21 @@ int run_lm_head(gp_engine* e, const float* x, int ldx, int B, int slot0, float* 
   return GP_OK;
 }
 
+// ln_f + lm_head + token selection (+ bookkeeping when `lens` is given) for rows x[B,H]: greedy argmax fused into
+// the lm_head kernel, or - sampler on - logits into the workspace followed by the sampling kernel.
+// fixed_pos: position of the new token when `lens` is NULL (prefill: T).
+int select_tokens(gp_engine* e, const float* x, int ldx, int B, int slot0, float* logits, int32_t* next_ids,
+                  int32_t* lens, int32_t* seq, int fixed_pos, cudaStream_t s) {
+  if (!e->sampler_on) return run_lm_head(e, x, ldx, B, slot0, logits, next_ids, lens, seq, s);
+  float* lg = logits ? logits : e->logits_ws;
+  int32_t* ids = next_ids ? next_ids : e->mailbox;
+  int r = run_lm_head(e, x, ldx, B, slot0, lg, ids, nullptr, nullptr, s);   // its argmax is overwritten below
+  if (r != GP_OK) return r;
+  LAUNCH(e, launch_sample_topk(lg, e->V, B, e->V, e->sampler_temperature, e->sampler_top_k, e->sampler_seed, slot0,
+                               fixed_pos, ids, lens, slot0, seq, e->seq_stride, s));
+  return GP_OK;
+}
+
 int check_ready(gp_engine* e) {
   if (e->loaded.size() != e->required.size()) {
     for (auto& n : e->required)
@@ -166,7 +188,8 @@ int check_ready(gp_engine* e) {
 }
 
 bool use_mega(const gp_engine* e, int B) {
-  return !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms);
+  // the persistent kernel fuses the greedy argmax; sampled decoding runs the per-op kernels
+  return !e->sampler_on && !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms);
 }
 
 int upload_mega_layers(gp_engine* e) {
@@ -298,7 +321,7 @@ int prefill_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B
   if (next_ids || seq_for_generate || (logits && !logits_all)) {
     LAUNCH(e, launch_gather_last(e->h, e->hlast, B, T, H, s));
     // generate: the first new token goes to seq[b][len] with len (= T) unchanged
-    r = run_lm_head(e, e->hlast, H, B, slot0, (logits && !logits_all) ? logits : nullptr, next_ids, nullptr, nullptr, s);
+    r = select_tokens(e, e->hlast, H, B, slot0, (logits && !logits_all) ? logits : nullptr, next_ids, nullptr, nullptr, T, s);
     if (r != GP_OK) return r;
   }
   return GP_OK;
@@ -372,16 +395,20 @@ int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
       LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, e->h, H, dst, H, B, H, F, 0u, s));
     }
   }
-  if (c.has_head && !use_gemv && e->logits_ws != nullptr && gemm_tc_supported(B, e->V, H)) {
+  if (c.has_head && !use_gemv && tc_ok && e->logits_ws != nullptr && gemm_tc_supported(B, e->V, H)) {
     // batched decode: ln_f -> tcgen05 GEMM over the tied head -> per-row argmax (+ bookkeeping)
     float* lg = logits ? logits : e->logits_ws;
     LAUNCH(e, launch_layernorm(e->h, H, e->lnf_g, e->lnf_b, e->xa, true, B, H, c.ln_eps, s));
     LAUNCH(e, gemm(e, e->xa, H, e->wte, nullptr, nullptr, 0, lg, e->V, B, e->V, H, 0u, s));
-    LAUNCH(e, launch_argmax_rows(lg, e->V, B, e->V, next_ids ? next_ids : e->mailbox, e->lens, slot0, seq,
-                                 e->seq_stride, s));
+    if (e->sampler_on)
+      LAUNCH(e, launch_sample_topk(lg, e->V, B, e->V, e->sampler_temperature, e->sampler_top_k, e->sampler_seed, slot0, 0,
+                                   next_ids ? next_ids : e->mailbox, e->lens, slot0, seq, e->seq_stride, s));
+    else
+      LAUNCH(e, launch_argmax_rows(lg, e->V, B, e->V, next_ids ? next_ids : e->mailbox, e->lens, slot0, seq,
+                                   e->seq_stride, s));
   } else if (c.has_head) {
     // the last CTA of the (last) lm_head launch advances the cache lengths and appends to seq
-    r = run_lm_head(e, e->h, H, B, slot0, logits, next_ids, e->lens, seq, s);
+    r = select_tokens(e, e->h, H, B, slot0, logits, next_ids, e->lens, seq, 0, s);
     if (r != GP_OK) return r;
   } else {
     LAUNCH(e, launch_set_lens(e->lens, slot0, B, 1, 1, s));
@@ -501,8 +528,8 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
     e->splitk_floats = (size_t)8 * 256 * (size_t)(F > V ? F : (cfg->has_head ? V : F));
     if (e->splitk_floats > ((size_t)48 << 20)) e->splitk_floats = (size_t)48 << 20;   // 192 MB cap
     TRY(alloc((void**)&e->splitk, e->splitk_floats * 4));
-    if (cfg->has_head) TRY(alloc((void**)&e->logits_ws, MB * V * 4));
   }
+  if (cfg->has_head) TRY(alloc((void**)&e->logits_ws, MB * V * 4));   // GEMM-path lm_head and the sampler
   TRY(alloc((void**)&e->seq, MB * (size_t)e->seq_stride * sizeof(int32_t)));
   TRY(alloc((void**)&e->prompt, MB * (size_t)cfg->n_positions * sizeof(int32_t)));
   TRY(alloc((void**)&e->mailbox, MB * sizeof(int32_t)));
@@ -637,6 +664,31 @@ int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, in
   return decode_impl(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, nullptr, (cudaStream_t)stream);
 }
 
+int gp_set_sampler(gp_engine* e, float temperature, int32_t top_k, uint64_t seed) {
+  if (!e) return GP_EINVAL;
+  if (!(temperature > 0.f) || top_k <= 0) {   // greedy
+    e->sampler_on = false;
+  } else {
+    if (top_k > kMaxTopK) { set_err(e, "gp_set_sampler: top_k %d exceeds the supported maximum of %d", top_k, kMaxTopK); return GP_EINVAL; }
+    if (!e->cfg.has_head) { set_err(e, "gp_set_sampler: this stage has no lm_head"); return GP_EINVAL; }
+    e->sampler_on = true;
+    e->sampler_temperature = temperature;
+    e->sampler_top_k = top_k;
+    e->sampler_seed = seed;
+  }
+  // captured decode steps carry the sampler's parameters as kernel arguments
+  for (auto it = e->decode_graphs.begin(); it != e->decode_graphs.end();) {
+    if (it->first >= kSampledKey) {
+      cudaGraphExecDestroy(it->second);
+      e->decode_graph_launches.erase(it->first);
+      it = e->decode_graphs.erase(it);
+    } else {
+      ++it;
+    }
+  }
+  return GP_OK;
+}
+
 int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t P, int32_t n_new,
                 int32_t* out_ids_host, float* timings_ms_host) {
   if (!e || !prompt_ids_host || !out_ids_host) { set_err(e, "gp_generate: NULL argument"); return GP_EINVAL; }
@@ -689,7 +741,8 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
     cudaGraphExec_t exec = nullptr;
     int64_t per_step = 0;
     if (use_graph) {
-      auto it = e->decode_graphs.find(B);
+      const int gkey = B + (e->sampler_on ? kSampledKey : 0);
+      auto it = e->decode_graphs.find(gkey);
       if (it == e->decode_graphs.end()) {
         const int64_t before = e->launches;
         CK(e, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
@@ -702,11 +755,11 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
         e->launches = before;
         CK(e, cudaGraphInstantiate(&exec, g, 0));
         cudaGraphDestroy(g);
-        e->decode_graphs[B] = exec;
-        e->decode_graph_launches[B] = per_step;
+        e->decode_graphs[gkey] = exec;
+        e->decode_graph_launches[gkey] = per_step;
       } else {
         exec = it->second;
-        per_step = e->decode_graph_launches[B];
+        per_step = e->decode_graph_launches[gkey];
       }
     }
     for (int i = 0; i < steps; ++i) {
@@ -785,6 +838,7 @@ int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds,
   }
   if (!e->inbox || !e->peer_inbox) { set_err(e, "gp_pipeline_decode: stage boundary not connected (gp_comm_export / gp_comm_connect)"); return GP_ESTATE; }
   if (c.has_embed && (!first_ids || !tokens_out)) { set_err(e, "gp_pipeline_decode: stage 0 needs first_ids and tokens_out"); return GP_EINVAL; }
+  if (e->sampler_on) { set_err(e, "gp_pipeline_decode: the device-resident pipeline selects greedily; sampled decoding runs per step (gp_stage_decode)"); return GP_ESTATE; }
   if (!use_mega(e, B)) { set_err(e, "gp_pipeline_decode: shape outside the persistent kernel's envelope (B<=4, head_dim 64)"); return GP_EINVAL; }
   CK(e, cudaSetDevice(c.device));
   int r = check_ready(e);
@@ -897,6 +951,18 @@ int gp_op_attn_prefill(const void* qkv, void* out, int32_t B, int32_t T, int32_t
                        void* stream) {
   if (!qkv || !out) { set_err(nullptr, "gp_op_attn_prefill: NULL argument"); return GP_EINVAL; }
   OPCK(launch_attn_prefill(qkv, out, B, T, nh, d, dtype, (cudaStream_t)stream));
+  return GP_OK;
+}
+
+int gp_op_sample_topk(const float* logits, int32_t B, int32_t V, float temperature, int32_t top_k, uint64_t seed,
+                      int32_t row0, int32_t position, int32_t* ids_out, void* stream) {
+  if (!logits || !ids_out || B <= 0 || V <= 0) { record_error("gp_op_sample_topk: bad argument"); return GP_EINVAL; }
+  if (!(temperature > 0.f) || top_k <= 0 || top_k > kMaxTopK) {
+    record_error("gp_op_sample_topk: temperature must be > 0 and 1 <= top_k <= 64");
+    return GP_EINVAL;
+  }
+  OPCK(launch_sample_topk(logits, V, B, V, temperature, top_k, seed, row0, position, ids_out, nullptr, 0, nullptr, 0,
+                          (cudaStream_t)stream));
   return GP_OK;
 }
 

@@ -8,6 +8,7 @@
 namespace gp {
 
 constexpr int kGemvMaxBatch = 8;        // rows one GEMV launch carries
+constexpr int kMaxTopK = 64;            // candidates the sampling kernel can hold (the reference uses 40)
 constexpr int kGemvMaxSmem = 200 * 1024;  // bytes of x staged in shared memory
 constexpr int kLmheadMaxGrid = 1184;    // 148 SMs x 8 CTAs
 constexpr int kLmheadScratchHeader = 256;
@@ -131,6 +132,11 @@ cudaError_t launch_gemm_tc(const void* A, int lda, const void* Wt, const float* 
                            int ldr, void* out, int ldo, int M, int N, int K, uint32_t flags, cudaStream_t s,
                            float* partial = nullptr, size_t partial_floats = 0);
 // per-row argmax of fp32 logits [B,V] (lowest index wins ties) + the decode bookkeeping of the lm_head kernel
+// temperature / top-k / multinomial selection of server.py:187-205 (k_sample.cu); `lens`, `seq` as in launch_argmax_rows,
+// the draw depends on (seed, row0 + b, position of the new token) only; position = lens + 1, or fixed_pos when lens is NULL
+cudaError_t launch_sample_topk(const float* logits, int ldl, int B, int V, float temperature, int top_k, uint64_t seed,
+                               int row0, int fixed_pos, int32_t* ids_out, int32_t* lens, int slot0, int32_t* seq,
+                               int seq_stride, cudaStream_t s);
 cudaError_t launch_argmax_rows(const float* logits, int ldl, int B, int V, int32_t* ids_out, int32_t* lens, int slot0,
                                int32_t* seq, int seq_stride, cudaStream_t s);
 

@@ -81,6 +81,12 @@ class StageEngine:
     def kv_reset(self, slot: int = -1):
         check(self.lib.gp_kv_reset(self._h, slot, _stream_ptr(self.device)), self._h)
 
+    def set_sampler(self, temperature: float = 0.0, top_k: int = 0, seed: int = 0):
+        """Token selection of this stage: greedy (default, also temperature <= 0 or top_k <= 0) or the
+        reference's temperature / top-k / multinomial (server.py:187-205 uses 0.6 / 40).  The draw
+        depends on (seed, KV slot, position of the new token) only."""
+        check(self.lib.gp_set_sampler(self._h, float(temperature), int(top_k), int(seed) & (2**64 - 1)), self._h)
+
     def kv_lengths(self):
         buf = (C.c_int32 * self.max_batch)()
         check(self.lib.gp_kv_lengths(self._h, buf, self.max_batch, _stream_ptr(self.device)), self._h)
@@ -148,7 +154,7 @@ class StageEngine:
         return out
 
     def generate(self, prompt_ids: torch.Tensor, n_new: int, timings: bool = False):
-        """Greedy decode on a single-stage engine. prompt_ids: CPU int32 [B,P] (pinned memory
+        """Decode on a single-stage engine (greedy unless set_sampler switched it). prompt_ids: CPU int32 [B,P] (pinned memory
         avoids a staging copy).  Returns CPU int32 [B,P+n_new] (+ timings dict)."""
         assert prompt_ids.device.type == "cpu" and prompt_ids.dtype == torch.int32 and prompt_ids.dim() == 2
         prompt_ids = prompt_ids.contiguous()

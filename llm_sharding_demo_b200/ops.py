@@ -100,6 +100,19 @@ def lmhead_argmax(x, gamma, beta, wte, eps=1e-5, want_logits=False, scratch=None
     return (ids, logits) if want_logits else ids
 
 
+def sample_topk(logits, temperature, top_k, seed, row0=0, position=0):
+    """The reference coordinator's token selection (server.py:187-205) on fp32 logits [B,V]:
+    logits / temperature -> top-k -> softmax -> one draw per row; row b draws with the Philox
+    counter (position, row0 + b) under key `seed`.  Returns int32 ids [B]."""
+    lib = load_library()
+    assert logits.dtype == torch.float32 and logits.dim() == 2 and logits.is_contiguous()
+    B, V = logits.shape
+    ids = torch.empty((B,), dtype=torch.int32, device=logits.device)
+    check(lib.gp_op_sample_topk(_p(logits), B, V, float(temperature), int(top_k), int(seed) & (2**64 - 1), int(row0),
+                                int(position), _p(ids), _s(logits)))
+    return ids
+
+
 def lmhead_argmax_static(x, gamma, beta, wte, eps=1e-5, want_logits=False):
     """ln_f + lm_head + argmax for callers that cannot allocate device memory: like
     `lmhead_argmax` but the kernel's cross-CTA scratch is a fixed array inside the library, so

@@ -5,10 +5,13 @@ Same three routes, request bodies, defaults, env vars and role-gate behaviour:
   POST /forward_b  {"hidden_states":[B][T][H]}    -> {"logits":[B][T][V]}                (server.py:143-151)
   POST /generate   {"prompt":str,"max_new_tokens":int=20} -> {"generated":str}           (server.py:154-210)
 Env: MODEL_ID, SHARD_ROLE (a|b|coordinator), SPLIT_AT, SHARD_A_SERVICE, SHARD_B_SERVICE, SHARD_PORT
-(server.py:20-25).  New optional env: GP_DTYPE (bf16|f32), GP_SEED, GP_COORD_MODE (device|http).
+(server.py:20-25).  New optional env: GP_DTYPE (bf16|f32), GP_SEED, GP_COORD_MODE (device|http),
+GP_SAMPLING (greedy|reference), GP_SAMPLE_SEED.
 
 Differences, all deliberate:
-  * selection is greedy (BASELINE.json north_star) instead of temperature/top-k sampling;
+  * selection is greedy by default (BASELINE.json north_star); GP_SAMPLING=reference restores the
+    reference's temperature 0.6 / top-k 40 / multinomial selection (server.py:187-205), seeded: request n
+    of a process draws with seed GP_SAMPLE_SEED + n, so a restarted server replays its answers;
   * a coordinator that has a GPU runs the whole loop on the device (`gp_generate`); with
     GP_COORD_MODE=http it drives /forward and /forward_b of remote shards exactly like the
     reference, so unmodified reference shards or coordinators interoperate;
@@ -74,7 +77,12 @@ def read_env(env=None) -> Dict:
         "GP_DTYPE": env.get("GP_DTYPE", "bf16"),
         "GP_SEED": int(env.get("GP_SEED", "0")),
         "GP_COORD_MODE": env.get("GP_COORD_MODE", "device"),
+        "GP_SAMPLING": env.get("GP_SAMPLING", "greedy").lower(),
+        "GP_SAMPLE_SEED": int(env.get("GP_SAMPLE_SEED", "0")),
     }
+
+
+REF_TEMPERATURE, REF_TOP_K = 0.6, 40   # server.py:187-188
 
 
 def validate_split(dims: W.GPT2Dims, split_at: int):
@@ -99,8 +107,11 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
     dtype = GP_BF16 if cfg["GP_DTYPE"] == "bf16" else GP_F32
     print("Starting server role:", role, "model:", cfg["MODEL_ID"])
 
+    if cfg["GP_SAMPLING"] not in ("greedy", "reference"):
+        raise ValueError(f"GP_SAMPLING={cfg['GP_SAMPLING']!r} must be 'greedy' or 'reference'")
+    sampled = cfg["GP_SAMPLING"] == "reference"
     lock = threading.Lock()   # an engine handle is not re-entrant; handlers run on a thread pool
-    state = {"engine": None}
+    state = {"engine": None, "requests": 0}
 
     def engine():
         if state["engine"] is None:
@@ -181,6 +192,9 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
             import requests
             post = http_post or requests.post
             ids = list(input_ids)
+            with lock:
+                state["requests"] += 1
+                gen = torch.Generator().manual_seed(cfg["GP_SAMPLE_SEED"] + state["requests"] - 1)
             for _ in range(n_new):
                 url_a = f"http://{cfg['SHARD_A_SERVICE']}:{cfg['SHARD_PORT']}/forward"
                 resp = post(url_a, json={"input_ids": ids}, timeout=30)
@@ -190,10 +204,18 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
                 resp2 = post(url_b, json={"hidden_states": hidden}, timeout=30)
                 resp2.raise_for_status()
                 last = torch.tensor(resp2.json()["logits"][0][-1], dtype=torch.float32)
-                ids.append(int(torch.argmax(last)))
+                if sampled:   # server.py:190-205 verbatim in meaning, with a seeded generator
+                    vals, idx = torch.topk(last / REF_TEMPERATURE, min(REF_TOP_K, last.numel()))
+                    probs = torch.softmax(vals, dim=-1)
+                    ids.append(int(idx[torch.multinomial(probs, 1, generator=gen)]))
+                else:
+                    ids.append(int(torch.argmax(last)))
             return {"generated": tokenizer.decode(ids, skip_special_tokens=True)}
         with lock:
             eng = engine()
+            state["requests"] += 1
+            if sampled:
+                eng.set_sampler(REF_TEMPERATURE, min(REF_TOP_K, dims.vocab_size), cfg["GP_SAMPLE_SEED"] + state["requests"] - 1)
             out = eng.generate(torch.tensor([input_ids], dtype=torch.int32), n_new)
         return {"generated": tokenizer.decode(out[0].tolist(), skip_special_tokens=True)}
 

@@ -25,6 +25,7 @@ from dataclasses import dataclass, asdict
 from typing import Dict, List, Optional, Tuple
 
 import torch
+import torch.nn.functional as F
 
 Weights = Dict[str, torch.Tensor]
 
@@ -266,6 +267,93 @@ def greedy_select(last_logits: torch.Tensor) -> torch.Tensor:
     argmax and the positive temperature (0.6) does not move it.  Ties -> lowest index
     (torch.argmax on CPU returns the first maximum)."""
     return torch.argmax(last_logits, dim=-1)
+
+
+# --------------------------------------------------------------------------- sampled selection
+_PHILOX_M0, _PHILOX_M1 = 0xD2511F53, 0xCD9E8D57
+_PHILOX_W0, _PHILOX_W1 = 0x9E3779B9, 0xBB67AE85
+
+
+def philox4x32_10(counter, key):
+    """Philox4x32 with 10 rounds (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as
+    1, 2, 3", SC'11).  counter: 4 words, key: 2 words -> 4 words.  Pinned by the Random123
+    known-answer vectors in tests/test_oracle.py."""
+    c = [int(x) & 0xFFFFFFFF for x in counter]
+    k = [int(x) & 0xFFFFFFFF for x in key]
+    for _ in range(10):
+        p0, p1 = _PHILOX_M0 * c[0], _PHILOX_M1 * c[2]
+        c = [(p1 >> 32) ^ c[1] ^ k[0], p1 & 0xFFFFFFFF, (p0 >> 32) ^ c[3] ^ k[1], p0 & 0xFFFFFFFF]
+        k = [(k[0] + _PHILOX_W0) & 0xFFFFFFFF, (k[1] + _PHILOX_W1) & 0xFFFFFFFF]
+    return c
+
+
+def topk_probs(last_logits: torch.Tensor, temperature: float, top_k: int):
+    """`server.py:187-199` for one logits row [V]: `logits / temperature`, `torch.topk` (sorted),
+    `softmax` over the k values.  Returns (token ids [k], probabilities [k]) in the reference's
+    order; ties between equal logits resolve to the lower token id (torch leaves that unspecified)."""
+    x = last_logits.to(torch.float32) / temperature
+    kth = torch.topk(x, top_k).values[-1]
+    above = torch.nonzero(x > kth).flatten()
+    equal = torch.nonzero(x == kth).flatten()[: top_k - above.numel()]   # ascending ids: the lower ones
+    idx = torch.cat([above, equal]).sort().values
+    idx = idx[torch.sort(x[idx], descending=True, stable=True).indices]   # value desc, id asc among equals
+    probs = F.softmax(x[idx], dim=-1)
+    return idx, probs
+
+
+def reference_sample(last_logits: torch.Tensor, temperature: float = 0.6, top_k: int = 40) -> int:
+    """`server.py:187-205` line for line for one logits row, drawing from torch's GLOBAL generator
+    like the reference does.  Pinned against the reference's own /generate under torch.manual_seed
+    (tests/golden/sampled_*.npz)."""
+    logits_tensor = last_logits.to(torch.float32) / temperature
+    topk_values, topk_indices = torch.topk(logits_tensor, top_k)
+    probs = F.softmax(topk_values, dim=-1)
+    return int(topk_indices[torch.multinomial(probs, 1)])
+
+
+@torch.no_grad()
+def generate_reference_sampled(w: Weights, dims: GPT2Dims, ids, n_new: int, split_at: int, torch_seed: int,
+                               temperature: float = 0.6, top_k: int = 40):
+    """The coordinator loop `server.py:169-206` with its own sampler: full recompute of Shard A and
+    Shard B per token, `reference_sample` on logits[0, -1].  ids: python list (batch of one)."""
+    ids = [int(i) for i in ids]
+    torch.manual_seed(torch_seed)
+    for _ in range(n_new):
+        x = torch.tensor([ids], dtype=torch.long)
+        logits = shard_b_forward(w, dims, shard_a_forward(w, dims, x, split_at), split_at)
+        ids.append(reference_sample(logits[0, -1], temperature, top_k))
+    return ids
+
+
+def sample_select(last_logits: torch.Tensor, temperature: float, top_k: int, seed: int, row: int, position: int):
+    """Seeded restatement of `server.py:187-205` for one row: the candidate set and its probabilities
+    are the reference's (`topk_probs`); the reference's `torch.multinomial` draw comes from torch's
+    unseeded global generator and cannot be restated, so the draw here is inverse-CDF sampling with
+    u = (philox4x32_10((position, row, 0, 0), seed)[0] >> 8) * 2^-24 over the UNNORMALISED weights
+    exp(x_j - x_0) accumulated in fp32 in candidate order - the arithmetic of csrc/k_sample.cu.
+    Returns (token id, margin) with margin = distance of u * sum to the nearest CDF step (a draw
+    closer than ~1e-5 may legitimately differ between exp implementations)."""
+    import numpy as np
+    idx, _ = topk_probs(last_logits, temperature, top_k)
+    v = last_logits.to(torch.float32)[idx].numpy().astype(np.float32)
+    inv_t = np.float32(1.0) / np.float32(temperature)
+    m = np.float32(v[0] * inv_t)
+    w = np.exp((v * inv_t - m).astype(np.float32)).astype(np.float32)
+    total = np.float32(0.0)
+    for x in w:
+        total = np.float32(total + x)
+    word = philox4x32_10((position, row, 0, 0), (seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF))[0]
+    u = np.float32(word >> 8) * np.float32(1.0 / 16777216.0)
+    target = np.float32(u * total)
+    acc = np.float32(0.0)
+    pick, margin = len(w) - 1, float("inf")
+    found = False
+    for j, x in enumerate(w):
+        acc = np.float32(acc + x)
+        margin = min(margin, abs(float(target) - float(acc)))
+        if not found and target < acc:
+            pick, found = j, True
+    return int(idx[pick]), margin / max(float(total), 1e-30)
 
 
 @torch.no_grad()

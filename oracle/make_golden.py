@@ -96,15 +96,34 @@ def golden_124m(n_new=16):
     restore_block_forward()
 
 
+def golden_sampled(name, preset, seed, recipe, split_at, prompt_text, n_new, torch_seeds):
+    """The reference's /generate with its temperature / top-k / multinomial selection (server.py:187-205),
+    repeatable because torch's global generator is seeded before each request."""
+    dims = O.PRESETS[preset]
+    w = O.init_weights(dims, seed, recipe)
+    pipe = ReferencePipeline(dims, w, split_at, tag=name)
+    ids = np.array([pipe.generate_sampled_ids(prompt_text, n_new, ts) for ts in torch_seeds], dtype=np.int64)
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), meta=_meta(dims, seed, recipe, split_at, prompt_text),
+                        torch_seeds=np.array(torch_seeds, dtype=np.int64), ids=ids, n_new=n_new)
+    restore_block_forward()
+    print(name, ids.shape, ids[0].tolist())
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(8)
+    if "--sampled-only" in sys.argv:
+        golden_sampled("sampled_mini", "mini", 11, "dense", 2, "Hi, ", 12, [2024, 7, 99])
+        golden_sampled("sampled_tiny_gpt2", "tiny-gpt2", 0, "hf", 1, "Hi, ", 20, [5])
+        return
     # config 1 of BASELINE.json: tiny-gpt2, prompt "Hi, " (README.md:115-120), 20 tokens.
     golden_small("tiny_gpt2", "tiny-gpt2", 0, "hf", 1, list("Hi, ".encode()), 20, "Hi, ")
     golden_small("tiny_gpt2_dense", "tiny-gpt2", 3, "dense", 1, list("Hi, ".encode()), 6, "Hi, ")
     golden_small("mini", "mini", 11, "dense", 2, [5, 1040, 17, 300, 2], 8)
     golden_small("mini32", "mini32", 12, "dense", 1, [1, 2, 3, 500, 522, 0, 7], 6)
     golden_124m()
+    golden_sampled("sampled_mini", "mini", 11, "dense", 2, "Hi, ", 12, [2024, 7, 99])
+    golden_sampled("sampled_tiny_gpt2", "tiny-gpt2", 0, "hf", 1, "Hi, ", 20, [5])
 
 
 if __name__ == "__main__":

@@ -161,6 +161,27 @@ class ReferencePipeline:
         r.raise_for_status()
         return r.json()
 
+    def generate_sampled_ids(self, prompt: str, max_new_tokens: int, torch_seed: int):
+        """The reference's own `/generate` (sampler of server.py:187-205 included), made repeatable:
+        its multinomial draws come from torch's global generator, which is seeded here right before
+        the request.  Returns the token ids the reference handed to `tokenizer.decode` (the stub
+        tokenizer's text is lossy for ids >= 256, so the ids are captured there)."""
+        tok = self.mod_c.tokenizer
+        seen = {}
+        orig = tok.decode
+
+        def spy(ids, skip_special_tokens=True):
+            seen["ids"] = [int(i) for i in ids]
+            return orig(ids, skip_special_tokens=skip_special_tokens)
+
+        tok.decode = spy
+        try:
+            torch.manual_seed(torch_seed)
+            self.generate(prompt, max_new_tokens)
+        finally:
+            del tok.decode
+        return seen["ids"]
+
     # --- greedy decode through the HTTP/JSON routes (full path, what /generate would do
     #     with argmax in place of `server.py:187-205`'s sampler)
     def greedy_via_routes(self, ids, n_new):

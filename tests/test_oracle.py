@@ -126,3 +126,58 @@ def test_oracle_matches_hf_model_directly():
         ref = m(ids).logits
     got = O.stage_forward(w, dims, ids, 0, dims.n_layer, True, True)
     assert float((ref - got).abs().max()) < 3e-5
+
+
+# ----------------------------------------------------------------------- sampled selection
+@pytest.mark.parametrize("name", ["sampled_mini", "sampled_tiny_gpt2"])
+def test_reference_sampler_restatement_matches_reference_generate(golden_dir, name):
+    """The unmodified reference's /generate, run under torch.manual_seed (oracle/make_golden.py), against the
+    oracle's line-for-line restatement of server.py:169-206 under the same seed: identical token ids."""
+    g = np.load(os.path.join(golden_dir, name + ".npz"), allow_pickle=False)
+    meta = json.loads(str(g["meta"]))
+    dims = O.GPT2Dims(**meta["dims"])
+    w = O.init_weights(dims, meta["seed"], meta["recipe"])
+    prompt = list(meta["prompt"].encode("utf-8")) if isinstance(meta["prompt"], str) else meta["prompt"]
+    for ts, want in zip(g["torch_seeds"].tolist(), g["ids"].tolist()):
+        got = O.generate_reference_sampled(w, dims, prompt, int(g["n_new"]), meta["split_at"], ts)
+        assert got == want
+
+
+def test_philox_known_answers():
+    """Random123 known-answer vectors for philox4x32, 10 rounds."""
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8)),
+           ((0xFFFFFFFF,) * 4, (0xFFFFFFFF,) * 2, (0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD)),
+           ((0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344), (0xA4093822, 0x299F31D0),
+            (0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1))]
+    for ctr, key, want in kat:
+        assert tuple(O.philox4x32_10(ctr, key)) == want
+
+
+def test_seeded_sampler_uses_the_reference_candidates_and_distribution():
+    gen = torch.Generator().manual_seed(3)
+    logits = torch.randn(50257, generator=gen) * 2.0
+    idx, probs = O.topk_probs(logits, 0.6, 40)
+    vals, ref_idx = torch.topk(logits / 0.6, 40)          # server.py:196
+    assert torch.equal(idx, ref_idx)
+    assert torch.allclose(probs, torch.softmax(vals, -1), atol=0, rtol=0)
+    # ties resolve to the lower token id, also across the k-th place
+    flat = torch.zeros(100)
+    flat[[7, 3, 50]] = 1.0
+    assert O.topk_probs(flat, 0.6, 5)[0].tolist() == [3, 7, 50, 0, 1]
+    # the seeded draw follows those probabilities (chi-square, 39 degrees of freedom, 99.9 % point = 72.1)
+    n = 3000
+    counts = torch.zeros(40)
+    where = {int(t): j for j, t in enumerate(idx.tolist())}
+    for pos in range(n):
+        tok, _ = O.sample_select(logits, 0.6, 40, seed=77, row=0, position=pos)
+        counts[where[tok]] += 1
+    expect = probs * n
+    big = expect >= 5          # pool the sparse tail as usual for the test
+    chi2 = float((((counts - expect) ** 2) / expect)[big].sum())
+    chi2 += float((counts[~big].sum() - expect[~big].sum()) ** 2 / max(float(expect[~big].sum()), 1e-9))
+    assert chi2 < 72.1, chi2
+    # and it is a pure function of (seed, row, position)
+    a = O.sample_select(logits, 0.6, 40, 77, 1, 5)[0]
+    assert a == O.sample_select(logits, 0.6, 40, 77, 1, 5)[0]
+    draws = {O.sample_select(logits, 0.6, 40, 77, r, 5)[0] for r in range(16)}
+    assert len(draws) > 1

@@ -130,3 +130,30 @@ def test_routes_match_reference_routes(golden_dir, name):
         # default max_new_tokens is 20 (server.py:124)
         g3 = c_dev.post("/generate", json={"prompt": text_prompt}).json()["generated"]
         assert len(S.ByteTokenizer().encode(g3)) >= len(prompt)
+
+
+def test_sampling_env_contract():
+    assert S.read_env({})["GP_SAMPLING"] == "greedy" and S.read_env({})["GP_SAMPLE_SEED"] == 0
+    assert S.read_env({"GP_SAMPLING": "Reference", "GP_SAMPLE_SEED": "7"})["GP_SAMPLING"] == "reference"
+    assert (S.REF_TEMPERATURE, S.REF_TOP_K) == (0.6, 40)                                     # server.py:187-188
+    with pytest.raises(ValueError):
+        app_for("coordinator", env={"GP_SAMPLING": "nucleus"})
+
+
+@pytest.mark.gpu
+def test_generate_with_the_reference_sampler_is_seeded_and_replayable(golden_dir):
+    """GP_SAMPLING=reference: /generate draws like server.py:187-205; request n of a process uses seed
+    GP_SAMPLE_SEED + n, so two fresh servers replay the same answers and successive requests differ."""
+    z, meta, dims, w = _golden(golden_dir, "mini")
+    env = {"SPLIT_AT": str(meta["split_at"]), "GP_DTYPE": "f32", "MODEL_ID": "x", "SHARD_ROLE": "coordinator"}
+    mk = lambda **e: TestClient(S.create_app(env=dict(env, **e), dims=dims, weights=w, tokenizer=S.ByteTokenizer()))
+    body = {"prompt": "Hi, ", "max_new_tokens": 16}
+    s1, s2 = mk(GP_SAMPLING="reference", GP_SAMPLE_SEED="5"), mk(GP_SAMPLING="reference", GP_SAMPLE_SEED="5")
+    first = s1.post("/generate", json=body).json()["generated"]
+    second = s1.post("/generate", json=body).json()["generated"]
+    assert first == s2.post("/generate", json=body).json()["generated"]
+    assert second == s2.post("/generate", json=body).json()["generated"]
+    assert first != second
+    greedy = mk().post("/generate", json=body).json()["generated"]
+    assert greedy != first and first.startswith("Hi, ")
+    assert mk(GP_SAMPLING="reference", GP_SAMPLE_SEED="6").post("/generate", json=body).json()["generated"] == second
