@@ -66,6 +66,9 @@ struct gp_engine {
   int sampler_top_k = 0;
   uint64_t sampler_seed = 0;
   std::map<int, int64_t> decode_graph_launches;
+  // gp_generate's prefill, captured per (batch, prompt length, sampler on): ~150 launches of a few us each
+  std::map<int64_t, cudaGraphExec_t> prefill_graphs;
+  std::map<int64_t, int64_t> prefill_graph_launches;
   std::vector<cudaEvent_t> events;
   // persistent decode kernel
   MegaLayer* mega_layers = nullptr;
@@ -557,6 +560,7 @@ int gp_engine_destroy(gp_engine* e) {
   cudaSetDevice(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& kv : e->decode_graphs) cudaGraphExecDestroy(kv.second);
+  for (auto& kv : e->prefill_graphs) cudaGraphExecDestroy(kv.second);
   for (auto ev : e->events) cudaEventDestroy(ev);
   for (void* p : e->allocs) cudaFree(p);
   if (e->stage) cudaFree(e->stage);
@@ -676,7 +680,16 @@ int gp_set_sampler(gp_engine* e, float temperature, int32_t top_k, uint64_t seed
     e->sampler_top_k = top_k;
     e->sampler_seed = seed;
   }
-  // captured decode steps carry the sampler's parameters as kernel arguments
+  // captured steps carry the sampler's parameters as kernel arguments
+  for (auto it = e->prefill_graphs.begin(); it != e->prefill_graphs.end();) {
+    if (it->first & 1) {
+      cudaGraphExecDestroy(it->second);
+      e->prefill_graph_launches.erase(it->first);
+      it = e->prefill_graphs.erase(it);
+    } else {
+      ++it;
+    }
+  }
   for (auto it = e->decode_graphs.begin(); it != e->decode_graphs.end();) {
     if (it->first >= kSampledKey) {
       cudaGraphExecDestroy(it->second);
@@ -722,8 +735,37 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
   CK(e, cudaMemsetAsync(e->lens, 0, c.max_batch * sizeof(int32_t), s));
   CK(e, cudaEventRecord(e->events[0], s));
   if (n_new > 0) {
-    int r = prefill_impl(e, e->prompt, nullptr, B, P, 0, 1, nullptr, nullptr, 0, e->mailbox, nullptr, s);
-    if (r != GP_OK) return r;
+    // the prefill works on engine-owned buffers only, so its launch sequence is replayable for a given shape
+    const bool graph_ok = !(c.flags & GP_FLAG_NO_GRAPH);
+    const int64_t pkey = ((int64_t)B << 32) | ((int64_t)P << 1) | (e->sampler_on ? 1 : 0);
+    auto pit = e->prefill_graphs.find(pkey);
+    if (graph_ok && pit == e->prefill_graphs.end()) {
+      if (e->prefill_graphs.size() >= 64) {   // a server sees many prompt lengths: bound the cache
+        for (auto& kv : e->prefill_graphs) cudaGraphExecDestroy(kv.second);
+        e->prefill_graphs.clear();
+        e->prefill_graph_launches.clear();
+      }
+      const int64_t before = e->launches;
+      CK(e, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      int r = prefill_impl(e, e->prompt, nullptr, B, P, 0, 1, nullptr, nullptr, 0, e->mailbox, nullptr, s);
+      cudaGraph_t g = nullptr;
+      cudaError_t ce = cudaStreamEndCapture(s, &g);
+      if (r != GP_OK) { if (g) cudaGraphDestroy(g); return r; }
+      CK(e, ce);
+      cudaGraphExec_t exec = nullptr;
+      CK(e, cudaGraphInstantiate(&exec, g, 0));
+      cudaGraphDestroy(g);
+      e->prefill_graph_launches[pkey] = e->launches - before;
+      e->launches = before;
+      pit = e->prefill_graphs.emplace(pkey, exec).first;
+    }
+    if (graph_ok) {
+      CK(e, cudaGraphLaunch(pit->second, s));
+      e->launches += e->prefill_graph_launches[pkey];
+    } else {
+      int r = prefill_impl(e, e->prompt, nullptr, B, P, 0, 1, nullptr, nullptr, 0, e->mailbox, nullptr, s);
+      if (r != GP_OK) return r;
+    }
     // first new token: mailbox -> seq[:, P]
     CK(e, cudaMemcpy2DAsync(e->seq + P, e->seq_stride * sizeof(int32_t), e->mailbox, sizeof(int32_t), sizeof(int32_t), B,
                             cudaMemcpyDeviceToDevice, s));

@@ -262,7 +262,9 @@ struct Phase {
   const u64* sentinel; uint32_t sentinel_epoch;      // inbox input: one word thread 0 watches before all poll
 };
 
-template <typename WT> struct Ctx {
+// TR: the phase trace is compiled in only for the kernels launched under GP_MEGA_TRACE - a stamp that is merely
+// predicated off still costs ~85 cycles of dependent latency, and there are a dozen per phase.
+template <typename WT, bool TR> struct Ctx {
   Ring rg;
   float *xs, *red, *hloc, *h2loc, *sbv; int* sbi; int *s_ids, *s_pos;
   const WT *wte, *wpe;
@@ -270,13 +272,15 @@ template <typename WT> struct Ctx {
   long long* trace; int trace_cap; int n_stamp; bool tracing;   // debug: per-CTA clock64 stamps (thread 0)
   // tag = kind * 8 + event (kind of the phase, 7 = step boundary), kept in the top byte
   __device__ __forceinline__ void stamp(int tag) {
-    if (tracing && threadIdx.x == 0 && n_stamp < trace_cap)
-      trace[n_stamp++] = (long long)(((u64)clock64() & 0x00FFFFFFFFFFFFFFull) | ((u64)tag << 56));
+    if constexpr (TR) {
+      if (tracing && threadIdx.x == 0 && n_stamp < trace_cap)
+        trace[n_stamp++] = (long long)(((u64)clock64() & 0x00FFFFFFFFFFFFFFull) | ((u64)tag << 56));
+    }
   }
 };
 
-template <typename WT>
-__device__ __forceinline__ bool fetch_x(const Ctx<WT>& cx, const Phase& ph, int b, int k, float& v) {
+template <typename WT, bool TR>
+__device__ __forceinline__ bool fetch_x(const Ctx<WT, TR>& cx, const Phase& ph, int b, int k, float& v) {
   if (ph.src_kind == SRC_LL) {
     u64 w;
     if (ph.sentinel != nullptr) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(ph.src_ll + (size_t)b * ph.K + k) : "memory");
@@ -338,8 +342,8 @@ __device__ __forceinline__ void copy_ll(float* xrow, const u64* src, int k0, int
 // LayerNorm variant (K = H <= 1920): the row lives in registers; mean and the two-pass biased
 // variance ([hf] modeling_gpt2.py:252,254,505) each cost one shared-memory exchange.  Fully
 // unrolled on purpose: every load of a thread is in flight before the first one is checked.
-template <typename WT, int BT>
-__device__ __forceinline__ void stage_x(Ctx<WT>& cx, const Phase& ph) {
+template <typename WT, int BT, bool TR>
+__device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
   const int tid = threadIdx.x, w = tid >> 5, l = tid & 31, K = ph.K, B = cx.B;
   float* xs = cx.xs;
   if (ph.ln_g == nullptr) {
@@ -480,8 +484,8 @@ __device__ __forceinline__ void best_merge(Best& a, float v, int i) {
 // element-to-lane mapping is the conflict-free one: of every 256-element block a lane takes elements
 // [4 lane, 4 lane + 4) and [128 + 4 lane, 128 + 4 lane + 4) - a quarter-warp then reads 128 contiguous bytes
 // of x per float4 load (8 consecutive floats per lane would be a 2-way bank conflict on every x load).
-template <typename WT, int BT, int RB>
-__device__ __forceinline__ void chunk_rows(Ctx<WT>& cx, const Phase& ph, const uint8_t* slot, int first, int r,
+template <typename WT, int BT, int RB, bool TR>
+__device__ __forceinline__ void chunk_rows(Ctx<WT, TR>& cx, const Phase& ph, const uint8_t* slot, int first, int r,
                                            Best (&best)[BT]) {
   const int K = ph.K, B = cx.B;
   const int rowbytes = K * (int)sizeof(WT);
@@ -560,8 +564,8 @@ __device__ __forceinline__ void chunk_rows(Ctx<WT>& cx, const Phase& ph, const u
 // Every warp walks the same chunk sequence.  Rows are dealt round-robin over the CTA's whole row range
 // (row j of the range belongs to warp j % 15), not per chunk: with 21-row chunks a per-chunk deal gives
 // six warps twice the work of the other nine in every chunk, and the warps only meet at the ring.
-template <typename WT, int BT>
-__device__ __forceinline__ void run_rows(Ctx<WT>& cx, const Phase& ph, const KindInfo& ki) {
+template <typename WT, int BT, bool TR>
+__device__ __forceinline__ void run_rows(Ctx<WT, TR>& cx, const Phase& ph, const KindInfo& ki) {
   Ring& rg = cx.rg;
   const int r0 = ki.r0, r1 = ki.r1, rps = ki.rps;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -634,8 +638,8 @@ struct AttnArgs {
 // Decode attention for one (b, head) task.  Cached K/V rows do not depend on this step, so the
 // first two rows of every 8-lane group are fetched before q is waited for.  `pub_ctr` (the
 // CTA's own qkv publish) is consumed by the first task.
-template <typename WT>
-__device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, int task, uint32_t* pub_ctr) {
+template <typename WT, bool TR>
+__device__ __forceinline__ void attention_task(Ctx<WT, TR>& cx, const AttnArgs& a, int task, uint32_t* pub_ctr) {
   constexpr int D = 64;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, sub = lane >> 3, l8 = lane & 7;
   const int grp = warp * 4 + sub;                    // key rows t = grp + kGroups*j belong to this 8-lane group
@@ -748,7 +752,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT>& cx, const AttnArgs& a, i
   if (tid == 0) ctr_bump(a.ctr_attn, task);
 }
 
-template <typename WT, int BT>
+template <typename WT, int BT, bool TR>
 __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const MegaParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int G = gridDim.x, cta = blockIdx.x;
@@ -826,7 +830,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
 
   // ================================= CONSUMERS =================================
   // optional phase trace (GP_MEGA_TRACE): every CTA records %globaltimer (ns, one clock for the whole GPU)
-  Ctx<WT> cx;
+  Ctx<WT, TR> cx;
   cx.trace = p.trace ? p.trace + (size_t)cta * p.trace_cap : nullptr; cx.trace_cap = p.trace_cap; cx.n_stamp = 0;
   cx.tracing = false;
   const int n_items = p.n_steps * p.n_streams;   // item = (round, stream); one decode step of B sequences each
@@ -1034,14 +1038,26 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   }
 }
 
+// traced kernels exist for bf16 storage only (the trace is a tuning aid for the bandwidth-bound configuration)
+template <typename WT> constexpr bool kHasTraced = false;
+template <> constexpr bool kHasTraced<bf16> = true;
+
 template <typename WT, int BT>
 cudaError_t launch_t(const MegaParams& p, int grid, size_t smem, cudaStream_t s) {
   void* args[] = {const_cast<MegaParams*>(&p)};
-  return cudaLaunchCooperativeKernel((const void*)decode_mega_kernel<WT, BT>, dim3(grid), dim3(kMegaThreads), args,
-                                     smem, s);
+  const void* fn = (const void*)decode_mega_kernel<WT, BT, false>;
+  if constexpr (kHasTraced<WT>) {
+    if (p.trace != nullptr) fn = (const void*)decode_mega_kernel<WT, BT, true>;
+  }
+  return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kMegaThreads), args, smem, s);
 }
 template <typename WT, int BT> cudaError_t set_attr() {
-  return cudaFuncSetAttribute(decode_mega_kernel<WT, BT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  cudaError_t e = cudaFuncSetAttribute(decode_mega_kernel<WT, BT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if constexpr (kHasTraced<WT>) {
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(decode_mega_kernel<WT, BT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  }
+  return e;
 }
 
 int padded(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : 4); }
