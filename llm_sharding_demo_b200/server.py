@@ -6,7 +6,7 @@ Same three routes, request bodies, defaults, env vars and role-gate behaviour:
   POST /generate   {"prompt":str,"max_new_tokens":int=20} -> {"generated":str}           (server.py:154-210)
 Env: MODEL_ID, SHARD_ROLE (a|b|coordinator), SPLIT_AT, SHARD_A_SERVICE, SHARD_B_SERVICE, SHARD_PORT
 (server.py:20-25).  New optional env: GP_DTYPE (bf16|f32), GP_SEED, GP_COORD_MODE (device|http),
-GP_SAMPLING (greedy|reference), GP_SAMPLE_SEED.
+GP_SAMPLING (greedy|reference), GP_SAMPLE_SEED, GP_WEIGHTS (checkpoint path).
 
 Differences, all deliberate:
   * selection is greedy by default (BASELINE.json north_star); GP_SAMPLING=reference restores the
@@ -17,8 +17,10 @@ Differences, all deliberate:
     reference, so unmodified reference shards or coordinators interoperate;
   * sequences longer than n_positions are refused with a clear error (the reference would
     raise IndexError -> 500);
-  * weights: seeded random init from the model's GPT2Config shape (no checkpoints offline); a
-    `weights` dict (HF state_dict) can be passed to `create_app`.
+  * weights: GP_WEIGHTS (or a MODEL_ID that is a local directory) names a Hugging Face GPT-2 checkpoint -
+    directory with config.json, `.safetensors` or torch state_dict - which is loaded like server.py:40-41
+    loads the hub model; without one (nothing can be downloaded here) the weights are a seeded random init
+    of the model's GPT2Config shape.  A `weights` dict (HF state_dict) can also be passed to `create_app`.
 """
 from __future__ import annotations
 
@@ -79,6 +81,7 @@ def read_env(env=None) -> Dict:
         "GP_COORD_MODE": env.get("GP_COORD_MODE", "device"),
         "GP_SAMPLING": env.get("GP_SAMPLING", "greedy").lower(),
         "GP_SAMPLE_SEED": int(env.get("GP_SAMPLE_SEED", "0")),
+        "GP_WEIGHTS": env.get("GP_WEIGHTS", ""),
     }
 
 
@@ -99,6 +102,10 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
 
     cfg = read_env(env)
     role = cfg["SHARD_ROLE"]
+    ckpt = cfg["GP_WEIGHTS"] or (cfg["MODEL_ID"] if os.path.isdir(cfg["MODEL_ID"]) else "")
+    if ckpt and weights is None:
+        ck_dims, weights = W.load_checkpoint(ckpt)
+        dims = dims or ck_dims
     dims = dims or W.PRESETS.get(cfg["MODEL_ID"])
     if dims is None:
         raise ValueError(f"unknown MODEL_ID {cfg['MODEL_ID']!r}; known: {sorted(W.PRESETS)}")

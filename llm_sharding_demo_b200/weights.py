@@ -116,3 +116,72 @@ def init_weights(dims: GPT2Dims, seed: int, recipe: str = "hf", only: Optional[L
             t = 0.1 * torch.randn(shape, generator=g) if recipe == "dense" else torch.zeros(shape)
         w[name] = t.contiguous()
     return w
+
+
+# --------------------------------------------------------------------------- checkpoints
+def dims_from_config(cfg: dict) -> GPT2Dims:
+    """A Hugging Face GPT-2 `config.json` -> shapes (`[hf] models/gpt2/configuration_gpt2.py`)."""
+    act = cfg.get("activation_function", "gelu_new")
+    if act != "gelu_new":
+        raise ValueError(f"activation_function={act!r}: only GPT-2's gelu_new is implemented")
+    return GPT2Dims(n_layer=int(cfg["n_layer"]), n_embd=int(cfg["n_embd"]), n_head=int(cfg["n_head"]),
+                    vocab_size=int(cfg.get("vocab_size", 50257)),
+                    n_positions=int(cfg.get("n_positions", cfg.get("n_ctx", 1024))),
+                    layer_norm_epsilon=float(cfg.get("layer_norm_epsilon", 1e-5)))
+
+
+def _read_safetensors(path: str) -> Dict[str, torch.Tensor]:
+    """The safetensors container: u64 header length, JSON header {name: {dtype, shape, data_offsets}}, raw data.
+    Read directly so that a checkpoint loads without the `safetensors` package."""
+    import json
+    import numpy as np
+    kinds = {"F32": (np.float32, torch.float32), "F16": (np.float16, torch.float16), "BF16": (np.uint16, torch.bfloat16),
+             "F64": (np.float64, torch.float64), "I64": (np.int64, torch.int64), "I32": (np.int32, torch.int32)}
+    with open(path, "rb") as f:
+        n = int.from_bytes(f.read(8), "little")
+        header = json.loads(f.read(n))
+        base = 8 + n
+        out = {}
+        for name, meta in header.items():
+            if name == "__metadata__":
+                continue
+            if meta["dtype"] not in kinds:
+                continue   # e.g. the boolean causal-mask buffers `attn.bias` of old GPT-2 exports: not weights
+            np_dt, t_dt = kinds[meta["dtype"]]
+            b, e = meta["data_offsets"]
+            f.seek(base + b)
+            arr = np.frombuffer(f.read(e - b), dtype=np_dt).copy()
+            t = torch.from_numpy(arr)
+            if t_dt == torch.bfloat16:
+                t = t.view(torch.bfloat16)
+            out[name] = t.reshape(meta["shape"])
+    return out
+
+
+def load_checkpoint(path: str):
+    """GPT-2 weights from disk -> (dims or None, state_dict).  `path` is a Hugging Face model directory
+    (`config.json` + `model.safetensors` or `pytorch_model.bin`), a `.safetensors` file, or a torch `.bin/.pt`
+    state_dict.  Names may carry the `transformer.` prefix; Conv1D matrices stay `[in, out]`
+    (`[hf] pytorch_utils.py:119-123`) - the engine transposes them at load; `lm_head.weight` is the
+    tied `wte.weight` (`[hf] modeling_gpt2.py:646`) and is ignored."""
+    import json
+    import os
+    dims = None
+    file = path
+    if os.path.isdir(path):
+        cfg = os.path.join(path, "config.json")
+        if os.path.exists(cfg):
+            with open(cfg) as f:
+                dims = dims_from_config(json.load(f))
+        for cand in ("model.safetensors", "pytorch_model.bin"):
+            if os.path.exists(os.path.join(path, cand)):
+                file = os.path.join(path, cand)
+                break
+        else:
+            raise FileNotFoundError(f"{path}: neither model.safetensors nor pytorch_model.bin")
+    if file.endswith(".safetensors"):
+        sd = _read_safetensors(file)
+    else:
+        sd = torch.load(file, map_location="cpu", weights_only=True)
+    sd = {k: v.to(torch.float32) for k, v in sd.items() if torch.is_tensor(v) and v.is_floating_point()}
+    return dims, sd

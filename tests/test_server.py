@@ -157,3 +157,62 @@ def test_generate_with_the_reference_sampler_is_seeded_and_replayable(golden_dir
     greedy = mk().post("/generate", json=body).json()["generated"]
     assert greedy != first and first.startswith("Hi, ")
     assert mk(GP_SAMPLING="reference", GP_SAMPLE_SEED="6").post("/generate", json=body).json()["generated"] == second
+
+
+def _write_checkpoint(tmp_path, dims, w, as_safetensors):
+    """A Hugging Face style model directory built by hand: config.json + weights with the `transformer.` prefix,
+    the tied lm_head and (like old GPT-2 exports) a boolean causal-mask buffer that is not a weight."""
+    import struct
+    d = tmp_path / ("ckpt_st" if as_safetensors else "ckpt_bin")
+    d.mkdir()
+    (d / "config.json").write_text(json.dumps({"n_layer": dims.n_layer, "n_embd": dims.n_embd, "n_head": dims.n_head,
+                                               "vocab_size": dims.vocab_size, "n_positions": dims.n_positions,
+                                               "layer_norm_epsilon": dims.layer_norm_epsilon,
+                                               "activation_function": "gelu_new", "model_type": "gpt2"}))
+    sd = {"transformer." + k: v for k, v in w.items()}
+    sd["lm_head.weight"] = w["wte.weight"]
+    if not as_safetensors:
+        sd["transformer.h.0.attn.bias"] = torch.ones(1, 1, 4, 4, dtype=torch.bool)
+        torch.save(sd, d / "pytorch_model.bin")
+        return str(d)
+    header, blobs, off = {}, [], 0
+    for k, v in sd.items():
+        raw = v.contiguous().numpy().astype(np.float32).tobytes()
+        header[k] = {"dtype": "F32", "shape": list(v.shape), "data_offsets": [off, off + len(raw)]}
+        blobs.append(raw)
+        off += len(raw)
+    header["transformer.h.0.attn.bias"] = {"dtype": "BOOL", "shape": [1], "data_offsets": [off, off + 1]}
+    blobs.append(b"\x01")
+    hj = json.dumps(header).encode()
+    with open(d / "model.safetensors", "wb") as f:
+        f.write(struct.pack("<Q", len(hj)) + hj + b"".join(blobs))
+    return str(d)
+
+
+@pytest.mark.parametrize("as_safetensors", [True, False])
+def test_checkpoint_loader_reads_hf_layouts(tmp_path, as_safetensors):
+    """a Hugging Face GPT-2 checkpoint (directory, safetensors or torch state_dict) yields
+    the shapes and exactly the tensors the engine loader wants; nothing is downloaded (server.py:40-41 does)."""
+    dims = L.PRESETS["tiny-gpt2"]
+    w = L.init_weights(dims, 3, "hf")
+    path = _write_checkpoint(tmp_path, dims, w, as_safetensors)
+    got_dims, sd = L.load_checkpoint(path)
+    assert got_dims == dims
+    for name in L.stage_weight_names(dims, 0, dims.n_layer, True, True):
+        assert torch.equal(sd["transformer." + name], w[name]), name
+    assert all(v.dtype == torch.float32 for v in sd.values()) and "transformer.h.0.attn.bias" not in sd
+    if as_safetensors:   # the hand-rolled reader agrees with the safetensors package where that is installed
+        st = pytest.importorskip("safetensors.torch")
+        ref = st.load_file(os.path.join(path, "model.safetensors"))
+        assert all(torch.equal(ref[k], sd[k]) for k in sd)
+
+
+@pytest.mark.gpu
+def test_server_serves_a_checkpoint_from_disk(tmp_path, golden_dir):
+    z, meta, dims, w = _golden(golden_dir, "mini")
+    path = _write_checkpoint(tmp_path, dims, w, True)
+    env = {"SPLIT_AT": str(meta["split_at"]), "GP_DTYPE": "f32", "SHARD_ROLE": "coordinator"}
+    from_disk = TestClient(S.create_app(env=dict(env, MODEL_ID=path), tokenizer=S.ByteTokenizer()))
+    from_dict = TestClient(S.create_app(env=dict(env, MODEL_ID="x"), dims=dims, weights=w, tokenizer=S.ByteTokenizer()))
+    body = {"prompt": "Hi, ", "max_new_tokens": 8}
+    assert from_disk.post("/generate", json=body).json() == from_dict.post("/generate", json=body).json()
