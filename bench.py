@@ -39,7 +39,7 @@ DEFAULT_WORKLOAD = "gpt2-124m-b1-p32-n128"
 METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
 # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu --set full
 # capture (profiles/), per launch; None until a capture of the current kernel exists
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 31895878664  # profiles/r01_ncu_full_summary.txt: 31.881589 GB read + 14.29 MB written
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 31880962952  # profiles/r01_ncu_full_summary.txt: 31.868069 GB read + 12.89 MB written
 
 
 def synthetic_prompts(B, P, vocab, seed=7):
@@ -158,6 +158,18 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_p
     return B * len(lat) / sum(lat), statistics.median(lat), info
 
 
+def workload_config(workload, n_gpus):
+    """The `config` object of the JSON line - the same for both arms: N stages, N streams of `batch_per_stream`
+    sequences in flight (the reference arm works through the same sequences one request at a time)."""
+    import llm_sharding_demo_b200.weights as W
+    preset, B, P, n_new, _ = WORKLOADS[workload]
+    dims = W.PRESETS[preset]
+    bytes_step = algorithmic_bytes_per_step(dims, B, P + n_new // 2, 1, 2)
+    return {"workload": workload, "model": preset, "batch_per_stream": B, "streams": n_gpus, "prompt": P,
+            "new_tokens": n_new, "stages": n_gpus,
+            "l2": "inputs larger than L2: %.0f MB of weights and KV cache are streamed every decode step" % (bytes_step / 1e6)}
+
+
 def run_reference(args):
     preset, B, P, n_new, seed = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
@@ -182,7 +194,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1000 * wall / args.steps, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "model": preset, "batch": B, "prompt": P, "new_tokens": n_new},
+        "config": workload_config(args.workload, args.gpus),
         "p50_token_ms": round(1000 * statistics.median(lats), 3),
         "cpu_baseline": {"value": round(value, 3), "unit": "tokens/s", "cores": cores, "kind": "port",
                          "sample": f"{sample} of the {n_new} decode steps per bench step, evenly spread over the run, "
@@ -296,9 +308,7 @@ def run_b200(args):
         "metric": METRIC, "value": round(value, 2), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(dev_total_ms / args.steps, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-        "config": {"workload": args.workload, "model": preset, "batch_per_stream": B, "streams": n_streams,
-                   "prompt": P, "new_tokens": n_new, "stages": world,
-                   "l2": "inputs larger than L2: %.0f MB of weights are streamed every token" % (bytes_step / 1e6)},
+        "config": workload_config(args.workload, world),
         "p50_token_ms": None if p50_tok_ms is None else round(p50_tok_ms, 4),
         "decode_tokens_per_s": None if not p50_tok_ms else round(B * n_streams * 1000.0 / p50_tok_ms, 1),
         "e2e": {"value": round(e2e, 2), "unit": "tokens/s", "h2d_bytes_per_step": int(prompts.numel() * 4),
