@@ -293,3 +293,35 @@ def test_persistent_decode_kernel_matches_per_op_kernels(L, dtype_name, B):
             assert int(ids_m[b, 7 + t]) == int(ids_o[b, 7 + t]) == int(ref_ids[b, 7 + t]), (b, t)
     assert len(tm_m["step_ms"]) == n_new - 1 and all(x > 0 for x in tm_m["step_ms"])
     assert abs(sum(tm_m["step_ms"]) - tm_m["decode_ms"]) < 0.5 * tm_m["decode_ms"] + 0.05
+
+
+# ------------------------------------------------------------------ full-size properties (BASELINE.json sizes)
+@pytest.mark.parametrize("B,P,n_new", [(1, 32, 128), (2, 896, 128)])
+def test_full_size_cached_decode_agrees_with_stateless_prefill(L, B, P, n_new):
+    """At the headline size (124M, bf16; configs[1] and a context-filling 896 + 128 = 1024 = n_positions) the
+    oracle is too slow to run per token, so the check is a size-independent property: the tokens the cached decode
+    (persistent kernel, KV cache) produced must be the argmax of a STATELESS full-sequence pass over the finished
+    sequence (prefill kernels: tcgen05 GEMMs, causal attention; no cache) - two independent code paths - at every
+    position whose top-2 margin exceeds twice the bf16 tolerance.  Also: the run is reproducible and fills the
+    cache exactly to P + n_new - 1."""
+    dims = O.PRESETS["gpt2"]
+    w = O.init_weights(dims, 1234, "hf")
+    eng = L.StageEngine(L.GPT2Dims(**dims.to_dict()), dtype=L.GP_BF16, max_batch=B, max_ctx=P + n_new,
+                        max_tokens=B * (P + n_new))
+    eng.load_weights(w)
+    g = torch.Generator().manual_seed(7)
+    prompt = torch.randint(0, dims.vocab_size, (B, P), generator=g, dtype=torch.int32)
+    out = eng.generate(prompt, n_new)
+    assert out.shape == (B, P + n_new) and torch.equal(out[:, :P], prompt)
+    assert eng.kv_lengths()[:B] == [P + n_new - 1] * B
+    assert torch.equal(out, eng.generate(prompt, n_new))
+    full = eng.prefill(out[:, :-1].to(DEV), use_cache=False, want_logits="all")["logits"]     # [B, P+n_new-1, V]
+    top2 = torch.topk(full[:, P - 1:], 2, dim=-1)
+    margin = (top2.values[..., 0] - top2.values[..., 1]).cpu()
+    pred = top2.indices[..., 0].cpu().to(torch.int32)
+    firm = margin > 2 * TOL_BF16
+    assert int(firm.sum()) >= n_new * B // 4
+    assert torch.equal(pred[firm], out[:, P:][firm])
+    # beyond the context: refused with a message, not a fault (the reference raises IndexError -> 500)
+    with pytest.raises(L.GPError):
+        eng.generate(prompt, n_new + 2)
