@@ -6,18 +6,19 @@
 //
 //   * one CTA per SM; warp 15 is the PRODUCER: a single thread walks the (static) sequence of
 //     weight row-chunks this CTA will need and streams them HBM -> shared memory with
-//     cp.async.bulk (TMA bulk copy, mbarrier complete_tx) into a ring of 24 KB slots, the
+//     cp.async.bulk (TMA bulk copy, mbarrier complete_tx) into a ring of six 32 KB slots, the
 //     matching bias slice riding in the same transaction.  Weights do not depend on activations,
 //     so the producer runs ahead across phases, layers and steps (~190 KB per SM in flight).
 //   * warps 0..14 are CONSUMERS: per phase they collect the activation vector into shared memory
-//     (LayerNorm fused, row held in registers), then each warp dots one weight row of the current
-//     slot (128-bit shared loads, shuffle reduction) and applies the epilogue.
+//     (LayerNorm fused, row held in registers), then each warp dots its one or two weight rows of the
+//     current slot (conflict-free shared loads, shuffle reduction) and applies the epilogue.
 //   * phases exchange activations through "flag-in-data" buffers in L2: every fp32 value travels
 //     in one 64-bit word together with the epoch of the phase that produced it, so a reader can
 //     verify each element by itself - no grid barrier and no memory fence anywhere.  To keep the
-//     polling traffic off L2, each CTA also publishes one flag word per phase; one warp watches
-//     the (coalesced) flag array while the others sleep at the CTA barrier.  Reuse of a buffer
-//     one layer later is ordered by the data dependencies themselves.
+//     polling traffic off L2, each CTA also bumps one of eight "published" counters per buffer (a
+//     fire-and-forget reduction); one warp watches the counters while the others sleep at the CTA
+//     barrier.  Reuse of a buffer one layer later is ordered by the data dependencies themselves
+//     (see DESIGN.md).
 //   * the residual stream slice a CTA owns stays in its shared memory across phases and layers;
 //     decode attention is a phase of the same kernel: CTA (b, head) prefetches the cached K/V rows
 //     while it waits for q, appends the new row and runs an online softmax per 8-lane group.
