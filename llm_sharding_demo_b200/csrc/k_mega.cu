@@ -114,6 +114,22 @@ __device__ __forceinline__ u64 ll_load(const u64* p) {
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
   return w;
 }
+// predicated form (no branch, no access when `on` is false): lanes beyond the end of a row must not fall back
+// to a clamped address - 148 CTAs x several warps re-reading ONE word turn it into an L2 hot spot
+__device__ __forceinline__ u64 ll_load_if(const u64* p, bool on) {
+  u64 w;
+  asm volatile(
+      "{\n"
+      ".reg .pred q;\n"
+      "setp.ne.u32 q, %2, 0;\n"
+      "mov.u64 %0, 0;\n"
+      "@q ld.relaxed.gpu.global.u64 %0, [%1];\n"
+      "}\n"
+      : "=l"(w)
+      : "l"(p), "r"((uint32_t)on)
+      : "memory");
+  return w;
+}
 // system scope: words another GPU writes into this GPU's inbox over NVLink (and our writes into a peer's)
 __device__ __forceinline__ void ll_store_sys(u64* p, uint32_t bits, uint32_t epoch) {
   const u64 w = ((u64)epoch << 32) | (u64)bits;
@@ -281,11 +297,11 @@ template <typename WT, bool TR> struct Ctx {
 };
 
 template <typename WT, bool TR>
-__device__ __forceinline__ bool fetch_x(const Ctx<WT, TR>& cx, const Phase& ph, int b, int k, float& v) {
+__device__ __forceinline__ bool fetch_x(const Ctx<WT, TR>& cx, const Phase& ph, int b, int k, float& v, bool live = true) {
   if (ph.src_kind == SRC_LL) {
     u64 w;
     if (ph.sentinel != nullptr) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(ph.src_ll + (size_t)b * ph.K + k) : "memory");
-    else w = ll_load(ph.src_ll + (size_t)b * ph.K + k);
+    else w = ll_load_if(ph.src_ll + (size_t)b * ph.K + k, live);   // (b, k) are clamped by the caller; dead lanes skip the access
     v = __uint_as_float((uint32_t)w);
     return (uint32_t)(w >> 32) == ph.src_epoch;
   }
@@ -308,15 +324,15 @@ __device__ __forceinline__ void stage_enter(uint32_t* pub_ctr, int pub_idx, cons
   consumer_sync();
 }
 
-// One row of a flag-in-data buffer -> shared memory.  All PER loads of a thread are issued
-// back to back (addresses clamped instead of predicated, so no branch separates them) and only
-// then checked; words whose epoch is still old are re-read, again as one batch.
+// One array of flag-in-data words -> shared memory.  All PER loads of a thread are issued back to back
+// (predicated inside the asm, so no branch separates them) and only then checked; words whose epoch is
+// still old are re-read.
 template <int PER>
 __device__ __forceinline__ void copy_ll(float* xrow, const u64* src, int k0, int K, uint32_t epoch) {
   const int tid = threadIdx.x;
   u64 w[PER];
 #pragma unroll
-  for (int i = 0; i < PER; ++i) w[i] = ll_load(src + min(k0 + tid + i * kConsumers, K - 1));
+  for (int i = 0; i < PER; ++i) w[i] = ll_load_if(src + k0 + tid + i * kConsumers, k0 + tid + i * kConsumers < K);
   unsigned pending = 0;
 #pragma unroll
   for (int i = 0; i < PER; ++i) {
@@ -352,22 +368,18 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
     stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, ph.sentinel,
                 ph.sentinel_epoch);
     cx.stamp(ph.mode * 8 + 0);
-    const int per = (K + kConsumers - 1) / kConsumers;
-#pragma unroll
-    for (int b = 0; b < BT; ++b) {
-      if (b >= B) {
-        for (int k = tid; k < K; k += kConsumers) xs[b * K + k] = 0.f;
-        continue;
-      }
-      const u64* src = ph.src_ll + (size_t)b * K;
-      if (per <= 2) {
-        copy_ll<2>(xs + b * K, src, 0, K, ph.src_epoch);
-      } else if (per <= 7) {
-        copy_ll<7>(xs + b * K, src, 0, K, ph.src_epoch);    // K = 4 * 768: 6.4 words per thread
-      } else {
-        for (int k0 = 0; k0 < K; k0 += 8 * kConsumers) copy_ll<8>(xs + b * K, src, k0, K, ph.src_epoch);
-      }
+    // the B rows are adjacent both in the exchange buffer and in xs: one array of B * K words, so that the loads
+    // of ALL rows are in flight together (row after row cost one L2 round trip per row)
+    const int KT = B * K;
+    const int per = (KT + kConsumers - 1) / kConsumers;
+    if (per <= 2) {
+      copy_ll<2>(xs, ph.src_ll, 0, KT, ph.src_epoch);
+    } else if (per <= 7) {
+      copy_ll<7>(xs, ph.src_ll, 0, KT, ph.src_epoch);       // K = 4 * 768: 6.4 words per thread
+    } else {
+      for (int k0 = 0; k0 < KT; k0 += 9 * kConsumers) copy_ll<9>(xs, ph.src_ll, k0, KT, ph.src_epoch);
     }
+    for (int k = KT + tid; k < BT * K; k += kConsumers) xs[k] = 0.f;   // padding rows of a partial batch
     cx.stamp(ph.mode * 8 + 1);
     consumer_sync();
     return;
@@ -404,8 +416,8 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
     if (i * kConsumers < K) {
 #pragma unroll
       for (int b = 0; b < BT; ++b) {
-        const bool ok = fetch_x(cx, ph, min(b, B - 1), min(tid + i * kConsumers, K - 1), v[b][i]);
         const bool live = b < B && tid + i * kConsumers < K;
+        const bool ok = fetch_x(cx, ph, min(b, B - 1), min(tid + i * kConsumers, K - 1), v[b][i], live);
         if (!live) v[b][i] = 0.f;
         else if (!ok) pending |= 1u << (b * kLnPer + i);
       }
@@ -415,25 +427,56 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
     gate_ctr(ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, kGateSlack);
     consumer_sync();
   }
-  while (pending) {
-#pragma unroll
-    for (int b = 0; b < BT; ++b)
+  if (ph.src_kind == SRC_LL && ph.sentinel == nullptr) {
+    // what is still missing is re-read as ONE batch of loads per round (one at a time it cost an L2 round trip
+    // per word: 8 in a row at batch 4)
+    while (pending) {
 #pragma unroll
       for (int i = 0; i < kLnPer; ++i)
-        if (pending & (1u << (b * kLnPer + i))) {
-          if (fetch_x(cx, ph, b, tid + i * kConsumers, v[b][i])) pending &= ~(1u << (b * kLnPer + i));
+        if (i * kConsumers < K) {
+          u64 wv[BT];   // the rows of one element slot together: BT loads in flight, then BT checks
+#pragma unroll
+          for (int b = 0; b < BT; ++b)
+            wv[b] = ll_load_if(ph.src_ll + (size_t)b * K + tid + i * kConsumers, (pending >> (b * kLnPer + i)) & 1u);
+#pragma unroll
+          for (int b = 0; b < BT; ++b) {
+            const unsigned bit = 1u << (b * kLnPer + i);
+            if ((pending & bit) && (uint32_t)(wv[b] >> 32) == ph.src_epoch) {
+              v[b][i] = __uint_as_float((uint32_t)wv[b]);
+              pending &= ~bit;
+            }
+          }
         }
+    }
+  } else {
+    while (pending) {
+#pragma unroll
+      for (int b = 0; b < BT; ++b)
+#pragma unroll
+        for (int i = 0; i < kLnPer; ++i)
+          if (pending & (1u << (b * kLnPer + i))) {
+            if (fetch_x(cx, ph, b, tid + i * kConsumers, v[b][i])) pending &= ~(1u << (b * kLnPer + i));
+          }
+    }
   }
   cx.stamp(ph.mode * 8 + 1);
   float* redA = cx.red;             // [BT][kNW]
   float* redB = cx.red + BT * kNW;  // [BT][kNW]
+  // the BT butterflies are independent: one shuffle level of all rows at a time
+  float part[BT];
 #pragma unroll
   for (int b = 0; b < BT; ++b) {
-    float sum = 0.f;
+    part[b] = 0.f;
 #pragma unroll
-    for (int i = 0; i < kLnPer; ++i) sum += v[b][i];
-    sum = warp_sum(sum);
-    if (l == 0) redA[b * kNW + w] = sum;
+    for (int i = 0; i < kLnPer; ++i) part[b] += v[b][i];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int b = 0; b < BT; ++b) part[b] += __shfl_xor_sync(FULL_MASK, part[b], o);
+  if (l == 0) {
+#pragma unroll
+    for (int b = 0; b < BT; ++b) redA[b * kNW + w] = part[b];
   }
   consumer_sync();
   float mean[BT];
@@ -452,8 +495,15 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
         q += dlt * dlt;
       }
     }
-    q = warp_sum(q);
-    if (l == 0) redB[b * kNW + w] = q;
+    part[b] = q;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int b = 0; b < BT; ++b) part[b] += __shfl_xor_sync(FULL_MASK, part[b], o);
+  if (l == 0) {
+#pragma unroll
+    for (int b = 0; b < BT; ++b) redB[b * kNW + w] = part[b];
   }
   consumer_sync();
 #pragma unroll
