@@ -160,7 +160,6 @@ __device__ __forceinline__ uint32_t flag_load(const uint32_t* p) {
 // poll one counter each until it reaches its target.  The counters only throttle polling;
 // correctness rests on the per-element epochs, so no fence is needed on either side.
 constexpr int kSub = 8;
-constexpr uint32_t kGateSlack = 1;     // see gate_ctr
 constexpr int kCtrWords = kSub * 32;   // words per exchange buffer id
 __device__ __forceinline__ void ctr_bump(uint32_t* ctr, int producer) {
   asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(ctr + (producer % kSub) * 32) : "memory");
@@ -285,7 +284,7 @@ template <typename WT, bool TR> struct Ctx {
   Ring rg;
   float *xs, *red, *hloc, *h2loc, *sbv; int* sbi; int *s_ids, *s_pos;
   const WT *wte, *wpe;
-  int B, H, V, n_pos, G, cta, c0; float eps; float* logits_out;
+  int B, H, V, n_pos, G, cta, c0; float eps; float* logits_out; uint32_t slack;   // slack: see gate_ctr
   long long* trace; int trace_cap; int n_stamp; bool tracing;   // debug: per-CTA clock64 stamps (thread 0)
   // tag = kind * 8 + event (kind of the phase, 7 = step boundary), kept in the top byte
   __device__ __forceinline__ void stamp(int tag) {
@@ -315,11 +314,11 @@ __device__ __forceinline__ bool fetch_x(const Ctx<WT, TR>& cx, const Phase& ph, 
 
 // barrier (previous phase fully done in this CTA) -> publish it -> wait for this phase's producers
 __device__ __forceinline__ void stage_enter(uint32_t* pub_ctr, int pub_idx, const uint32_t* ctr, const uint32_t* base,
-                                         uint32_t rounds, int n_prod, const u64* sentinel = nullptr,
+                                         uint32_t rounds, int n_prod, uint32_t slack, const u64* sentinel = nullptr,
                                          uint32_t sentinel_epoch = 0) {
   consumer_sync();
   if (threadIdx.x == 0 && pub_ctr != nullptr) ctr_bump(pub_ctr, pub_idx);
-  gate_ctr(ctr, base, rounds, n_prod, kGateSlack);
+  gate_ctr(ctr, base, rounds, n_prod, slack);
   if (sentinel != nullptr && threadIdx.x == 0) ll_wait_sys(sentinel, sentinel_epoch);   // previous pipeline stage
   consumer_sync();
 }
@@ -365,7 +364,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
   float* xs = cx.xs;
   if (ph.ln_g == nullptr) {
     // plain copy: always from a flag-in-data buffer (attention output, GELU output)
-    stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, ph.sentinel,
+    stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, cx.slack, ph.sentinel,
                 ph.sentinel_epoch);
     cx.stamp(ph.mode * 8 + 0);
     // the B rows are adjacent both in the exchange buffer and in xs: one array of B * K words, so that the loads
@@ -407,7 +406,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
     if (tid == 0 && ph.pub_ctr != nullptr) ctr_bump(ph.pub_ctr, ph.pub_idx);
   } else {
     stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
-                ph.src_nprod, ph.sentinel, ph.sentinel_epoch);
+                ph.src_nprod, cx.slack, ph.sentinel, ph.sentinel_epoch);
   }
   cx.stamp(ph.mode * 8 + 0);
   unsigned pending = 0;
@@ -424,7 +423,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
     }
   }
   if (spec && !consumer_all(pending == 0)) {
-    gate_ctr(ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, kGateSlack);
+    gate_ctr(ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, cx.slack);
     consumer_sync();
   }
   if (ph.src_kind == SRC_LL && ph.sentinel == nullptr) {
@@ -712,7 +711,7 @@ __device__ __forceinline__ void attention_task(Ctx<WT, TR>& cx, const AttnArgs& 
   }
   // publish this CTA's own qkv rows; no gate on the other 147 producers: a task needs only the 192
   // words of its head, which 192 threads of 12 CTAs can poll directly without loading L2
-  stage_enter(pub_ctr, cx.cta, nullptr, a.base_qkv, a.rounds, cx.G);
+  stage_enter(pub_ctr, cx.cta, nullptr, a.base_qkv, a.rounds, cx.G, 0u);
   cx.stamp(KIND_ATTN * 8 + 0);
   // q, k_new, v_new of this head: 192 values, one per thread, into shared memory
   if (tid < 3 * D) {
@@ -893,7 +892,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   cx.rg = Ring{ring_base, full, empty, p.n_slots, 0, 0u};
   cx.xs = xs; cx.red = red; cx.hloc = hloc; cx.h2loc = h2loc; cx.sbv = sbv; cx.sbi = sbi; cx.s_ids = s_ids; cx.s_pos = s_pos;
   cx.wte = reinterpret_cast<const WT*>(p.wte); cx.wpe = reinterpret_cast<const WT*>(p.wpe);
-  cx.B = B; cx.H = H; cx.V = p.V; cx.n_pos = p.n_pos; cx.G = G; cx.cta = cta; cx.eps = p.eps; cx.logits_out = p.logits_out;
+  cx.B = B; cx.H = H; cx.V = p.V; cx.n_pos = p.n_pos; cx.G = G; cx.cta = cta; cx.eps = p.eps; cx.logits_out = p.logits_out; cx.slack = p.gate_slack;
   int c0, c1;                                        // residual rows this CTA owns (same split as N = H phases)
   rows_of(cta, G, H, c0, c1);
   cx.c0 = c0;
@@ -1030,7 +1029,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       cx.stamp(7 * 8 + 2);
       // publish, wait for every CTA's partials, then every CTA reduces them itself (index
       // tie-break => deterministic): every CTA knows the next token without another exchange
-      stage_enter(ctr_of(6), cta, ctr_of(6), base_of(6), (uint32_t)step + 1u, G);
+      stage_enter(ctr_of(6), cta, ctr_of(6), base_of(6), (uint32_t)step + 1u, G, cx.slack);
       for (int b = warp; b < B; b += kNW) {
         Best r{-INFINITY, 0x7fffffff};
         // the loads of a lane go out in batches of 2 x 4 before the first one is checked (they were 10
@@ -1164,6 +1163,8 @@ cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_
   if (n_slots > kMaxSlots) n_slots = kMaxSlots;
   if (const char* env = getenv("GP_MEGA_SLOTS")) { int v = atoi(env); if (v >= 2 && v < n_slots) n_slots = v; }
   p.n_slots = n_slots;
+  p.gate_slack = 1;
+  if (const char* env = getenv("GP_MEGA_SLACK")) { int v = atoi(env); if (v >= 0 && v <= 8) p.gate_slack = (uint32_t)v; }
   const size_t smem = fixed + (size_t)n_slots * kSlotBytes;
   const int grid = num_sms;
   if (dtype == GP_BF16) {
