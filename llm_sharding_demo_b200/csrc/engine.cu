@@ -74,8 +74,6 @@ struct gp_engine {
   MegaLayer* mega_layers = nullptr;
   unsigned long long *qkv_ll = nullptr, *attn_ll = nullptr, *h2_ll = nullptr, *act_ll = nullptr, *h_ll = nullptr;
   unsigned long long* part_ll = nullptr;
-  uint32_t* mega_flags = nullptr;
-  uint32_t mega_ctr[64] = {0};   // host mirror of the device "published" counters
   // pipeline stage boundary: this stage's inbox (peers write into it) and the mapped inbox of the peer it feeds
   unsigned char* inbox = nullptr;       // [1024 B ids words][64*H hidden words]
   unsigned char* peer_inbox = nullptr;  // next stage's inbox (stage 0's for the last stage), cudaIpcOpenMemHandle
@@ -226,7 +224,7 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   p.max_ctx = c.max_ctx; p.eps = c.ln_eps; p.B = B; p.slot0 = slot0; p.has_embed = c.has_embed; p.has_head = c.has_head;
   p.wte = e->wte; p.wpe = e->wpe; p.lnf_g = e->lnf_g; p.lnf_b = e->lnf_b; p.ids = ids; p.hidden_in = hidden_in;
   p.hidden_out = hidden_out; p.lens = e->lens; p.qkv_ll = e->qkv_ll; p.attn_ll = e->attn_ll; p.h2_ll = e->h2_ll;
-  p.act_ll = e->act_ll; p.h_ll = e->h_ll; p.part_ll = e->part_ll; p.flags = e->mega_flags; p.ids_out = next_ids ? next_ids : e->mailbox;
+  p.act_ll = e->act_ll; p.h_ll = e->h_ll; p.part_ll = e->part_ll; p.ids_out = next_ids ? next_ids : e->mailbox;
   p.seq = seq; p.seq_stride = e->seq_stride; p.logits_out = logits; p.n_steps = n_steps;
   p.n_streams = pipe.n_streams;
   if (pipe.on) {
@@ -243,14 +241,10 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
     CK(e, cudaMemsetAsync(e->qkv_ll, 0, MBx * 3 * e->H * 8, s)); CK(e, cudaMemsetAsync(e->attn_ll, 0, MBx * e->H * 8, s));
     CK(e, cudaMemsetAsync(e->h2_ll, 0, MBx * e->H * 8, s)); CK(e, cudaMemsetAsync(e->act_ll, 0, MBx * e->F * 8, s));
     CK(e, cudaMemsetAsync(e->h_ll, 0, MBx * e->H * 8, s)); CK(e, cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, s));
-    CK(e, cudaMemsetAsync(e->mega_flags, 0, mega_flag_words() * 4, s));
-    memset(e->mega_ctr, 0, sizeof(e->mega_ctr));
     e->mega_epoch = 8;
   }
   p.epoch0 = e->mega_epoch;
   e->mega_epoch += span;
-  memcpy(p.ctr_base, e->mega_ctr, sizeof(p.ctr_base));
-  mega_advance_counters(e->mega_ctr, e->L, n_steps * pipe.n_streams, B, e->nh, e->num_sms, c.has_head);
   p.step_clock = clock ? e->step_clock : nullptr;
   const char* trace_path = getenv("GP_MEGA_TRACE");
   const bool trace = trace_path != nullptr && n_steps > 1;
@@ -543,7 +537,6 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRY(alloc((void**)&e->act_ll, MB * F * 8)); TRYCK(cudaMemsetAsync(e->act_ll, 0, MB * F * 8, e->stream));
   TRY(alloc((void**)&e->h_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->h_ll, 0, MB * H * 8, e->stream));
   TRY(alloc((void**)&e->part_ll, mega_part_words() * 8)); TRYCK(cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, e->stream));
-  TRY(alloc((void**)&e->mega_flags, mega_flag_words() * 4)); TRYCK(cudaMemsetAsync(e->mega_flags, 0, mega_flag_words() * 4, e->stream));
   TRY(alloc((void**)&e->step_clock, (size_t)(cfg->n_positions + 2) * 64 * sizeof(unsigned long long)));
   TRYCK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
   if (e->num_sms > 1024) e->num_sms = 1024;

@@ -14,11 +14,12 @@
 //     current slot (conflict-free shared loads, shuffle reduction) and applies the epilogue.
 //   * phases exchange activations through "flag-in-data" buffers in L2: every fp32 value travels
 //     in one 64-bit word together with the epoch of the phase that produced it, so a reader can
-//     verify each element by itself - no grid barrier and no memory fence anywhere.  To keep the
-//     polling traffic off L2, each CTA also bumps one of eight "published" counters per buffer (a
-//     fire-and-forget reduction); one warp watches the counters while the others sleep at the CTA
-//     barrier.  Reuse of a buffer one layer later is ordered by the data dependencies themselves
-//     (see DESIGN.md).
+//     verify each element by itself - no grid barrier, no memory fence, no "ready" counter anywhere:
+//     a reader polls exactly the words it needs, every outstanding word of a thread in one batch of
+//     predicated loads per round.  (A counter gate in front of the polling - one warp watching eight
+//     "published" counters per buffer - was the first design; it only protected against an L2 hot spot
+//     that clamped out-of-range addresses had created, and cost one extra L2 round trip per exchange.)
+//     Reuse of a buffer one layer later is ordered by the data dependencies themselves.
 //   * the residual stream slice a CTA owns stays in its shared memory across phases and layers;
 //     decode attention is a phase of the same kernel: CTA (b, head) prefetches the cached K/V rows
 //     while it waits for q, appends the new row and runs an online softmax per 8-lane group.
@@ -78,21 +79,6 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
                : "memory");
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
-// CTA-wide AND over the consumer warps (doubles as a barrier)
-__device__ __forceinline__ bool consumer_all(bool pred) {
-  uint32_t r;
-  asm volatile(
-      "{\n"
-      ".reg .pred p, q;\n"
-      "setp.ne.u32 q, %1, 0;\n"
-      "bar.red.and.pred p, 1, %2, q;\n"
-      "selp.u32 %0, 1, 0, p;\n"
-      "}\n"
-      : "=r"(r)
-      : "r"((uint32_t)pred), "n"(kConsumers)
-      : "memory");
-  return r != 0;
-}
 __device__ __forceinline__ u64 globaltimer() {
   u64 t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -147,39 +133,6 @@ __device__ __forceinline__ uint32_t ll_wait_bits(const u64* p, uint32_t epoch) {
   while ((uint32_t)(w >> 32) != epoch) w = ll_load(p);
   return (uint32_t)w;
 }
-__device__ __forceinline__ void flag_store(uint32_t* p, uint32_t epoch) {
-  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(epoch) : "memory");
-}
-__device__ __forceinline__ uint32_t flag_load(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-// "Published" counters: every exchange buffer has kSub monotonic counters, each on its own 128-byte
-// line; producer i bumps counter i % kSub (a fire-and-forget reduction), lanes 0..kSub-1 of warp 0
-// poll one counter each until it reaches its target.  The counters only throttle polling;
-// correctness rests on the per-element epochs, so no fence is needed on either side.
-constexpr int kSub = 8;
-constexpr int kCtrWords = kSub * 32;   // words per exchange buffer id
-__device__ __forceinline__ void ctr_bump(uint32_t* ctr, int producer) {
-  asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(ctr + (producer % kSub) * 32) : "memory");
-}
-// target_j = base_j + n_j where n_j = number of producers i < n with i % kSub == j
-// `slack`: open the gate when each counter is within `slack` of its target, i.e. while up to kSub * slack
-// producers are still missing; the readers then spin on exactly the words of those producers (few
-// threads, little traffic) and see them one L2 round trip earlier than via counter + re-read.
-__device__ __forceinline__ void gate_ctr(const uint32_t* ctr, const uint32_t* base, uint32_t rounds, int n,
-                                         uint32_t slack = 0) {
-  if ((threadIdx.x >> 5) != 0 || ctr == nullptr) return;
-  const int lane = threadIdx.x & 31;
-  if (lane < kSub) {
-    const uint32_t per_round = (uint32_t)((n - lane + kSub - 1) / kSub);
-    const uint32_t target = base[lane] + rounds * per_round - (per_round > 4u * slack ? slack : 0u);
-    while ((int32_t)(flag_load(ctr + lane * 32) - target) < 0) {}
-  }
-  __syncwarp();
-}
-
 __device__ __forceinline__ void lds8(const bf16* p, float (&v)[8]) {
   const uint4 u = *reinterpret_cast<const uint4*>(p);
   unpack8(u, v);
@@ -267,10 +220,7 @@ enum { EPI_QKV = 0, KIND_ATTN = 1, EPI_PROJ = 2, EPI_FC = 3, EPI_PROJ2 = 4, EPI_
 struct Phase {
   // ---- input vector x[B,K]
   int src_kind; const u64* src_ll; const float* src_plain; int K; uint32_t src_epoch;
-  const uint32_t* src_ctr; const uint32_t* src_base; uint32_t src_rounds; int src_nprod;
   const float* ln_g; const float* ln_b;              // LayerNorm affine, or NULL for a plain copy
-  // ---- what to publish for the previous phase (counter block + producer index), or NULL
-  uint32_t* pub_ctr; int pub_idx;
   // ---- rows
   int N; int has_bias; int mode;
   u64* dst_ll; float* dst_plain; uint32_t dst_epoch;
@@ -284,7 +234,7 @@ template <typename WT, bool TR> struct Ctx {
   Ring rg;
   float *xs, *red, *hloc, *h2loc, *sbv; int* sbi; int *s_ids, *s_pos;
   const WT *wte, *wpe;
-  int B, H, V, n_pos, G, cta, c0; float eps; float* logits_out; uint32_t slack;   // slack: see gate_ctr
+  int B, H, V, n_pos, G, cta, c0; float eps; float* logits_out;
   long long* trace; int trace_cap; int n_stamp; bool tracing;   // debug: per-CTA clock64 stamps (thread 0)
   // tag = kind * 8 + event (kind of the phase, 7 = step boundary), kept in the top byte
   __device__ __forceinline__ void stamp(int tag) {
@@ -312,15 +262,14 @@ __device__ __forceinline__ bool fetch_x(const Ctx<WT, TR>& cx, const Phase& ph, 
   return true;
 }
 
-// barrier (previous phase fully done in this CTA) -> publish it -> wait for this phase's producers
-__device__ __forceinline__ void stage_enter(uint32_t* pub_ctr, int pub_idx, const uint32_t* ctr, const uint32_t* base,
-                                         uint32_t rounds, int n_prod, uint32_t slack, const u64* sentinel = nullptr,
-                                         uint32_t sentinel_epoch = 0) {
+// barrier (previous phase fully done in this CTA: its shared-memory operands may be overwritten); a stage whose
+// input comes from the previous pipeline stage first lets one thread watch a single inbox word
+__device__ __forceinline__ void stage_enter(const u64* sentinel = nullptr, uint32_t sentinel_epoch = 0) {
   consumer_sync();
-  if (threadIdx.x == 0 && pub_ctr != nullptr) ctr_bump(pub_ctr, pub_idx);
-  gate_ctr(ctr, base, rounds, n_prod, slack);
-  if (sentinel != nullptr && threadIdx.x == 0) ll_wait_sys(sentinel, sentinel_epoch);   // previous pipeline stage
-  consumer_sync();
+  if (sentinel != nullptr) {
+    if (threadIdx.x == 0) ll_wait_sys(sentinel, sentinel_epoch);
+    consumer_sync();
+  }
 }
 
 // One array of flag-in-data words -> shared memory.  All PER loads of a thread are issued back to back
@@ -341,15 +290,14 @@ __device__ __forceinline__ void copy_ll(float* xrow, const u64* src, int k0, int
       else pending |= 1u << i;
     }
   }
-  while (pending) {   // rare: the counters said "published" before the last words became visible
-#pragma unroll 1
+  while (pending) {   // what is still missing is re-read as one batch of (predicated) loads per round
+#pragma unroll
+    for (int i = 0; i < PER; ++i) w[i] = ll_load_if(src + k0 + tid + i * kConsumers, (pending >> i) & 1u);
+#pragma unroll
     for (int i = 0; i < PER; ++i)
-      if (pending & (1u << i)) {
-        const u64 v = ll_load(src + k0 + tid + i * kConsumers);
-        if ((uint32_t)(v >> 32) == epoch) {
-          xrow[k0 + tid + i * kConsumers] = __uint_as_float((uint32_t)v);
-          pending &= ~(1u << i);
-        }
+      if (((pending >> i) & 1u) && (uint32_t)(w[i] >> 32) == epoch) {
+        xrow[k0 + tid + i * kConsumers] = __uint_as_float((uint32_t)w[i]);
+        pending &= ~(1u << i);
       }
   }
 }
@@ -364,8 +312,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
   float* xs = cx.xs;
   if (ph.ln_g == nullptr) {
     // plain copy: always from a flag-in-data buffer (attention output, GELU output)
-    stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, cx.slack, ph.sentinel,
-                ph.sentinel_epoch);
+    stage_enter();
     cx.stamp(ph.mode * 8 + 0);
     // the B rows are adjacent both in the exchange buffer and in xs: one array of B * K words, so that the loads
     // of ALL rows are in flight together (row after row cost one L2 round trip per row)
@@ -397,17 +344,7 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
       bb[i] = (k < K) ? ph.ln_b[k] : 0.f;
     }
   }
-  // Speculative first read: the CTA that arrives last (the one everybody else waits for) finds all of
-  // its input already published, so it skips the counter poll and one barrier; only CTAs that arrive
-  // early fall back to the gate before re-reading what was missing.
-  const bool spec = ph.src_kind == SRC_LL && ph.src_ctr != nullptr && ph.sentinel == nullptr;
-  if (spec) {
-    consumer_sync();
-    if (tid == 0 && ph.pub_ctr != nullptr) ctr_bump(ph.pub_ctr, ph.pub_idx);
-  } else {
-    stage_enter(ph.pub_ctr, ph.pub_idx, ph.src_kind == SRC_LL ? ph.src_ctr : nullptr, ph.src_base, ph.src_rounds,
-                ph.src_nprod, cx.slack, ph.sentinel, ph.sentinel_epoch);
-  }
+  stage_enter(ph.sentinel, ph.sentinel_epoch);
   cx.stamp(ph.mode * 8 + 0);
   unsigned pending = 0;
 #pragma unroll
@@ -421,10 +358,6 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
         else if (!ok) pending |= 1u << (b * kLnPer + i);
       }
     }
-  }
-  if (spec && !consumer_all(pending == 0)) {
-    gate_ctr(ph.src_ctr, ph.src_base, ph.src_rounds, ph.src_nprod, cx.slack);
-    consumer_sync();
   }
   if (ph.src_kind == SRC_LL && ph.sentinel == nullptr) {
     // what is still missing is re-read as ONE batch of loads per round (one at a time it cost an L2 round trip
@@ -681,15 +614,13 @@ __device__ __forceinline__ void soft_merge(SoftState& a, float mo, float lo, con
 
 struct AttnArgs {
   void *kc, *vc; const u64* qkv_ll; u64* attn_ll; uint32_t ep_qkv, ep_attn;
-  uint32_t *ctr_qkv, *ctr_attn; const uint32_t* base_qkv; uint32_t rounds;
   int nh, slot0, max_ctx; float *part, *pm, *pl, *qkv_s;
 };
 
 // Decode attention for one (b, head) task.  Cached K/V rows do not depend on this step, so the
-// first two rows of every 8-lane group are fetched before q is waited for.  `pub_ctr` (the
-// CTA's own qkv publish) is consumed by the first task.
+// first two rows of every 8-lane group are fetched before q is waited for.
 template <typename WT, bool TR>
-__device__ __forceinline__ void attention_task(Ctx<WT, TR>& cx, const AttnArgs& a, int task, uint32_t* pub_ctr) {
+__device__ __forceinline__ void attention_task(Ctx<WT, TR>& cx, const AttnArgs& a, int task) {
   constexpr int D = 64;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, sub = lane >> 3, l8 = lane & 7;
   const int grp = warp * 4 + sub;                    // key rows t = grp + kGroups*j belong to this 8-lane group
@@ -709,9 +640,8 @@ __device__ __forceinline__ void attention_task(Ctx<WT, TR>& cx, const AttnArgs& 
     pk1.load(Kc + (size_t)(grp + kGroups) * D + l8 * 8);
     pv1.load(Vc + (size_t)(grp + kGroups) * D + l8 * 8);
   }
-  // publish this CTA's own qkv rows; no gate on the other 147 producers: a task needs only the 192
-  // words of its head, which 192 threads of 12 CTAs can poll directly without loading L2
-  stage_enter(pub_ctr, cx.cta, nullptr, a.base_qkv, a.rounds, cx.G, 0u);
+  // a task needs only the 192 words of its head, which 192 threads poll directly
+  stage_enter();
   cx.stamp(KIND_ATTN * 8 + 0);
   // q, k_new, v_new of this head: 192 values, one per thread, into shared memory
   if (tid < 3 * D) {
@@ -798,8 +728,6 @@ __device__ __forceinline__ void attention_task(Ctx<WT, TR>& cx, const AttnArgs& 
     }
     ll_store(a.attn_ll + (size_t)b * H + head * D + tid, o / Lsum, a.ep_attn);
   }
-  consumer_sync();
-  if (tid == 0) ctr_bump(a.ctr_attn, task);
 }
 
 template <typename WT, int BT, bool TR>
@@ -824,15 +752,12 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   int* s_pos = s_ids + 8;                                                       // [8]
   uint64_t* full = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(s_pos + 8) + 15) & ~(uintptr_t)15);
   uint64_t* empty = full + kMaxSlots;
-  uint32_t* s_base = reinterpret_cast<uint32_t*>(empty + kMaxSlots);            // [64] counter values at launch
-  int* s_pos0 = reinterpret_cast<int*>(s_base + 64);                            // [64] cache lengths at launch
+  int* s_pos0 = reinterpret_cast<int*>(empty + kMaxSlots);                      // [64] cache lengths at launch
   KindInfo* s_kind = reinterpret_cast<KindInfo*>(s_pos0 + 64);                  // [8] (6 used)
   MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_kind + 8);               // [L]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
-#pragma unroll
-    for (int i = 0; i < 64; ++i) s_base[i] = p.ctr_base[i];   // constant indices: no local copy of the params
     for (int s = 0; s < p.n_slots; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], kNW);
@@ -892,15 +817,10 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   cx.rg = Ring{ring_base, full, empty, p.n_slots, 0, 0u};
   cx.xs = xs; cx.red = red; cx.hloc = hloc; cx.h2loc = h2loc; cx.sbv = sbv; cx.sbi = sbi; cx.s_ids = s_ids; cx.s_pos = s_pos;
   cx.wte = reinterpret_cast<const WT*>(p.wte); cx.wpe = reinterpret_cast<const WT*>(p.wpe);
-  cx.B = B; cx.H = H; cx.V = p.V; cx.n_pos = p.n_pos; cx.G = G; cx.cta = cta; cx.eps = p.eps; cx.logits_out = p.logits_out; cx.slack = p.gate_slack;
+  cx.B = B; cx.H = H; cx.V = p.V; cx.n_pos = p.n_pos; cx.G = G; cx.cta = cta; cx.eps = p.eps; cx.logits_out = p.logits_out;
   int c0, c1;                                        // residual rows this CTA owns (same split as N = H phases)
   rows_of(cta, G, H, c0, c1);
   cx.c0 = c0;
-  // counter blocks, one per exchange buffer id (1 qkv, 2 attn, 3 h2, 4 act, 5 h, 6 argmax); their values at
-  // launch are in p.ctr_base; `rounds` = publishes per producer so far in this launch, this one included
-  auto ctr_of = [&](int id) { return p.flags + id * kCtrWords; };
-  auto base_of = [&](int id) { return s_base + id * kSub; };
-
   for (int step = 0; step < n_items; ++step) {
     const int round = step / p.n_streams, strm = step - round * p.n_streams;
     const int slot_base = p.slot0 + strm * B;
@@ -934,64 +854,57 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
     }
     cx.tracing = (p.trace != nullptr && step == n_items - 1);
     cx.stamp(7 * 8 + 0);
-    uint32_t* pub_ctr = nullptr;   // counter block the next stage has to bump for the phase before it
     for (int li = 0; li < p.L; ++li) {
       const MegaLayer& w = s_layers[li];
       const bool last = (li == p.L - 1);
       const uint32_t ep = ep_step + (uint32_t)li * 8u;         // +1 qkv, +2 attn, +3 h2, +4 act, +5 h
-      const uint32_t rnd = (uint32_t)(step * p.L + li) + 1u;   // publishes per producer and buffer, this layer included
       (void)last;
       Phase ph;
       // ---- P1: ln_1 + c_attn -> qkv[b, 3H]
       ph.src_kind = (li > 0) ? SRC_LL : (p.has_embed ? SRC_EMBED : (in_hid ? SRC_LL : SRC_PLAIN));
       ph.src_ll = p.h_ll; ph.src_plain = p.hidden_in; ph.K = H; ph.src_epoch = ep - 8u + 5u;
-      ph.src_ctr = ctr_of(5); ph.src_base = base_of(5); ph.src_rounds = rnd - 1u; ph.src_nprod = G;
       ph.dst_sys = 0; ph.sentinel = nullptr; ph.sentinel_epoch = 0;
       if (li == 0 && !p.has_embed && in_hid != nullptr) {
         // input = what the previous pipeline stage wrote into this GPU's inbox
-        ph.src_ll = in_hid; ph.src_epoch = cep; ph.src_ctr = nullptr;
+        ph.src_ll = in_hid; ph.src_epoch = cep;
         ph.sentinel = in_hid + (H - 1); ph.sentinel_epoch = cep;
       }
-      ph.ln_g = w.ln1_g; ph.ln_b = w.ln1_b; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
+      ph.ln_g = w.ln1_g; ph.ln_b = w.ln1_b;
       ph.N = 3 * H; ph.has_bias = 1; ph.mode = EPI_QKV; ph.dst_ll = p.qkv_ll; ph.dst_plain = nullptr; ph.dst_epoch = ep + 1u;
       stage_x<WT, BT>(cx, ph);
       cx.stamp(ph.mode * 8 + 2);
       run_rows<WT, BT>(cx, ph, s_kind[EPI_QKV]);
-      pub_ctr = ctr_of(1);
       cx.stamp(ph.mode * 8 + 4);
       ph.sentinel = nullptr;
       // ---- P2: attention for the (b, head) tasks of this CTA
       if (cta < B * nh) {
         AttnArgs a;
         a.kc = w.kc; a.vc = w.vc; a.qkv_ll = p.qkv_ll; a.attn_ll = p.attn_ll; a.ep_qkv = ep + 1u; a.ep_attn = ep + 2u;
-        a.ctr_qkv = ctr_of(1); a.ctr_attn = ctr_of(2); a.base_qkv = base_of(1); a.rounds = rnd;
         a.nh = nh; a.slot0 = slot_base; a.max_ctx = p.max_ctx; a.part = part; a.pm = pm; a.pl = pl; a.qkv_s = qkv_s;
         for (int task = cta; task < B * nh; task += G) {
-          attention_task<WT>(cx, a, task, pub_ctr);
-          pub_ctr = nullptr;
+          attention_task<WT>(cx, a, task);
         }
       }
       cx.stamp(KIND_ATTN * 8 + 3);
       // ---- P3: attention c_proj + residual -> h2   (CTAs without an attention task publish qkv here)
       ph.src_kind = SRC_LL; ph.src_ll = p.attn_ll; ph.K = H; ph.src_epoch = ep + 2u;
-      ph.src_ctr = ctr_of(2); ph.src_base = base_of(2); ph.src_rounds = rnd; ph.src_nprod = B * nh;
-      ph.ln_g = nullptr; ph.ln_b = nullptr; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
+      ph.ln_g = nullptr; ph.ln_b = nullptr;
       ph.N = H; ph.mode = EPI_PROJ; ph.dst_ll = p.h2_ll; ph.dst_epoch = ep + 3u;
       stage_x<WT, BT>(cx, ph);
       cx.stamp(ph.mode * 8 + 2);
       run_rows<WT, BT>(cx, ph, s_kind[EPI_PROJ]);
       cx.stamp(ph.mode * 8 + 4);
       // ---- P4: ln_2 + c_fc + gelu_new -> act
-      ph.src_ll = p.h2_ll; ph.src_epoch = ep + 3u; ph.src_ctr = ctr_of(3); ph.src_base = base_of(3); ph.src_nprod = G;
-      ph.ln_g = w.ln2_g; ph.ln_b = w.ln2_b; ph.pub_ctr = ctr_of(3);
+      ph.src_ll = p.h2_ll; ph.src_epoch = ep + 3u;
+      ph.ln_g = w.ln2_g; ph.ln_b = w.ln2_b;
       ph.N = F; ph.mode = EPI_FC; ph.dst_ll = p.act_ll; ph.dst_epoch = ep + 4u;
       stage_x<WT, BT>(cx, ph);
       cx.stamp(ph.mode * 8 + 2);
       run_rows<WT, BT>(cx, ph, s_kind[EPI_FC]);
       cx.stamp(ph.mode * 8 + 4);
       // ---- P5: mlp c_proj + residual -> h (or the stage output)
-      ph.src_ll = p.act_ll; ph.K = F; ph.src_epoch = ep + 4u; ph.src_ctr = ctr_of(4); ph.src_base = base_of(4);
-      ph.ln_g = nullptr; ph.ln_b = nullptr; ph.pub_ctr = ctr_of(4);
+      ph.src_ll = p.act_ll; ph.K = F; ph.src_epoch = ep + 4u;
+      ph.ln_g = nullptr; ph.ln_b = nullptr;
       ph.N = H; ph.mode = EPI_PROJ2; ph.dst_ll = p.h_ll; ph.dst_epoch = ep + 5u;
       if (last && !p.has_head) {
         if (p.peer_hid != nullptr) {   // straight into the next stage's inbox over NVLink
@@ -1003,7 +916,6 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       stage_x<WT, BT>(cx, ph);
       cx.stamp(ph.mode * 8 + 2);
       run_rows<WT, BT>(cx, ph, s_kind[EPI_PROJ2]);
-      pub_ctr = ctr_of(5);   // bumped even when the rows went to hidden_out: counts stay regular
       cx.stamp(ph.mode * 8 + 4);
     }
     if (p.has_head) {
@@ -1011,8 +923,7 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       const uint32_t ep = ep_step + (uint32_t)p.L * 8u;
       Phase ph;
       ph.src_kind = SRC_LL; ph.src_ll = p.h_ll; ph.src_plain = nullptr; ph.K = H; ph.src_epoch = ep - 8u + 5u;
-      ph.src_ctr = ctr_of(5); ph.src_base = base_of(5); ph.src_rounds = (uint32_t)(step * p.L + p.L); ph.src_nprod = G;
-      ph.ln_g = p.lnf_g; ph.ln_b = p.lnf_b; ph.pub_ctr = pub_ctr; ph.pub_idx = cta;
+      ph.ln_g = p.lnf_g; ph.ln_b = p.lnf_b;
       ph.N = p.V; ph.has_bias = 0; ph.mode = EPI_HEAD; ph.dst_ll = nullptr; ph.dst_plain = nullptr; ph.dst_epoch = 0;
       ph.dst_sys = 0; ph.sentinel = nullptr; ph.sentinel_epoch = 0;
       stage_x<WT, BT>(cx, ph);
@@ -1027,9 +938,8 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
         ll_store_int(p.part_ll + ((size_t)tid * 2 + 1) * kFlagStride + cta, r.i, ep + 6u);
       }
       cx.stamp(7 * 8 + 2);
-      // publish, wait for every CTA's partials, then every CTA reduces them itself (index
-      // tie-break => deterministic): every CTA knows the next token without another exchange
-      stage_enter(ctr_of(6), cta, ctr_of(6), base_of(6), (uint32_t)step + 1u, G, cx.slack);
+      // every CTA reduces all partials itself (index tie-break => deterministic): every CTA knows the next
+      // token without another exchange; the readers spin on the words themselves
       for (int b = warp; b < B; b += kNW) {
         Best r{-INFINITY, 0x7fffffff};
         // the loads of a lane go out in batches of 2 x 4 before the first one is checked (they were 10
@@ -1072,9 +982,6 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
         }
       }
       cx.stamp(7 * 8 + 1);
-    } else if (pub_ctr != nullptr) {
-      consumer_sync();
-      if (tid == 0) ctr_bump(pub_ctr, cta);
     }
     // ---- bookkeeping: the cache grew by one position
     if (cta == 0 && tid < B) p.lens[slot_base + tid] = s_pos[tid] + 1;
@@ -1115,7 +1022,7 @@ int padded(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : 4); }
 size_t fixed_smem(int BT, int H, int L) {
   return (size_t)BT * 4 * H * 4 /*xs*/ + kNW * 64 * 4 /*part*/ + 2 * kNW * 4 /*pm,pl*/ + (size_t)2 * BT * kNW * 4 /*red*/ +
          (size_t)2 * BT * kOwnMax * 4 /*hloc,h2loc*/ + 3 * 64 * 4 /*qkv_s*/ + (size_t)kNW * BT * 8 /*sbv,sbi*/ +
-         64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + 256 /*ctr base*/ + 256 /*pos0*/ + 8 * sizeof(KindInfo) +
+         64 /*ids,pos*/ + 16 + 2 * kMaxSlots * 8 + 256 /*pos0*/ + 8 * sizeof(KindInfo) +
          (size_t)L * sizeof(MegaLayer) + 128;
 }
 
@@ -1133,16 +1040,6 @@ bool mega_supported(int B, int H, int nh, int L, int dtype, int num_sms) {
 }
 
 uint32_t mega_epochs_per_launch(int L, int n_steps) { return (uint32_t)n_steps * (uint32_t)(L + 1) * 8u + 8u; }
-size_t mega_flag_words() { return (size_t)8 * kCtrWords; }
-// counter values after a launch: what the next launch must pass as ctr_base (host mirror of ctr_bump)
-void mega_advance_counters(uint32_t* base /*[8][8]*/, int L, int n_steps, int B, int nh, int grid, int has_head) {
-  auto add = [&](int id, int n_prod, uint32_t rounds) {
-    for (int j = 0; j < kSub; ++j) base[id * kSub + j] += rounds * (uint32_t)((n_prod - j + kSub - 1) / kSub);
-  };
-  const uint32_t r = (uint32_t)n_steps * (uint32_t)L;
-  add(1, grid, r); add(2, B * nh, r); add(3, grid, r); add(4, grid, r); add(5, grid, r);
-  if (has_head) add(6, grid, (uint32_t)n_steps);
-}
 size_t mega_part_words() { return (size_t)kGemvMaxBatch * 2 * kFlagStride; }
 
 cudaError_t init_mega_attrs() {
@@ -1154,7 +1051,7 @@ cudaError_t init_mega_attrs() {
 }
 
 cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_t s) {
-  if (!mega_supported(p.B, p.H, p.nh, p.L, dtype, num_sms) || p.n_steps < 1 || p.epoch0 == 0 || p.flags == nullptr ||
+  if (!mega_supported(p.B, p.H, p.nh, p.L, dtype, num_sms) || p.n_steps < 1 || p.epoch0 == 0 ||
       p.n_streams < 1 || p.n_streams * p.B > 64)
     return cudaErrorInvalidValue;
   const int BT = padded(p.B);
@@ -1163,8 +1060,6 @@ cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_
   if (n_slots > kMaxSlots) n_slots = kMaxSlots;
   if (const char* env = getenv("GP_MEGA_SLOTS")) { int v = atoi(env); if (v >= 2 && v < n_slots) n_slots = v; }
   p.n_slots = n_slots;
-  p.gate_slack = 1;
-  if (const char* env = getenv("GP_MEGA_SLACK")) { int v = atoi(env); if (v >= 0 && v <= 8) p.gate_slack = (uint32_t)v; }
   const size_t smem = fixed + (size_t)n_slots * kSlotBytes;
   const int grid = num_sms;
   if (dtype == GP_BF16) {

@@ -94,8 +94,6 @@ struct MegaParams {
   // flag-in-data exchange buffers: one 64-bit word {epoch, fp32} per element
   unsigned long long *qkv_ll = nullptr, *attn_ll = nullptr, *h2_ll = nullptr, *act_ll = nullptr, *h_ll = nullptr;
   unsigned long long* part_ll = nullptr;                     // [8][2][256] argmax partials (value | index per CTA)
-  uint32_t* flags = nullptr;                                 // [8][8][32] "published" counters per exchange buffer
-  uint32_t ctr_base[64] = {0};                               // their values when this launch starts
   uint32_t epoch0 = 0;                                       // first epoch of this launch (> every earlier one)
   int32_t* ids_out = nullptr; int32_t* seq = nullptr; int seq_stride = 0; float* logits_out = nullptr;
   int n_steps = 1;                                           // decode steps (rounds) per launch
@@ -109,14 +107,11 @@ struct MegaParams {
   int32_t* tok_out = nullptr; int tok_stride = 0;            // stage 0: tokens [n_streams*B][n_steps]
   unsigned long long* step_clock = nullptr;                  // [items+1] globaltimer ns: end of each item, then start
   int n_slots = 0;                                           // filled by the launcher
-  uint32_t gate_slack = 1;                                   // filled by the launcher (see gate_ctr in k_mega.cu)
   long long* trace = nullptr; int trace_cap = 0;             // debug: clock64 of CTA 0 per phase boundary
 };
 bool mega_supported(int B, int H, int nh, int L, int dtype, int num_sms);
 uint32_t mega_epochs_per_launch(int L, int n_steps);
-size_t mega_flag_words();
 size_t mega_part_words();
-void mega_advance_counters(uint32_t* base, int L, int n_steps, int B, int nh, int grid, int has_head);
 cudaError_t init_mega_attrs();
 cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_t s);
 
