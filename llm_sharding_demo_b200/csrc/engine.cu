@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <ctime>
+#include <algorithm>
 #include <map>
 #include <set>
 #include <string>
@@ -245,6 +246,8 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   }
   p.epoch0 = e->mega_epoch;
   e->mega_epoch += span;
+  p.l2_stream_hint = 1;
+  if (const char* env = getenv("GP_MEGA_L2HINT")) p.l2_stream_hint = atoi(env);   // 0: weight copies at normal L2 priority
   p.step_clock = clock ? e->step_clock : nullptr;
   const char* trace_path = getenv("GP_MEGA_TRACE");
   const bool trace = trace_path != nullptr && n_steps > 1;

@@ -107,6 +107,7 @@ struct MegaParams {
   int32_t* tok_out = nullptr; int tok_stride = 0;            // stage 0: tokens [n_streams*B][n_steps]
   unsigned long long* step_clock = nullptr;                  // [items+1] globaltimer ns: end of each item, then start
   int n_slots = 0;                                           // filled by the launcher
+  int l2_stream_hint = 1;                                    // weight copies carry an L2 evict-first policy
   long long* trace = nullptr; int trace_cap = 0;             // debug: clock64 of CTA 0 per phase boundary
 };
 bool mega_supported(int B, int H, int nh, int L, int dtype, int num_sms);
