@@ -39,7 +39,7 @@ DEFAULT_WORKLOAD = "gpt2-124m-b1-p32-n128"
 METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
 # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu --set full
 # capture (profiles/), per launch; None until a capture of the current kernel exists
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 31884872384  # profiles/r01_ncu_full_summary.txt: 31.871032 GB read + 13.84 MB written
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 31413734176  # profiles/r01_ncu_full_summary.txt: 31.405780 GB read + 7.95 MB written (K/V rows now hit in L2)
 
 
 def synthetic_prompts(B, P, vocab, seed=7):
