@@ -74,7 +74,8 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // The weights are a 250 MB-per-token stream through a 126 MB L2: left at normal priority they evict what a token
 // re-reads (above all the KV cache rows) before it comes round again.  The stream is therefore marked evict-first
-// and what the consumers load stays resident: +10 % at a context of 576, +2 % at 160 (GP_MEGA_L2HINT=0 turns it off).
+// and what the consumers load stays resident: +10 % at a context of 576, +3 % at 160.  The host sets the hint only
+// when the stage's weights exceed what L2 could keep (MegaParams::l2_stream_hint; GP_MEGA_L2HINT overrides).
 __device__ __forceinline__ uint64_t l2_stream_policy(bool evict_first) {
   uint64_t pol;
   if (evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
@@ -373,17 +374,18 @@ __device__ __forceinline__ void stage_x(Ctx<WT, TR>& cx, const Phase& ph) {
     // what is still missing is re-read as ONE batch of loads per round (one at a time it cost an L2 round trip
     // per word: 8 in a row at batch 4)
     while (pending) {
+      const unsigned want = pending;   // the load predicates of a round must not depend on its checks
 #pragma unroll
       for (int i = 0; i < kLnPer; ++i)
         if (i * kConsumers < K) {
           u64 wv[BT];   // the rows of one element slot together: BT loads in flight, then BT checks
 #pragma unroll
           for (int b = 0; b < BT; ++b)
-            wv[b] = ll_load_if(ph.src_ll + (size_t)b * K + tid + i * kConsumers, (pending >> (b * kLnPer + i)) & 1u);
+            wv[b] = ll_load_if(ph.src_ll + (size_t)b * K + tid + i * kConsumers, (want >> (b * kLnPer + i)) & 1u);
 #pragma unroll
           for (int b = 0; b < BT; ++b) {
             const unsigned bit = 1u << (b * kLnPer + i);
-            if ((pending & bit) && (uint32_t)(wv[b] >> 32) == ph.src_epoch) {
+            if ((want & bit) && (uint32_t)(wv[b] >> 32) == ph.src_epoch) {
               v[b][i] = __uint_as_float((uint32_t)wv[b]);
               pending &= ~bit;
             }
@@ -953,28 +955,36 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       // token without another exchange; the readers spin on the words themselves
       for (int b = warp; b < B; b += kNW) {
         Best r{-INFINITY, 0x7fffffff};
-        // the loads of a lane go out in batches of 2 x 4 before the first one is checked (they were 10
-        // serial round trips); 148 CTAs need two batches
+        // 148 CTAs = two batches of 2 x 4 words per lane.  Every word of a batch that is still missing is re-read
+        // in ONE round of predicated loads (spinning on them one after the other cost a round trip per word:
+        // +3 us per token once the counter gate in front of this loop was gone)
         const u64* pv = p.part_ll + ((size_t)b * 2 + 0) * kFlagStride;
         const u64* pi = p.part_ll + ((size_t)b * 2 + 1) * kFlagStride;
 #pragma unroll 1
         for (int j0 = 0; j0 < G; j0 += 128) {
           u64 wv[4], wi[4];
+          unsigned pend = 0;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int g = min(j0 + j * 32 + lane, G - 1);
-            wv[j] = ll_load(pv + g);
-            wi[j] = ll_load(pi + g);
-          }
+          for (int j = 0; j < 4; ++j)
+            if (j0 + j * 32 + lane < G) pend |= 3u << (2 * j);
+          while (pend) {
+            const unsigned want = pend;   // the predicates of a round must not depend on its checks
+            u64 nv[4], ni[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int g = j0 + j * 32 + lane;
-            if (g < G) {
-              if ((uint32_t)(wv[j] >> 32) != ep + 6u) wv[j] = ll_wait_bits(pv + g, ep + 6u);
-              if ((uint32_t)(wi[j] >> 32) != ep + 6u) wi[j] = ll_wait_bits(pi + g, ep + 6u);
-              best_merge(r, __uint_as_float((uint32_t)wv[j]), (int)(uint32_t)wi[j]);
+            for (int j = 0; j < 4; ++j) {
+              const int g = j0 + j * 32 + lane;
+              nv[j] = ll_load_if(pv + g, (want >> (2 * j)) & 1u);
+              ni[j] = ll_load_if(pi + g, (want >> (2 * j + 1)) & 1u);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (((want >> (2 * j)) & 1u) && (uint32_t)(nv[j] >> 32) == ep + 6u) { wv[j] = nv[j]; pend &= ~(1u << (2 * j)); }
+              if (((want >> (2 * j + 1)) & 1u) && (uint32_t)(ni[j] >> 32) == ep + 6u) { wi[j] = ni[j]; pend &= ~(2u << (2 * j)); }
             }
           }
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (j0 + j * 32 + lane < G) best_merge(r, __uint_as_float((uint32_t)wv[j]), (int)(uint32_t)wi[j]);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
