@@ -111,6 +111,14 @@ __device__ __forceinline__ u64 ll_load(const u64* p) {
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
   return w;
 }
+__device__ __forceinline__ void red_add_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 // predicated form (no branch, no access when `on` is false): lanes beyond the end of a row must not fall back
 // to a clamped address - 148 CTAs x several warps re-reading ONE word turn it into an L2 hot spot
 __device__ __forceinline__ u64 ll_load_if(const u64* p, bool on) {
@@ -769,7 +777,10 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
   MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_kind + 8);               // [L]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // one monotonic counter gates the argmax exchange (see there); it lives in an unused row of the partials buffer
+  uint32_t* const argmax_ctr = reinterpret_cast<uint32_t*>(p.part_ll + (size_t)14 * kFlagStride);
   if (tid == 0) {
+    s_kind[7].r0 = (int)ld_relaxed_u32(argmax_ctr);   // its value when this launch starts: nobody bumps it before every CTA got here
     for (int s = 0; s < p.n_slots; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], kNW);
@@ -952,8 +963,19 @@ __global__ void __launch_bounds__(kMegaThreads, 1) decode_mega_kernel(const Mega
       }
       cx.stamp(7 * 8 + 2);
       // every CTA reduces all partials itself (index tie-break => deterministic): every CTA knows the next
-      // token without another exchange; the readers spin on the words themselves
+      // token without another exchange.  Unlike the per-layer exchanges this one keeps a counter in front of the
+      // data: 148 warps polling the same 19 lines that 148 producers are still writing delayed those writes
+      // (+3 us per token measured); one lane per reading warp watches one counter line instead.
+      if (warp == 0) {
+        __syncwarp();
+        if (lane == 0) red_add_u32(argmax_ctr, 1u);
+      }
       for (int b = warp; b < B; b += kNW) {
+        if (lane == 0) {
+          const uint32_t target = (uint32_t)s_kind[7].r0 + (uint32_t)(step + 1) * (uint32_t)G;
+          while ((int32_t)(ld_relaxed_u32(argmax_ctr) - target) < 0) {}
+        }
+        __syncwarp();
         Best r{-INFINITY, 0x7fffffff};
         // 148 CTAs = two batches of 2 x 4 words per lane.  Every word of a batch that is still missing is re-read
         // in ONE round of predicated loads (spinning on them one after the other cost a round trip per word:
