@@ -14,7 +14,8 @@
 //     current slot (conflict-free shared loads, shuffle reduction) and applies the epilogue.
 //   * phases exchange activations through "flag-in-data" buffers in L2: every fp32 value travels
 //     in one 64-bit word together with the epoch of the phase that produced it, so a reader can
-//     verify each element by itself - no grid barrier, no memory fence, no "ready" counter anywhere:
+//     verify each element by itself - no grid barrier, no memory fence, and (with one exception, the
+//     argmax exchange at the end of a step) no "ready" counter:
 //     a reader polls exactly the words it needs, every outstanding word of a thread in one batch of
 //     predicated loads per round.  (A counter gate in front of the polling - one warp watching eight
 //     "published" counters per buffer - was the first design; it only protected against an L2 hot spot
