@@ -153,15 +153,6 @@ __device__ __forceinline__ uint32_t ll_wait_bits(const u64* p, uint32_t epoch) {
   while ((uint32_t)(w >> 32) != epoch) w = ll_load(p);
   return (uint32_t)w;
 }
-__device__ __forceinline__ void lds8(const bf16* p, float (&v)[8]) {
-  const uint4 u = *reinterpret_cast<const uint4*>(p);
-  unpack8(u, v);
-}
-__device__ __forceinline__ void lds8(const float* p, float (&v)[8]) {
-  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-}
-
 // four consecutive weights of a row (8 bytes of bf16 / 16 bytes of fp32)
 __device__ __forceinline__ void lds4(const bf16* p, float (&v)[4]) {
   const uint2 u = *reinterpret_cast<const uint2*>(p);
