@@ -37,9 +37,21 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "gpt2-124m-b1-p32-n128"
 METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
-# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu --set full
-# capture (profiles/), per launch; None until a capture of the current kernel exists
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 31413734176  # profiles/r01_ncu_full_summary.txt: 31.405780 GB read + 7.95 MB written (K/V rows now hit in L2)
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the persistent decode kernel, from the newest
+    `profiles/rNN_traffic.json` (written by profiles/summarize.py from a `ncu --set full` capture of the default
+    workload).  Returns (bytes or None, source)."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
+    if not files:
+        return None, None
+    try:
+        d = json.load(open(files[-1]))
+        return int(d["dram_bytes_per_launch"]), os.path.relpath(files[-1], ROOT) + " (" + d.get("kernel", "?") + ")"
+    except Exception:
+        return None, None
 
 
 def synthetic_prompts(B, P, vocab, seed=7):
@@ -158,6 +170,47 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_p
     return B * len(lat) / sum(lat), statistics.median(lat), info
 
 
+def ids_check(workload, dims, seed, dtype, out, P, n_new, device):
+    """Parity of the ids the timed runs produced (rank 0, outside every timed region):
+      (1) default workload: sequence 0 is the prompt of tests/golden/gpt2_124m.npz, whose continuation came from
+          the reference's own /forward + /forward_b routes (oracle/make_golden.py): tokens must be equal up to the
+          first position whose reference top-2 margin is within twice the storage tolerance;
+      (2) every sequence: a STATELESS full-sequence pass over the finished sequence on a separate single-stage
+          engine (prefill kernels: tcgen05 GEMMs + causal attention, no KV cache, no persistent kernel, no stage
+          boundary) must have the generated token as its argmax wherever its top-2 margin exceeds twice the tolerance.
+    Returns {"checked": n, "mismatch": m, ...}; the caller fails the run when m > 0."""
+    import numpy as np
+    import llm_sharding_demo_b200 as L
+    tol = 0.06 if dtype == L.GP_BF16 else 3e-4
+    res = {"checked": 0, "mismatch": 0, "golden_checked": 0, "golden_mismatch": 0, "margin_rule": 2 * tol}
+    gpath = os.path.join(ROOT, "tests", "golden", "gpt2_124m.npz")
+    if workload == DEFAULT_WORKLOAD and os.path.exists(gpath):
+        z = np.load(gpath)
+        if z["prompt_ids"].tolist() == out[0, :P].tolist():
+            ref = z["greedy_ids"][P:]
+            for t in range(min(len(ref), n_new)):
+                if float(z["margins"][t]) <= 2 * tol:
+                    break
+                res["golden_checked"] += 1
+                res["golden_mismatch"] += int(int(out[0, P + t]) != int(ref[t]))
+    if n_new > 0:
+        eng = L.StageEngine(dims, dtype=dtype, max_batch=1, max_ctx=P + n_new, max_tokens=P + n_new, device=device)
+        eng.load_weights(L.init_weights(dims, seed, "hf"))
+        dev = torch.device("cuda", device)
+        for b in range(out.shape[0]):
+            full = eng.prefill(out[b:b + 1, :-1].to(dev), use_cache=False, want_logits="all")["logits"][0, P - 1:]
+            top2 = torch.topk(full, 2, dim=-1)
+            firm = ((top2.values[:, 0] - top2.values[:, 1]) > 2 * tol).cpu()
+            pred = top2.indices[:, 0].cpu().to(torch.int32)
+            res["checked"] += int(firm.sum())
+            res["mismatch"] += int((pred[firm] != out[b, P:][firm]).sum())
+        eng.close()
+    res["sequences"] = int(out.shape[0])
+    res["checked"] += res["golden_checked"]
+    res["mismatch"] += res["golden_mismatch"]
+    return res
+
+
 def workload_config(workload, n_gpus):
     """The `config` object of the JSON line - the same for both arms: N stages, N streams of `batch_per_stream`
     sequences in flight (the reference arm works through the same sequences one request at a time)."""
@@ -253,6 +306,10 @@ def run_b200(args):
 
     dev_total_ms = runner.max_over_ranks(sum(dev_ms))
     e2e_s = runner.max_over_ranks(e2e_s)
+    check = None
+    if rank == 0 and not args.no_ids_check:
+        check = ids_check(args.workload, dims, seed, dtype, out, P, n_new, local)
+    runner.barrier()
     if rank != 0:
         return
     tokens_per_step = B * n_streams * n_new
@@ -266,6 +323,7 @@ def run_b200(args):
     # (n_new-1) x the per-step figure of SURVEY.md 8(d) at the mean context of the run.
     # world > 1: the same kernel runs one step per launch on every stage; per-stage bytes / per-stage time.
     peak, peak_kind = measured_peaks()
+    traffic, traffic_src = ncu_traffic()
     esz = 2 if dtype == L.GP_BF16 else 4
     t_ctx = P + n_new // 2
     bytes_step = algorithmic_bytes_per_step(dims, B, t_ctx, world, esz)
@@ -289,7 +347,8 @@ def run_b200(args):
             kern = "decode_mega_kernel (one persistent launch per stage, %d rounds x %d streams)" % (n_new - 1, n_streams)
         roof = {"bound": "hbm", "kernel": kern, "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind,
                 "unit": "GB/s", "frac": round(achieved / peak, 4),
-                "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH if (world == 1 and args.workload == DEFAULT_WORKLOAD) else None,
+                "traffic": traffic if (world == 1 and args.workload == DEFAULT_WORKLOAD) else None,
+                "traffic_source": traffic_src if (world == 1 and args.workload == DEFAULT_WORKLOAD) else None,
                 "algorithmic_bytes_per_launch": int(bytes_launch),
                 "note": "per-GPU figure; small-batch decode is latency-bound (dependent phases), see DESIGN.md"}
 
@@ -314,9 +373,12 @@ def run_b200(args):
         "e2e": {"value": round(e2e, 2), "unit": "tokens/s", "h2d_bytes_per_step": int(prompts.numel() * 4),
                 "d2h_bytes_per_step": int(B * n_streams * (P + n_new) * 4)},
         "gpu_launches": int(launches),
-        "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+        "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "ids_check": check,
     }
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
+    if check is not None and check["mismatch"] > 0:
+        sys.stderr.write("bench.py: ids_check FAILED: %s\n" % json.dumps(check))
+        sys.exit(3)
 
 
 def main():
@@ -328,6 +390,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ids-check", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3   # timing rule: at least 3 warm-up steps

@@ -214,7 +214,9 @@ int gp_op_sample_topk(const float* logits, int32_t B, int32_t V, float temperatu
 
 /* K8+K9: ln_f, tied lm_head and greedy argmax fused (server.py:101-102,187-205 with greedy
  * selection); lowest index wins ties.  x fp32 [B,H]; wte `dtype` [V,H]; ids_out int32 [B];
- * logits_out fp32 [B,V] or NULL.  `scratch` must hold gp_lmhead_scratch_bytes(B,V) bytes. */
+ * logits_out fp32 [B,V] or NULL.  `scratch` must hold gp_lmhead_scratch_bytes(B,V) bytes.
+ * gamma and beta are given together (ln_f is applied to x first) or are both NULL (x is already normalised);
+ * one without the other is GP_EINVAL. */
 int64_t gp_lmhead_scratch_bytes(int32_t B, int32_t V);
 int gp_op_lmhead_argmax(const float* x, const float* gamma, const float* beta, const void* wte,
                         int32_t* ids_out, float* logits_out, void* scratch, int32_t B, int32_t V,
@@ -231,7 +233,9 @@ int gp_op_lmhead_argmax(const float* x, const float* gamma, const float* beta, c
  * shared memory; anything larger returns GP_EINVAL with the limits in gp_last_error(NULL).
  * The first call on each device looks up the array's device address
  * (cudaGetSymbolAddress) and sets kernel attributes: make that first call before starting any
- * stream capture on that device.  All calls share the one array: it still holds the previous
+ * stream capture on that device (concurrent first calls from several host threads are serialised
+ * inside).  The looked-up address is cached per device ordinal for the life of the process: it does
+ * not survive cudaDeviceReset, nor a second context created on the same ordinal.  All calls share the one array: it still holds the previous
  * call's partials (the ticket is cleared on `stream` before every launch), and two calls whose
  * kernels overlap on the GPU - different streams, or different host threads - race on it;
  * serialise them.  Arguments as gp_op_lmhead_argmax, minus `scratch`. */

@@ -39,6 +39,9 @@ struct gp_engine {
   std::set<std::string> required, loaded;
   std::vector<void*> allocs;
   int32_t* lens = nullptr;
+  // host mirror of lens[]: prefill sets it, decode advances it, kv_reset clears it.  It exists so that a step
+  // into a full slot is refused before launch (the reference raises IndexError past wpe)
+  std::vector<int32_t> hlens;
   // workspaces
   float* h = nullptr;       // [max_tokens, H]   residual stream
   void* xa = nullptr;       // [max_tokens, H]   LN / attention output feeding a GEMM
@@ -186,6 +189,17 @@ int check_ready(gp_engine* e) {
         return GP_ESTATE;
       }
   }
+  return GP_OK;
+}
+
+// GP_OK when every slot of [slot0, slot0+n) can take `steps` more tokens
+int slot_room(gp_engine* e, const char* who, int slot0, int n, int steps) {
+  for (int i = slot0; i < slot0 + n; ++i)
+    if (e->hlens[i] + steps > e->cfg.max_ctx) {
+      set_err(e, "%s: KV slot %d holds %d tokens; %d more would exceed max_ctx=%d", who, i, e->hlens[i], steps,
+              e->cfg.max_ctx);
+      return GP_ESTATE;
+    }
   return GP_OK;
 }
 
@@ -479,6 +493,7 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   e->L = cfg->layer_end - cfg->layer_begin;
   e->esz = cfg->dtype == GP_BF16 ? 2 : 4;
   e->seq_stride = cfg->n_positions + 1;
+  e->hlens.assign(cfg->max_batch, 0);
   auto fail = [&](int rc) { gp_engine_destroy(e); return rc; };
 #define TRY(x) do { int _r = (x); if (_r != GP_OK) return fail(_r); } while (0)
 #define TRYCK(call) do { cudaError_t _c = (call); if (_c != cudaSuccess) { set_err(nullptr, "%s: %s", #call, cudaGetErrorString(_c)); return fail(GP_ECUDA); } } while (0)
@@ -641,8 +656,13 @@ int gp_kv_reset(gp_engine* e, int32_t slot, void* stream) {
   if (!e || slot >= e->cfg.max_batch) { set_err(e, "gp_kv_reset: bad slot"); return GP_EINVAL; }
   CK(e, cudaSetDevice(e->cfg.device));
   cudaStream_t s = (cudaStream_t)stream;
-  if (slot < 0) CK(e, cudaMemsetAsync(e->lens, 0, e->cfg.max_batch * sizeof(int32_t), s));
-  else CK(e, cudaMemsetAsync(e->lens + slot, 0, sizeof(int32_t), s));
+  if (slot < 0) {
+    CK(e, cudaMemsetAsync(e->lens, 0, e->cfg.max_batch * sizeof(int32_t), s));
+    std::fill(e->hlens.begin(), e->hlens.end(), 0);
+  } else {
+    CK(e, cudaMemsetAsync(e->lens + slot, 0, sizeof(int32_t), s));
+    e->hlens[slot] = 0;
+  }
   return GP_OK;
 }
 
@@ -660,8 +680,11 @@ int gp_stage_prefill(gp_engine* e, const int32_t* ids, const float* hidden_in, i
   if (!e) return GP_EINVAL;
   CK(e, cudaSetDevice(e->cfg.device));
   e->launches = 0;
-  return prefill_impl(e, ids, hidden_in, B, T, slot0, use_cache, hidden_out, logits, logits_all, next_ids, nullptr,
-                      (cudaStream_t)stream);
+  int r = prefill_impl(e, ids, hidden_in, B, T, slot0, use_cache, hidden_out, logits, logits_all, next_ids, nullptr,
+                       (cudaStream_t)stream);
+  if (r == GP_OK && use_cache)
+    for (int b = 0; b < B; ++b) e->hlens[slot0 + b] = T;
+  return r;
 }
 
 int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, int32_t B, int32_t slot0,
@@ -669,7 +692,14 @@ int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, in
   if (!e) return GP_EINVAL;
   CK(e, cudaSetDevice(e->cfg.device));
   e->launches = 0;
-  return decode_impl(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, nullptr, (cudaStream_t)stream);
+  if (B > 0 && slot0 >= 0 && slot0 + B <= e->cfg.max_batch) {
+    int room = slot_room(e, "gp_stage_decode", slot0, B, 1);
+    if (room != GP_OK) return room;
+  }
+  int r = decode_impl(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, nullptr, (cudaStream_t)stream);
+  if (r == GP_OK)
+    for (int b = 0; b < B; ++b) ++e->hlens[slot0 + b];
+  return r;
 }
 
 int gp_set_sampler(gp_engine* e, float temperature, int32_t top_k, uint64_t seed) {
@@ -737,6 +767,9 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
   CK(e, cudaMemcpy2DAsync(e->seq, e->seq_stride * sizeof(int32_t), prompt_ids_host, P * sizeof(int32_t),
                           P * sizeof(int32_t), B, cudaMemcpyHostToDevice, s));
   CK(e, cudaMemsetAsync(e->lens, 0, c.max_batch * sizeof(int32_t), s));
+  std::fill(e->hlens.begin(), e->hlens.end(), 0);
+  if (n_new > 0)
+    for (int b = 0; b < B; ++b) e->hlens[b] = P + n_new - 1;
   CK(e, cudaEventRecord(e->events[0], s));
   if (n_new > 0) {
     // the prefill works on engine-owned buffers only, so its launch sequence is replayable for a given shape
@@ -889,6 +922,8 @@ int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds,
   CK(e, cudaSetDevice(c.device));
   int r = check_ready(e);
   if (r != GP_OK) return r;
+  r = slot_room(e, "gp_pipeline_decode", 0, n_streams * B, n_rounds);
+  if (r != GP_OK) return r;
   cudaStream_t s = (cudaStream_t)stream;
   e->launches = 0;
   while ((int)e->events.size() < 2) {
@@ -901,6 +936,7 @@ int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds,
   CK(e, cudaEventRecord(e->events[0], s));
   r = decode_mega(e, first_ids, nullptr, B, 0, nullptr, nullptr, nullptr, nullptr, n_rounds, false, s, pa);
   if (r != GP_OK) return r;
+  for (int i = 0; i < n_streams * B; ++i) e->hlens[i] += n_rounds;
   CK(e, cudaEventRecord(e->events[1], s));
   // host watchdog: the kernel waits on other GPUs; if a peer never shows up report it instead of hanging forever
   const double t0 = (double)clock() / CLOCKS_PER_SEC;
@@ -1016,6 +1052,10 @@ int gp_op_lmhead_argmax(const float* x, const float* gamma, const float* beta, c
                         float* logits_out, void* scratch, int32_t B, int32_t V, int32_t H, float eps, int32_t dtype,
                         void* stream) {
   if (!x || !wte || !ids_out || !scratch) { set_err(nullptr, "gp_op_lmhead_argmax: NULL argument"); return GP_EINVAL; }
+  if ((gamma == nullptr) != (beta == nullptr)) {
+    set_err(nullptr, "gp_op_lmhead_argmax: gamma and beta must both be given (ln_f is applied) or both be NULL (x is used as is)");
+    return GP_EINVAL;
+  }
   if (!gemv_supported(B, H)) { set_err(nullptr, "gp_op_lmhead_argmax: B=%d H=%d outside the GEMV envelope", B, H); return GP_EINVAL; }
   int r = op_init();
   if (r != GP_OK) return r;

@@ -87,7 +87,8 @@ __device__ __forceinline__ void gemv_epilogue(const GemvParams& p, int b, int n,
       const int slot = p.slot0 + b;
       const int pos = p.lens[slot];
       WT* cache = reinterpret_cast<WT*>(which ? p.vcache : p.kcache);
-      cache[(((size_t)slot * p.nh + head) * p.max_ctx + pos) * p.d + dd] = from_f<WT>(v);
+      // a full slot is refused on the host (engine.cu: slot_room); never write past the slot's rows
+      if (pos < p.max_ctx) cache[(((size_t)slot * p.nh + head) * p.max_ctx + pos) * p.d + dd] = from_f<WT>(v);
     }
     return;
   }
@@ -310,8 +311,10 @@ cudaError_t launch_lmhead_argmax(const LmheadParams& p, int dtype, cudaStream_t 
 // ticket live in the fixed array below instead; every GPU that loads this library carries
 // its kStaticScratchBytes until the process exits.
 #include <cstdio>
+#include <mutex>
 namespace gp {
 namespace {
+std::mutex g_static_scratch_mu;   // guards the per-device set-up below (two host threads may make the first call)
 constexpr size_t kStaticScratchBytes =
     kLmheadScratchHeader + (size_t)kLmheadMaxGrid * kGemvMaxBatch * (sizeof(float) + sizeof(int));  // 76,032 B
 static __device__ __align__(256) unsigned char g_lmhead_static_scratch[kStaticScratchBytes];
@@ -333,6 +336,8 @@ extern "C" int gp_op_lmhead_argmax_static(const float* x, const float* gamma, co
     return code;
   };
   if (!x || !wte || !ids_out) return fail(GP_EINVAL, "NULL argument", "");
+  if ((gamma == nullptr) != (beta == nullptr))
+    return fail(GP_EINVAL, "gamma and beta must both be given (ln_f is applied) or both be NULL (x is used as is)", "");
   if (dtype != GP_F32 && dtype != GP_BF16) return fail(GP_EINVAL, "dtype must be GP_F32 or GP_BF16", "");
   // the fixed array holds partials for at most kGemvMaxBatch rows; x must fit shared memory
   if (B < 1 || B > kGemvMaxBatch || V < 1 || H < 1 || !gemv_supported(B, H)) {
@@ -345,7 +350,9 @@ extern "C" int gp_op_lmhead_argmax_static(const float* x, const float* gamma, co
   cudaError_t ce = cudaGetDevice(&dev);
   if (ce != cudaSuccess) return fail(GP_ECUDA, "cudaGetDevice: ", cudaGetErrorString(ce));
   if (dev < 0 || dev >= kMaxDevices) return fail(GP_EINVAL, "device ordinal out of range", "");
-  if (!g_static_scratch_ready[dev]) {
+  {
+    std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+    if (!g_static_scratch_ready[dev]) {
     // One-time set-up on this device (it is current).  In host code the array's NAME is only a
     // host-side handle, not a device address: handing it to a kernel would fault, or silently hit
     // the wrong memory where the GPU can reach host memory.  Ask the runtime for the real address.
@@ -356,6 +363,7 @@ extern "C" int gp_op_lmhead_argmax_static(const float* x, const float* gamma, co
     if ((ce = init_gemv_attrs()) != cudaSuccess) return fail(GP_ECUDA, "kernel attribute set-up: ", cudaGetErrorString(ce));
     g_static_scratch_addr[dev] = p;
     g_static_scratch_ready[dev] = true;
+    }
   }
   void* scratch = g_static_scratch_addr[dev];
   cudaStream_t s = (cudaStream_t)stream;

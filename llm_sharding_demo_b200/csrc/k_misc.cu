@@ -196,8 +196,10 @@ qkv_split_decode_kernel(const AT* __restrict__ qkv, float* __restrict__ q, AT* _
     const int head = c / d, dd = c - head * d;
     const size_t dst = (((size_t)slot * nh + head) * max_ctx + pos) * d + dd;
     q[(size_t)b * H + c] = to_f(row[c]);
-    kc[dst] = row[H + c];
-    vc[dst] = row[2 * H + c];
+    if (pos < max_ctx) {   // a full slot is refused on the host; never write past the slot's rows
+      kc[dst] = row[H + c];
+      vc[dst] = row[2 * H + c];
+    }
   }
 }
 

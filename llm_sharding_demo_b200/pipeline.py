@@ -128,6 +128,8 @@ class PipelineRunner:
         dist, eng, B, S, M = self.dist, self.engine, self.B, self.world, self.n_streams
         H = self.dims.n_embd
         P = prompts.shape[1]
+        if P + max(n_new, 1) - 1 > eng.max_ctx:
+            raise ValueError(f"prompt of {P} tokens + {n_new} new tokens exceeds the KV cache of {eng.max_ctx} positions")
         dev = self.device
         nxt, prv = (self.rank + 1) % S, (self.rank - 1) % S
         eng.kv_reset(-1)

@@ -6,7 +6,8 @@ Same three routes, request bodies, defaults, env vars and role-gate behaviour:
   POST /generate   {"prompt":str,"max_new_tokens":int=20} -> {"generated":str}           (server.py:154-210)
 Env: MODEL_ID, SHARD_ROLE (a|b|coordinator), SPLIT_AT, SHARD_A_SERVICE, SHARD_B_SERVICE, SHARD_PORT
 (server.py:20-25).  New optional env: GP_DTYPE (bf16|f32), GP_SEED, GP_COORD_MODE (device|http),
-GP_SAMPLING (greedy|reference), GP_SAMPLE_SEED, GP_WEIGHTS (checkpoint path).
+GP_SAMPLING (greedy|reference), GP_SAMPLE_SEED, GP_WEIGHTS (checkpoint path), GP_RANDOM_INIT (0|1),
+GP_MAX_BATCH (KV slots = requests decoded together).
 
 Differences, all deliberate:
   * selection is greedy by default (BASELINE.json north_star); GP_SAMPLING=reference restores the
@@ -17,10 +18,14 @@ Differences, all deliberate:
     reference, so unmodified reference shards or coordinators interoperate;
   * sequences longer than n_positions are refused with a clear error (the reference would
     raise IndexError -> 500);
-  * weights: GP_WEIGHTS (or a MODEL_ID that is a local directory) names a Hugging Face GPT-2 checkpoint -
-    directory with config.json, `.safetensors` or torch state_dict - which is loaded like server.py:40-41
-    loads the hub model; without one (nothing can be downloaded here) the weights are a seeded random init
-    of the model's GPT2Config shape.  A `weights` dict (HF state_dict) can also be passed to `create_app`.
+  * weights, in this order: a `weights` dict passed to `create_app`; GP_WEIGHTS (or a MODEL_ID that is a local
+    directory) naming a Hugging Face GPT-2 checkpoint - directory with config.json, `.safetensors` or torch
+    state_dict; `AutoModelForCausalLM.from_pretrained(MODEL_ID)` exactly like server.py:40-41 (local cache
+    first, then the hub).  If none of them yields weights the server REFUSES TO START - it never answers
+    from a random network by accident.  GP_RANDOM_INIT=1 opts into a seeded random init of the model's
+    GPT2Config shape (benchmarks, tests, boxes without checkpoints) and says so on stderr;
+  * the GPT-2 BPE files come with the checkpoint; when they are missing the byte-level stand-in tokenizer is
+    used and a warning is printed (token ids then differ from the reference's).
 """
 from __future__ import annotations
 
@@ -59,12 +64,37 @@ class ByteTokenizer:
         return bytes(int(i) & 0xFF for i in ids).decode("utf-8", errors="replace")
 
 
+def _warn(msg: str):
+    import sys
+    print(f"[llm_sharding_demo_b200] WARNING: {msg}", file=sys.stderr, flush=True)
+
+
 def load_tokenizer(model_id: str):
     try:  # tokenizer stays host-side, as in server.py:40,160,209
         from transformers import AutoTokenizer
         return AutoTokenizer.from_pretrained(model_id, local_files_only=True)
-    except Exception:
+    except Exception as ex:
+        _warn(f"no tokenizer files for {model_id!r} ({type(ex).__name__}); using the byte-level stand-in - "
+              "token ids differ from the reference's GPT-2 BPE")
         return ByteTokenizer()
+
+
+def load_pretrained(model_id: str):
+    """server.py:40-41: the hub model's weights, from the local cache first, then online.
+    Returns (dims, state_dict) or raises."""
+    from transformers import AutoModelForCausalLM
+    last = None
+    for kw in ({"local_files_only": True}, {}):
+        if not kw and os.environ.get("HF_HUB_OFFLINE", "") == "1":
+            break
+        try:
+            model = AutoModelForCausalLM.from_pretrained(model_id, **kw)
+            dims = W.dims_from_config(model.config.to_dict())
+            sd = {k: v.detach().to(torch.float32) for k, v in model.state_dict().items() if v.is_floating_point()}
+            return dims, sd
+        except Exception as ex:   # not cached / no network / not a GPT-2
+            last = ex
+    raise RuntimeError(f"cannot load pretrained weights for {model_id!r}: {last}")
 
 
 def read_env(env=None) -> Dict:
@@ -82,6 +112,8 @@ def read_env(env=None) -> Dict:
         "GP_SAMPLING": env.get("GP_SAMPLING", "greedy").lower(),
         "GP_SAMPLE_SEED": int(env.get("GP_SAMPLE_SEED", "0")),
         "GP_WEIGHTS": env.get("GP_WEIGHTS", ""),
+        "GP_RANDOM_INIT": env.get("GP_RANDOM_INIT", "0") == "1",
+        "GP_MAX_BATCH": int(env.get("GP_MAX_BATCH", "4")),
     }
 
 
@@ -106,9 +138,20 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
     if ckpt and weights is None:
         ck_dims, weights = W.load_checkpoint(ckpt)
         dims = dims or ck_dims
+    if weights is None and not cfg["GP_RANDOM_INIT"]:
+        try:
+            hub_dims, weights = load_pretrained(cfg["MODEL_ID"])
+            dims = dims or hub_dims
+        except Exception as ex:
+            raise RuntimeError(
+                f"{ex}.  Point GP_WEIGHTS (or MODEL_ID) at a local GPT-2 checkpoint, or set GP_RANDOM_INIT=1 to "
+                "serve a seeded random-init network of that shape on purpose.") from ex
     dims = dims or W.PRESETS.get(cfg["MODEL_ID"])
     if dims is None:
         raise ValueError(f"unknown MODEL_ID {cfg['MODEL_ID']!r}; known: {sorted(W.PRESETS)}")
+    if weights is None:
+        _warn(f"GP_RANDOM_INIT=1: serving a RANDOM-INIT {cfg['MODEL_ID']} (seed {cfg['GP_SEED']}); "
+              "outputs are not the pretrained model's")
     validate_split(dims, cfg["SPLIT_AT"])
     tokenizer = tokenizer or load_tokenizer(cfg["MODEL_ID"])
     dtype = GP_BF16 if cfg["GP_DTYPE"] == "bf16" else GP_F32

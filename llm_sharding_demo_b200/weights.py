@@ -124,6 +124,14 @@ def dims_from_config(cfg: dict) -> GPT2Dims:
     act = cfg.get("activation_function", "gelu_new")
     if act != "gelu_new":
         raise ValueError(f"activation_function={act!r}: only GPT-2's gelu_new is implemented")
+    H = int(cfg["n_embd"])
+    if cfg.get("n_inner") not in (None, 4 * H):
+        raise ValueError(f"n_inner={cfg['n_inner']}: the kernels implement the GPT-2 MLP width 4*n_embd={4 * H} only")
+    for flag in ("scale_attn_by_inverse_layer_idx", "reorder_and_upcast_attn"):
+        if cfg.get(flag):
+            raise ValueError(f"{flag}=True changes the attention arithmetic ([hf] modeling_gpt2.py) and is not implemented")
+    if cfg.get("scale_attn_weights", True) is False:
+        raise ValueError("scale_attn_weights=False is not implemented (scores are always scaled by head_dim**-0.5)")
     return GPT2Dims(n_layer=int(cfg["n_layer"]), n_embd=int(cfg["n_embd"]), n_head=int(cfg["n_head"]),
                     vocab_size=int(cfg.get("vocab_size", 50257)),
                     n_positions=int(cfg.get("n_positions", cfg.get("n_ctx", 1024))),

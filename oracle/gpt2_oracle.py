@@ -60,6 +60,12 @@ PRESETS: Dict[str, GPT2Dims] = {
     # small shapes used only by tests (ragged vocab, d=64 and d=32 heads)
     "mini": GPT2Dims(n_layer=4, n_embd=128, n_head=2, vocab_size=1041, n_positions=64),
     "mini32": GPT2Dims(n_layer=2, n_embd=96, n_head=3, vocab_size=523, n_positions=48),
+    # 8 blocks of the `mini` shape (8-stage pipelines), and the WIDTHS of gpt2-medium / gpt2-xl with two
+    # blocks and a small vocabulary: row ownership, chunking and staging of the persistent kernel depend on
+    # H, not on L, so these keep the oracle fast while covering configs[2] / configs[3] shapes
+    "mini8": GPT2Dims(n_layer=8, n_embd=128, n_head=2, vocab_size=1041, n_positions=64),
+    "wide1024": GPT2Dims(n_layer=2, n_embd=1024, n_head=16, vocab_size=1041, n_positions=64),
+    "wide1600": GPT2Dims(n_layer=2, n_embd=1600, n_head=25, vocab_size=1041, n_positions=64),
 }
 
 

@@ -183,6 +183,74 @@ def test_stage_pipeline_vs_oracle(L, dtype_name, preset, n_stages, B, P, n_new):
         assert e.kv_lengths() == [P + n_new - 1] * B
 
 
+# ------------------------------------------------- configs[2] / configs[3] WIDTHS (H = 1024, 1600) vs the oracle
+@pytest.mark.parametrize("dtype_name", ["f32", "bf16"])
+@pytest.mark.parametrize("preset", ["wide1024", "wide1600"])
+@pytest.mark.parametrize("B,flags", [(1, 0), (2, 0), (4, 0), (8, 0), (8, 4), (32, 0)])
+def test_medium_and_xl_widths_vs_oracle(L, dtype_name, preset, B, flags):
+    """Engine-level parity at the hidden sizes of GPT-2 medium (H=1024, 16 heads) and XL (H=1600, 25 heads) with
+    two blocks and a 1041-word vocabulary: the persistent kernel (B <= 8 in bf16 storage, <= 4 in fp32), the GEMV
+    kernels (flags=4: one kernel per op) and the tcgen05 / SIMT GEMM decode path (B=32), teacher-forced on the
+    oracle's ids.  The per-CTA row ranges (H/148 = 6.9 and 10.8 rows), chunk sizes and staging widths of these
+    shapes occur nowhere in the small presets."""
+    dims = O.PRESETS[preset]
+    w = O.init_weights(dims, 91, "dense")
+    dtype = L.GP_F32 if dtype_name == "f32" else L.GP_BF16
+    tol = TOL_F32 if dtype_name == "f32" else TOL_BF16
+    P, n_new = 5, 4
+    (eng,) = make_stages(L, dims, w, 1, dtype, max_batch=B, flags=flags)
+    g = torch.Generator().manual_seed(17)
+    prompt = torch.randint(0, dims.vocab_size, (B, P), generator=g)
+    ref_ids, ref_logits = O.generate_cached(w, dims, prompt, n_new, return_logits=True)
+    if dtype_name == "bf16":
+        _, ref_logits_w = O.generate_cached(rounded(w, torch.bfloat16), dims, prompt, n_new, teacher=ref_ids,
+                                            return_logits=True)
+    margins = O.top2_margin(ref_logits)
+    out, _ = run_prefill([eng], prompt)
+    worst = worst_w = 0.0
+    for t in range(n_new):
+        if t > 0:
+            out = run_decode([eng], ref_ids[:, P + t - 1])
+        lg = out["logits"].cpu()
+        worst = max(worst, float((lg - ref_logits[:, t]).abs().max()))
+        if dtype_name == "bf16":
+            worst_w = max(worst_w, float((lg - ref_logits_w[:, t]).abs().max()))
+        for b in range(B):
+            if margins[b, t] > 2 * tol:
+                assert int(out["next_ids"][b]) == int(ref_ids[b, P + t]), (b, t)
+    print(f"{preset} {dtype_name} B={B} flags={flags}: worst |dlogit| {worst:.3e} (vs rounded weights {worst_w:.3e})")
+    assert worst <= tol
+    assert worst_w <= TOL_BF16_W
+    assert eng.kv_lengths() == [P + n_new - 1] * B
+    # the whole loop on the device gives the same tokens as the step-by-step calls where the margin allows
+    got = eng.generate(prompt.to(torch.int32), n_new)
+    for b in range(B):
+        for t in range(n_new):
+            if float(margins[b, t]) <= 2 * tol:
+                break
+            assert int(got[b, P + t]) == int(ref_ids[b, P + t]), (b, t)
+
+
+def test_decode_into_a_full_kv_slot_is_refused(L):
+    """One step past max_ctx: GP_ESTATE with a message from every decode entry, nothing written past the slot
+    (the reference raises IndexError past wpe)."""
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 3, "dense")
+    for flags in (0, 4):
+        (eng,) = make_stages(L, dims, w, 1, L.GP_BF16, max_batch=2, flags=flags, max_ctx=8)
+        prompt = torch.randint(0, dims.vocab_size, (2, 7), generator=torch.Generator().manual_seed(1))
+        out, _ = run_prefill([eng], prompt)
+        out = run_decode([eng], out["next_ids"].cpu())          # position 7: fills the slot
+        assert eng.kv_lengths() == [8, 8]
+        with pytest.raises(L.GPError, match="max_ctx"):
+            run_decode([eng], out["next_ids"].cpu())
+        assert eng.kv_lengths() == [8, 8]
+        eng.kv_reset(1)
+        assert eng.kv_lengths() == [8, 0]
+        run_prefill([eng], prompt)                                # usable again after a reset / new prefill
+        assert eng.kv_lengths() == [7, 7]
+
+
 def test_pipeline_depth_does_not_change_results(L):
     """S = 1, 2, 4 on identical weights: same logits (the stage boundary carries fp32)."""
     dims = O.PRESETS["mini"]

@@ -16,7 +16,7 @@ TINY = L.PRESETS["tiny-gpt2"]
 
 
 def app_for(role, **kw):
-    env = {"SHARD_ROLE": role, "MODEL_ID": "sshleifer/tiny-gpt2", "SPLIT_AT": "1"}
+    env = {"SHARD_ROLE": role, "MODEL_ID": "sshleifer/tiny-gpt2", "SPLIT_AT": "1", "GP_RANDOM_INIT": "1"}
     env.update(kw.pop("env", {}))
     return S.create_app(env=env, tokenizer=S.ByteTokenizer(), **kw)
 
@@ -66,9 +66,31 @@ def test_generate_zero_tokens_returns_prompt_without_gpu(golden_dir):
 def test_split_validation_rejects_the_shipped_k8s_mismatch():
     S.validate_split(L.PRESETS["gpt2"], 6)
     with pytest.raises(ValueError):
-        S.create_app(env={"SHARD_ROLE": "a", "SPLIT_AT": "2", "MODEL_ID": "sshleifer/tiny-gpt2"})  # 2 of 2 layers
+        S.create_app(env={"SHARD_ROLE": "a", "SPLIT_AT": "2", "MODEL_ID": "sshleifer/tiny-gpt2",
+                          "GP_RANDOM_INIT": "1"})  # 2 of 2 layers
     with pytest.raises(ValueError):
-        S.create_app(env={"MODEL_ID": "nope"})
+        S.create_app(env={"MODEL_ID": "nope", "GP_RANDOM_INIT": "1"})
+
+
+def test_server_refuses_to_start_on_a_random_network_by_accident(monkeypatch):
+    """server.py:40-41 loads the pretrained model; without weights (no checkpoint, nothing cached, no network)
+    the mirror must fail at start-up instead of answering 200 from a random init - unless GP_RANDOM_INIT=1."""
+    monkeypatch.setenv("HF_HUB_OFFLINE", "1")
+    with pytest.raises(RuntimeError, match="GP_RANDOM_INIT"):
+        S.create_app(env={"SHARD_ROLE": "a", "MODEL_ID": "sshleifer/tiny-gpt2", "SPLIT_AT": "1"},
+                     tokenizer=S.ByteTokenizer())
+    app = S.create_app(env={"SHARD_ROLE": "a", "MODEL_ID": "sshleifer/tiny-gpt2", "SPLIT_AT": "1",
+                            "GP_RANDOM_INIT": "1"}, tokenizer=S.ByteTokenizer())
+    assert app.state.cfg["GP_RANDOM_INIT"] is True
+
+
+def test_checkpoint_configs_that_change_the_arithmetic_are_rejected():
+    base = {"n_layer": 2, "n_embd": 8, "n_head": 2}
+    assert L.weights.dims_from_config(dict(base, n_inner=32)).n_embd == 8
+    for bad in ({"n_inner": 16}, {"scale_attn_by_inverse_layer_idx": True}, {"reorder_and_upcast_attn": True},
+                {"activation_function": "relu"}, {"scale_attn_weights": False}):
+        with pytest.raises(ValueError):
+            L.weights.dims_from_config(dict(base, **bad))
 
 
 # ------------------------------------------------------------------------------------ GPU

@@ -38,6 +38,13 @@ def test_static_scratch_entry_matches_allocating_entry_twice_in_a_row(dt):
         tol = 2e-4 if dt == torch.float32 else 2e-3
         assert float((got_logits - ref_logits).abs().max()) <= tol
         assert torch.equal(got_ids, ref_ids)
+        # and against plain fp32 torch on the storage-rounded weights (ln_f -> h wte^T -> argmax, server.py:101-102)
+        xn = torch.nn.functional.layer_norm(x, (H,), gm, bt, 1e-5)
+        want = xn @ wte.float().t()
+        assert float((got_logits - want).abs().max()) <= 5e-3
+        top2 = torch.topk(want, 2, dim=-1).values
+        firm = (top2[:, 0] - top2[:, 1]) > 1e-2
+        assert torch.equal(got_ids[firm].long(), want.argmax(-1)[firm])
         again = ops.lmhead_argmax_static(x, gm, bt, wte)
         torch.cuda.synchronize()
         assert torch.equal(again, ref_ids)
