@@ -173,8 +173,9 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_p
 def ids_check(workload, dims, seed, dtype, out, P, n_new, device):
     """Parity of the ids the timed runs produced (rank 0, outside every timed region):
       (1) default workload: sequence 0 is the prompt of tests/golden/gpt2_124m.npz, whose continuation came from
-          the reference's own /forward + /forward_b routes (oracle/make_golden.py): tokens must be equal up to the
-          first position whose reference top-2 margin is within twice the storage tolerance;
+          the reference's own /forward + /forward_b routes (oracle/make_golden.py): while the two sequences share
+          their prefix, tokens must be equal at every position whose reference top-2 margin exceeds twice the
+          storage tolerance (a flip below that margin is allowed and ends the comparison);
       (2) every sequence: a STATELESS full-sequence pass over the finished sequence on a separate single-stage
           engine (prefill kernels: tcgen05 GEMMs + causal attention, no KV cache, no persistent kernel, no stage
           boundary) must have the generated token as its argmax wherever its top-2 margin exceeds twice the tolerance.
@@ -189,10 +190,13 @@ def ids_check(workload, dims, seed, dtype, out, P, n_new, device):
         if z["prompt_ids"].tolist() == out[0, :P].tolist():
             ref = z["greedy_ids"][P:]
             for t in range(min(len(ref), n_new)):
-                if float(z["margins"][t]) <= 2 * tol:
+                firm = float(z["margins"][t]) > 2 * tol
+                same = int(out[0, P + t]) == int(ref[t])
+                if firm:
+                    res["golden_checked"] += 1
+                    res["golden_mismatch"] += int(not same)
+                if not same:     # a flip (allowed only below the margin rule) ends the common prefix
                     break
-                res["golden_checked"] += 1
-                res["golden_mismatch"] += int(int(out[0, P + t]) != int(ref[t]))
     if n_new > 0:
         eng = L.StageEngine(dims, dtype=dtype, max_batch=1, max_ctx=P + n_new, max_tokens=P + n_new, device=device)
         eng.load_weights(L.init_weights(dims, seed, "hf"))

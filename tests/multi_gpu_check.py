@@ -33,10 +33,12 @@ def oracle_agreement(out, w, odims, prompts, n_new, margin):
     checked = 0
     for b in range(prompts.shape[0]):
         for t in range(n_new):
-            if float(margins[b, t]) <= margin:   # free-running: stop at the first position a flip is allowed
+            same = int(out[b, P + t]) == int(ref_ids[b, P + t])
+            if float(margins[b, t]) > margin:
+                assert same, (b, t)
+                checked += 1
+            if not same:   # free-running: a flip below the margin rule ends the common prefix
                 break
-            assert int(out[b, P + t]) == int(ref_ids[b, P + t]), (b, t)
-            checked += 1
     return checked
 
 
