@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define GP_VERSION 100
+#define GP_VERSION 200
 
 #define GP_OK 0
 #define GP_EINVAL (-1)   /* bad argument / shape / state              */
@@ -122,6 +122,15 @@ int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, in
                     int32_t slot0, float* hidden_out, float* logits, int32_t* next_ids,
                     void* stream);
 
+/* gp_stage_decode for an arbitrary set of KV slots (continuous batching, SURVEY.md 8(f) N3: requests join and leave
+ * between steps, so the sequences of a step do not sit in adjacent slots).  slots_host: B distinct slot numbers
+ * (HOST memory); row b of ids / hidden_in / hidden_out / logits / next_ids belongs to slot slots_host[b].
+ * bf16 storage, head_dim 64, 1 <= B <= 8, greedy selection.  The reference serves one request at a time
+ * (server.py:154-169). */
+int gp_stage_decode_slots(gp_engine* e, const int32_t* ids, const float* hidden_in, int32_t B,
+                          const int32_t* slots_host, float* hidden_out, float* logits, int32_t* next_ids,
+                          void* stream);
+
 /* The coordinator loop of server.py:169-206 with greedy selection, run entirely on the
  * device by a single-stage engine (has_embed && has_head): prefill the prompts, then
  * n_new-1 cached decode steps; only token ids cross PCIe.
@@ -155,10 +164,17 @@ int gp_set_sampler(gp_engine* e, float temperature, int32_t top_k, uint64_t seed
  *     micro-batches (B sequences each, KV slots [m*B,(m+1)*B)); call it on every stage at the same
  *     time.  comm_epoch0 must be the same on all stages and larger than any used before
  *     (previous comm_epoch0 + n_rounds).  Stage 0: first_ids int32 [n_streams*B] (tokens the
- *     prefill produced) -> tokens_out int32 [n_streams*B, n_rounds].  Returns GP_ECUDA if the
- *     kernel has not finished after timeout_ms (a peer is missing). */
+ *     prefill produced) -> tokens_out int32 [n_streams*B, n_rounds].
+ *     timeout_ms > 0 arms a watchdog on PROGRESS: when no item finished for timeout_ms (a peer stage is missing or
+ *     stalled - the reference's `timeout=30`, server.py:173,179) the kernel is told to stop waiting, drains within
+ *     milliseconds, and the call returns GP_ECUDA with the GPU idle; the KV slots are then undefined until
+ *     gp_kv_reset.  (fp32 storage runs the first-generation kernel, which can only report the timeout.) */
 int gp_comm_export(gp_engine* e, void* handle_host);
 int gp_comm_connect(gp_engine* e, const void* peer_handle_host);
+/* The same connection for a host that owns several GPUs in ONE process (CUDA IPC handles cannot be opened by the
+ * process that exported them): `peer` is the engine this stage feeds; peer access is enabled when the two sit on
+ * different devices.  `peer` must outlive `e`'s use of the connection. */
+int gp_comm_connect_local(gp_engine* e, gp_engine* peer);
 int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds, int32_t n_streams, int32_t B,
                        uint32_t comm_epoch0, int32_t* tokens_out, int32_t timeout_ms, float* ms_host,
                        void* stream);

@@ -49,6 +49,8 @@ SIGNATURES = {
     "gp_last_launch_count": (C.c_int64, [_P]),
     "gp_comm_export": (C.c_int, [_P, _P]),
     "gp_comm_connect": (C.c_int, [_P, _P]),
+    "gp_comm_connect_local": (C.c_int, [_P, _P]),
+    "gp_stage_decode_slots": (C.c_int, [_P, _P, _P, _I, _P, _P, _P, _P, _P]),
     "gp_pipeline_decode": (C.c_int, [_P, _P, _I, _I, _I, _U, _P, _I, C.POINTER(C.c_float), _P]),
     "gp_op_embed": (C.c_int, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "gp_op_layernorm": (C.c_int, [_P, _P, _P, _P, _I, _I, _F, _U, _P]),

@@ -83,6 +83,13 @@ struct gp_engine {
   unsigned char* peer_inbox = nullptr;  // next stage's inbox (stage 0's for the last stage), cudaIpcOpenMemHandle
   bool peer_is_ipc = false;
   uint32_t mega_epoch = 8;
+  // watchdog words of the persistent kernel: ctrl[0] = abort (host -> kernel), ctrl[1] = items finished (kernel -> host);
+  // written / read through a side stream and a pinned host word while the kernel runs
+  int* ctrl = nullptr;
+  int* ctrl_host = nullptr;
+  cudaStream_t ctrl_stream = nullptr;
+  int32_t* slot_map = nullptr;     // [64] KV slot of every sequence of a slot-indexed decode step
+  bool coop_ok = true;             // the persistent kernels can be co-scheduled on this device / context
   unsigned long long* step_clock = nullptr;
   bool mega_uploaded = false;
   long long* trace = nullptr;
@@ -203,9 +210,15 @@ int slot_room(gp_engine* e, const char* who, int slot0, int n, int steps) {
   return GP_OK;
 }
 
+// second-generation persistent kernel (k_mega2.cu): bf16 storage, up to 8 sequences, tensor-core rows
+bool use_mega2(const gp_engine* e, int B) {
+  static const bool force_v1 = getenv("GP_MEGA_V1") != nullptr;
+  return !force_v1 && e->cfg.dtype == GP_BF16 && mega2_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms);
+}
 bool use_mega(const gp_engine* e, int B) {
-  // the persistent kernel fuses the greedy argmax; sampled decoding runs the per-op kernels
-  return !e->sampler_on && !(e->cfg.flags & GP_FLAG_NO_MEGA) && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms);
+  // the persistent kernels fuse the greedy argmax; sampled decoding runs the per-op kernels
+  if (e->sampler_on || (e->cfg.flags & GP_FLAG_NO_MEGA) || !e->coop_ok) return false;
+  return use_mega2(e, B) || (e->L > 0 && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms));
 }
 
 int upload_mega_layers(gp_engine* e) {
@@ -225,6 +238,7 @@ int upload_mega_layers(gp_engine* e) {
 // one launch = n_steps cached decode steps of this stage (n_steps > 1 only for single-stage engines)
 struct PipeArgs {
   int n_streams = 1; uint32_t comm_epoch0 = 0; int32_t* tok_out = nullptr; int tok_stride = 0; bool on = false;
+  bool slot_indexed = false;   // KV slots come from e->slot_map instead of slot0 + index
 };
 size_t inbox_bytes(const gp_engine* e) { return 1024 + (size_t)64 * e->H * 8; }
 
@@ -249,7 +263,9 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
     if (c.has_head) p.peer_ids = reinterpret_cast<unsigned long long*>(e->peer_inbox);
     else p.peer_hid = reinterpret_cast<unsigned long long*>(e->peer_inbox + 1024);
   }
-  const uint32_t span = mega_epochs_per_launch(e->L, n_steps * pipe.n_streams);
+  const bool v2 = use_mega2(e, B);
+  if (pipe.slot_indexed && !v2) { set_err(e, "slot-indexed decode needs the bf16 persistent kernel (B <= 8, head_dim 64)"); return GP_EINVAL; }
+  const uint32_t span = v2 ? mega2_epochs_per_launch(e->L, n_steps * pipe.n_streams) : mega_epochs_per_launch(e->L, n_steps * pipe.n_streams);
   if (e->mega_epoch > 0xFFFFFFFFu - span - 8u) {
     // epoch counter about to wrap: start over on zeroed exchange buffers
     const size_t MBx = c.max_batch;
@@ -279,7 +295,28 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
     CK(e, cudaMemsetAsync(e->trace, 0, (size_t)e->num_sms * kTraceCap * sizeof(long long), s));
     p.trace = e->trace; p.trace_cap = kTraceCap;
   }
-  LAUNCH(e, launch_decode_mega(p, c.dtype, e->num_sms, s));
+  if (v2) {
+    p.slot_map = pipe.slot_indexed ? e->slot_map : nullptr;
+    p.abort_flag = e->ctrl; p.progress = reinterpret_cast<unsigned int*>(e->ctrl + 1);
+    CK(e, cudaMemsetAsync(e->ctrl, 0, 2 * sizeof(int), s));
+    cudaError_t le = launch_decode_mega2(p, e->num_sms, s);
+    if (le == cudaErrorCooperativeLaunchTooLarge || le == cudaErrorLaunchOutOfResources) {
+      cudaGetLastError();
+      e->coop_ok = false;   // callers fall back to one kernel per op from now on
+      set_err(e, "persistent kernel cannot be co-scheduled here (%s)", cudaGetErrorString(le));
+      return GP_ESTATE;
+    }
+    LAUNCH(e, le);
+  } else {
+    cudaError_t le = launch_decode_mega(p, c.dtype, e->num_sms, s);
+    if (le == cudaErrorCooperativeLaunchTooLarge || le == cudaErrorLaunchOutOfResources) {
+      cudaGetLastError();
+      e->coop_ok = false;
+      set_err(e, "persistent kernel cannot be co-scheduled here (%s)", cudaGetErrorString(le));
+      return GP_ESTATE;
+    }
+    LAUNCH(e, le);
+  }
   if (trace) {
     std::vector<long long> t((size_t)e->num_sms * kTraceCap);
     CK(e, cudaStreamSynchronize(s));
@@ -363,7 +400,11 @@ int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   int r = check_ready(e);
   if (r != GP_OK) return r;
 
-  if (use_mega(e, B)) return decode_mega(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, seq, 1, false, s);
+  if (use_mega(e, B)) {
+    r = decode_mega(e, ids, hidden_in, B, slot0, hidden_out, logits, next_ids, seq, 1, false, s);
+    if (r != GP_ESTATE || e->coop_ok) return r;
+    // the cooperative launch was refused (MPS / MIG / SM-limited context): one kernel per op instead
+  }
 
   // GEMV kernels: fp32 mode and odd shapes; in bf16 mode more than 4 rows go to the tcgen05 GEMMs
   const bool tc_ok = bf(e) && !(c.flags & GP_FLAG_NO_TCGEN05) && gemm_tc_supported(B, H, H);
@@ -372,6 +413,10 @@ int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   const uint32_t oflag = obf ? GP_OUT_BF16 : 0u;
 
   const float* cur = hidden_in;  // current residual stream [B,H]
+  if (e->L == 0 && !c.has_embed) {   // head-only stage: the lm_head below reads e->h
+    CK(e, cudaMemcpyAsync(e->h, hidden_in, (size_t)B * H * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    cur = e->h;
+  }
   if (c.has_embed) {
     LAUNCH(e, launch_embed(ids, nullptr, 0, 1, e->lens, slot0, e->wte, e->wpe, e->h, B, H, e->V, c.n_positions, c.dtype, s));
     cur = e->h;
@@ -473,7 +518,8 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   *out = nullptr;
   if (cfg->n_embd <= 0 || cfg->n_head <= 0 || cfg->n_embd % cfg->n_head != 0 || cfg->vocab_size <= 0 ||
       cfg->n_positions <= 0 || cfg->n_layer <= 0 || cfg->layer_begin < 0 || cfg->layer_end > cfg->n_layer ||
-      cfg->layer_begin >= cfg->layer_end || cfg->max_batch <= 0 || cfg->max_ctx <= 0 ||
+      cfg->layer_begin > cfg->layer_end || (cfg->layer_begin == cfg->layer_end && !(cfg->has_head && !cfg->has_embed)) ||
+      cfg->max_batch <= 0 || cfg->max_ctx <= 0 ||
       cfg->max_ctx > cfg->n_positions || (cfg->dtype != GP_F32 && cfg->dtype != GP_BF16)) {
     set_err(nullptr, "gp_engine_create: invalid configuration");
     return GP_EINVAL;
@@ -567,6 +613,21 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRYCK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
   if (e->num_sms > 1024) e->num_sms = 1024;
   TRYCK(init_mega_attrs());
+  TRYCK(init_mega2_attrs());
+  TRY(alloc((void**)&e->ctrl, 2 * sizeof(int)));
+  TRYCK(cudaMemsetAsync(e->ctrl, 0, 2 * sizeof(int), e->stream));
+  TRY(alloc((void**)&e->slot_map, 64 * sizeof(int32_t)));
+  TRYCK(cudaHostAlloc((void**)&e->ctrl_host, 2 * sizeof(int), cudaHostAllocDefault));
+  TRYCK(cudaStreamCreateWithFlags(&e->ctrl_stream, cudaStreamNonBlocking));
+  {
+    // The persistent kernels spin on each other: the whole grid must be co-resident.  Under MPS / MIG / a green or
+    // SM-limited context that may be impossible; then decode runs one kernel per op.
+    int coop = 0;
+    TRYCK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, cfg->device));
+    e->coop_ok = coop != 0;
+    if (e->coop_ok && cfg->dtype == GP_BF16 && mega2_supported(1, e->H, e->nh, e->L, cfg->dtype, e->num_sms))
+      e->coop_ok = mega2_max_coresident(1, e->H, e->L) >= 1;
+  }
   TRYCK(cudaStreamSynchronize(e->stream));
 #undef TRY
 #undef TRYCK
@@ -586,6 +647,8 @@ int gp_engine_destroy(gp_engine* e) {
   if (e->trace) cudaFree(e->trace);
   if (e->peer_inbox && e->peer_is_ipc) cudaIpcCloseMemHandle(e->peer_inbox);
   if (e->inbox) cudaFree(e->inbox);
+  if (e->ctrl_host) cudaFreeHost(e->ctrl_host);
+  if (e->ctrl_stream) cudaStreamDestroy(e->ctrl_stream);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return GP_OK;
@@ -809,12 +872,15 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
   }
   CK(e, cudaEventRecord(e->events[1], s));
   const int steps = n_new > 1 ? n_new - 1 : 0;
-  const bool mega = steps > 0 && use_mega(e, B);
+  bool mega = steps > 0 && use_mega(e, B);
   if (mega) {
     // the whole greedy loop is ONE persistent launch; per-step times come from %globaltimer
     int r = decode_mega(e, e->mailbox, nullptr, B, 0, nullptr, nullptr, e->mailbox, e->seq, steps,
                         timings_ms_host != nullptr, s);
-    if (r != GP_OK) return r;
+    if (r == GP_ESTATE && !e->coop_ok) mega = false;   // cooperative launch refused: one kernel per op below
+    else if (r != GP_OK) return r;
+  }
+  if (mega) {
   } else if (steps > 0) {
     const bool use_graph = !(c.flags & GP_FLAG_NO_GRAPH);
     cudaGraphExec_t exec = nullptr;
@@ -906,6 +972,62 @@ int gp_comm_connect(gp_engine* e, const void* peer_handle_host) {
   return GP_OK;
 }
 
+int gp_comm_connect_local(gp_engine* e, gp_engine* peer) {
+  if (!e || !peer) { set_err(e, "gp_comm_connect_local: NULL argument"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(peer->cfg.device));
+  if (!peer->inbox) {
+    CK(e, cudaMalloc((void**)&peer->inbox, inbox_bytes(peer)));
+    CK(e, cudaMemset(peer->inbox, 0, inbox_bytes(peer)));
+    CK(e, cudaDeviceSynchronize());
+  }
+  if (inbox_bytes(peer) != inbox_bytes(e)) { set_err(e, "gp_comm_connect_local: the two stages have different hidden sizes"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(e->cfg.device));
+  if (peer->cfg.device != e->cfg.device) {
+    int can = 0;
+    CK(e, cudaDeviceCanAccessPeer(&can, e->cfg.device, peer->cfg.device));
+    if (!can) { set_err(e, "gp_comm_connect_local: device %d cannot access device %d", e->cfg.device, peer->cfg.device); return GP_ECUDA; }
+    cudaError_t pe = cudaDeviceEnablePeerAccess(peer->cfg.device, 0);
+    if (pe == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+    else CK(e, pe);
+  }
+  if (e->peer_inbox && e->peer_is_ipc) cudaIpcCloseMemHandle(e->peer_inbox);
+  e->peer_inbox = peer->inbox;
+  e->peer_is_ipc = false;
+  return GP_OK;
+}
+
+int gp_stage_decode_slots(gp_engine* e, const int32_t* ids, const float* hidden_in, int32_t B, const int32_t* slots_host,
+                          float* hidden_out, float* logits, int32_t* next_ids, void* stream) {
+  if (!e || !slots_host) { set_err(e, "gp_stage_decode_slots: NULL argument"); return GP_EINVAL; }
+  const gp_config& c = e->cfg;
+  if (B < 1 || B > 8) { set_err(e, "gp_stage_decode_slots: B=%d outside [1,8]", B); return GP_EINVAL; }
+  for (int i = 0; i < B; ++i) {
+    if (slots_host[i] < 0 || slots_host[i] >= c.max_batch) { set_err(e, "gp_stage_decode_slots: slot %d outside [0,%d)", slots_host[i], c.max_batch); return GP_EINVAL; }
+    for (int j = 0; j < i; ++j)
+      if (slots_host[j] == slots_host[i]) { set_err(e, "gp_stage_decode_slots: slot %d listed twice", slots_host[i]); return GP_EINVAL; }
+    int room = slot_room(e, "gp_stage_decode_slots", slots_host[i], 1, 1);
+    if (room != GP_OK) return room;
+  }
+  if (c.has_embed ? ids == nullptr : hidden_in == nullptr) { set_err(e, "gp_stage_decode_slots: missing input pointer"); return GP_EINVAL; }
+  if (!c.has_head && hidden_out == nullptr) { set_err(e, "gp_stage_decode_slots: hidden_out is NULL"); return GP_EINVAL; }
+  CK(e, cudaSetDevice(c.device));
+  int r = check_ready(e);
+  if (r != GP_OK) return r;
+  if (!use_mega(e, B) || !use_mega2(e, B)) {
+    set_err(e, "gp_stage_decode_slots: needs the bf16 persistent kernel (head_dim 64, B <= 8, greedy selection)");
+    return GP_EINVAL;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  e->launches = 0;
+  CK(e, cudaMemcpyAsync(e->slot_map, slots_host, B * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+  PipeArgs pa;
+  pa.slot_indexed = true;
+  r = decode_mega(e, ids, hidden_in, B, 0, hidden_out, logits, next_ids, nullptr, 1, false, s, pa);
+  if (r == GP_OK)
+    for (int i = 0; i < B; ++i) ++e->hlens[slots_host[i]];
+  return r;
+}
+
 int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds, int32_t n_streams, int32_t B,
                        uint32_t comm_epoch0, int32_t* tokens_out, int32_t timeout_ms, float* ms_host, void* stream) {
   if (!e) return GP_EINVAL;
@@ -918,7 +1040,7 @@ int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds,
   if (!e->inbox || !e->peer_inbox) { set_err(e, "gp_pipeline_decode: stage boundary not connected (gp_comm_export / gp_comm_connect)"); return GP_ESTATE; }
   if (c.has_embed && (!first_ids || !tokens_out)) { set_err(e, "gp_pipeline_decode: stage 0 needs first_ids and tokens_out"); return GP_EINVAL; }
   if (e->sampler_on) { set_err(e, "gp_pipeline_decode: the device-resident pipeline selects greedily; sampled decoding runs per step (gp_stage_decode)"); return GP_ESTATE; }
-  if (!use_mega(e, B)) { set_err(e, "gp_pipeline_decode: shape outside the persistent kernel's envelope (B<=4, head_dim 64)"); return GP_EINVAL; }
+  if (!use_mega(e, B)) { set_err(e, "gp_pipeline_decode: outside the persistent kernel's envelope (head_dim 64; B <= 8 in bf16 storage, <= 4 in fp32; cooperative launch available)"); return GP_EINVAL; }
   CK(e, cudaSetDevice(c.device));
   int r = check_ready(e);
   if (r != GP_OK) return r;
@@ -938,21 +1060,55 @@ int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds,
   if (r != GP_OK) return r;
   for (int i = 0; i < n_streams * B; ++i) e->hlens[i] += n_rounds;
   CK(e, cudaEventRecord(e->events[1], s));
-  // host watchdog: the kernel waits on other GPUs; if a peer never shows up report it instead of hanging forever
-  const double t0 = (double)clock() / CLOCKS_PER_SEC;
-  struct timespec ts0; clock_gettime(CLOCK_MONOTONIC, &ts0);
-  for (;;) {
-    cudaError_t q = cudaEventQuery(e->events[1]);
-    if (q == cudaSuccess) break;
-    if (q != cudaErrorNotReady) { CK(e, q); }
-    struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
-    const double el = (ts.tv_sec - ts0.tv_sec) * 1e3 + (ts.tv_nsec - ts0.tv_nsec) * 1e-6;
-    if (timeout_ms > 0 && el > timeout_ms) {
-      set_err(e, "gp_pipeline_decode: no progress after %d ms (a peer stage is missing); the kernel is still spinning - terminate the process", timeout_ms);
+  // Host watchdog.  The kernel waits on other GPUs; what is watched is PROGRESS (items finished, a device word the
+  // kernel bumps), not elapsed time, so a long healthy run is never cut short.  When nothing moved for timeout_ms the
+  // abort word is set through a side stream: every wait in the kernel then falls through, the launch runs to its end
+  // within milliseconds on whatever data is there, and the call returns an error with the GPU idle and the engine
+  // usable (KV slots hold garbage: gp_kv_reset before the next request).  The reference's counterpart is
+  // `timeout=30` + raise_for_status (server.py:173-174,179-180).
+  {
+    struct timespec t_last; clock_gettime(CLOCK_MONOTONIC, &t_last);
+    int last_prog = -1, polls = 0;
+    bool aborted = false;
+    for (;;) {
+      cudaError_t q = cudaEventQuery(e->events[1]);
+      if (q == cudaSuccess) break;
+      if (q != cudaErrorNotReady) { CK(e, q); }
+      struct timespec nap = {0, 50 * 1000};
+      nanosleep(&nap, nullptr);
+      if (timeout_ms <= 0 || (++polls & 31) != 0) continue;     // look at the progress word every ~2 ms
+      struct timespec now; clock_gettime(CLOCK_MONOTONIC, &now);
+      if (use_mega2(e, B)) {
+        CK(e, cudaMemcpyAsync(e->ctrl_host, e->ctrl + 1, sizeof(int), cudaMemcpyDeviceToHost, e->ctrl_stream));
+        CK(e, cudaStreamSynchronize(e->ctrl_stream));
+        if (e->ctrl_host[0] != last_prog) { last_prog = e->ctrl_host[0]; t_last = now; }
+      }
+      const double idle = (now.tv_sec - t_last.tv_sec) * 1e3 + (now.tv_nsec - t_last.tv_nsec) * 1e-6;
+      if (idle <= timeout_ms) continue;
+      if (!use_mega2(e, B)) {
+        set_err(e, "gp_pipeline_decode: not finished after %d ms (a peer stage is missing?); the fp32 persistent kernel cannot be "
+                   "aborted - terminate the process", timeout_ms);
+        return GP_ECUDA;
+      }
+      if (!aborted) {
+        e->ctrl_host[1] = 1;
+        CK(e, cudaMemcpyAsync(e->ctrl, e->ctrl_host + 1, sizeof(int), cudaMemcpyHostToDevice, e->ctrl_stream));
+        CK(e, cudaStreamSynchronize(e->ctrl_stream));
+        aborted = true;
+        t_last = now;                                            // give the kernel timeout_ms more to drain
+        continue;
+      }
+      set_err(e, "gp_pipeline_decode: the kernel did not drain after the abort request");
+      return GP_ECUDA;
+    }
+    if (aborted) {
+      for (int i = 0; i < n_streams * B; ++i) e->hlens[i] -= n_rounds;
+      set_err(e, "gp_pipeline_decode: no progress for %d ms after %d of %d items (a peer stage is missing or stalled); the launch "
+                 "was aborted, the GPU is idle, KV slots are undefined until gp_kv_reset", timeout_ms, last_prog < 0 ? 0 : last_prog,
+              n_rounds * n_streams);
       return GP_ECUDA;
     }
   }
-  (void)t0;
   if (ms_host) CK(e, cudaEventElapsedTime(ms_host, e->events[0], e->events[1]));
   return GP_OK;
 }

@@ -1,0 +1,1157 @@
+// Persistent decode kernel, second generation (bf16 storage, 1..8 sequences per step).
+//
+// Same contract as k_mega.cu - ONE cooperative launch runs every phase of every layer of every decode step of a
+// stage, CTAs exchange activations through "flag-in-data" words in L2, warp 15 streams the CTA's weight rows
+// HBM -> shared memory with TMA bulk copies - but rebuilt around what the round-1 phase trace showed to cost time:
+//
+//  * ONE copy of the code for all phases.  A step is ~60 phases that differ in parameters only.  The first kernel
+//    gave every phase of a layer its own constant-propagated copy of the staging / row routines (130 KB of SASS
+//    against a 32 KB instruction cache: every phase began on cold fetches).  Here a single loop walks the phases;
+//    what differs (matrix, K, N, source / destination buffer, epilogue) comes from small tables in shared memory.
+//  * rows on the tensor cores (mma.sync m16n8k16, bf16 x bf16 -> fp32).  The weight rows are the B operand (8 rows
+//    per instruction), the activations the A operand: row m < 8 of A holds the bf16 ROUNDING of sequence m's
+//    vector and row m + 8 its bf16 RESIDUAL (x - hi), so hi * w + lo * w reproduces the fp32 activation to ~2^-17
+//    inside one instruction and up to 8 sequences cost what one costs (B <= 4; 5..8 sequences use the rounding
+//    only, like the prefill GEMMs).  The K range of a chunk is split over the 15 consumer warps, partial tiles are
+//    summed through shared memory in a fixed order (deterministic).  No shuffle reductions, no per-sequence FMA loop.
+//  * weight rows land in shared memory with a 16-byte pad per row (one cp.async.bulk per row, issued by the 32
+//    lanes of the producer warp), which makes both fragment loads bank-conflict free.
+//  * LayerNorm with one block-wide exchange: per-warp (count, mean, M2) merged with Chan's formula.
+//  * decode attention "scores first": every thread owns ONE cached key (its 64-wide row is prefetched into
+//    registers before q arrives), the softmax weights never leave the warp (online softmax per warp), P.V runs over
+//    the warp's own keys, and the 15 per-warp partials merge through shared memory - 2 block barriers per task.
+//  * every spin loop polls an abort word the host can set (watchdog), a progress word counts finished items, and
+//    the KV slot of each sequence comes from a slot table (non-contiguous batches for continuous batching).
+//
+// Arithmetic per element restates [hf] modeling_gpt2.py:262-309 (GPT2Block), :144-226 (attention over the cache),
+// pytorch_utils.py:119-123 (Conv1D), activations.py:59-66 (gelu_new); greedy selection = server.py:187-205 with
+// lowest index winning ties.
+#include <cstdlib>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gp {
+namespace {
+
+typedef unsigned long long u64;
+
+constexpr int kNW = 15;                    // consumer warps (+1 producer warp)
+constexpr int kConsumers = kNW * 32;       // 480
+constexpr int kThreads = kConsumers + 32;  // 512
+constexpr int kMaxSlots = 6;
+constexpr int kSlotBias = 128;             // fp32 bias window of a chunk (<= 24 rows + alignment slack)
+constexpr int kMaxRows = 24;               // rows per chunk = 3 groups of 8
+constexpr int kOwnMax = 16;                // residual rows one CTA owns
+constexpr int kLnPairs = 2;                // LayerNorm: element pairs per thread and sequence (H <= 1920)
+constexpr int kFlagStride = 256;
+constexpr int kD = 64;                     // head dimension
+constexpr int kVPre = 8;                   // V values of a warp's keys prefetched before q arrives
+constexpr int kSpinCheck = 255;            // spin loops look at the abort word every 256 polls
+
+enum { K_QKV = 0, K_ATTN = 1, K_PROJ = 2, K_FC = 3, K_PROJ2 = 4, K_HEAD = 5 };
+enum { SRC_LL = 0, SRC_PLAIN = 1, SRC_EMBED = 2, SRC_INBOX = 3 };
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try(bar, parity)) {}
+}
+__device__ __forceinline__ uint64_t l2_stream_policy(bool evict_first) {
+  uint64_t pol;
+  if (evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
+__device__ __forceinline__ u64 globaltimer() {
+  u64 t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// ---- flag-in-data words {epoch:32 | payload:32}
+__device__ __forceinline__ void ll_store(u64* p, uint32_t bits, uint32_t epoch) {
+  const u64 w = ((u64)epoch << 32) | (u64)bits;
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ void ll_store_sys(u64* p, uint32_t bits, uint32_t epoch) {
+  const u64 w = ((u64)epoch << 32) | (u64)bits;
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ u64 ll_load(const u64* p) {
+  u64 w;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+  return w;
+}
+__device__ __forceinline__ u64 ll_load_sys(const u64* p) {
+  u64 w;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+  return w;
+}
+// predicated (no branch, no access when `on` is false): lanes beyond the end of a row must not fall back to a
+// clamped address - 148 CTAs re-reading ONE word turn it into an L2 hot spot
+__device__ __forceinline__ u64 ll_load_if(const u64* p, bool on) {
+  u64 w;
+  asm volatile(
+      "{\n"
+      ".reg .pred q;\n"
+      "setp.ne.u32 q, %2, 0;\n"
+      "mov.u64 %0, 0;\n"
+      "@q ld.relaxed.gpu.global.u64 %0, [%1];\n"
+      "}\n"
+      : "=l"(w)
+      : "l"(p), "r"((uint32_t)on)
+      : "memory");
+  return w;
+}
+// two adjacent words with one 16-byte access; each 64-bit half is single-copy atomic and carries its own epoch
+__device__ __forceinline__ void ll_load2_if(const u64* p, bool on, bool sys, u64& a, u64& b) {
+  if (sys) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.u32 q, %3, 0;\n"
+        "mov.u64 %0, 0;\n"
+        "mov.u64 %1, 0;\n"
+        "@q ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];\n"
+        "}\n"
+        : "=l"(a), "=l"(b)
+        : "l"(p), "r"((uint32_t)on)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.u32 q, %3, 0;\n"
+        "mov.u64 %0, 0;\n"
+        "mov.u64 %1, 0;\n"
+        "@q ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];\n"
+        "}\n"
+        : "=l"(a), "=l"(b)
+        : "l"(p), "r"((uint32_t)on)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void red_add_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32(const uint8_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
+
+// D(16x8, fp32) += A(16x16, bf16, row) * B(16x8, bf16, col)
+__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// x0, x1 -> packed bf16 roundings (low half = x0) and packed bf16 residuals
+__device__ __forceinline__ void split_hi_lo(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
+  const __nv_bfloat16 l0 = __float2bfloat16_rn(x0 - __bfloat162float(h0)), l1 = __float2bfloat16_rn(x1 - __bfloat162float(h1));
+  hi = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+  lo = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+}
+
+struct Ring {
+  uint8_t* slots;
+  uint64_t* full;
+  uint64_t* empty;
+  int n_slots;
+  int slot_bytes;   // data + bias window
+  int slot;
+  uint32_t par;
+  __device__ __forceinline__ void advance() {
+    if (++slot == n_slots) { slot = 0; par ^= 1u; }
+  }
+};
+
+// What a CTA needs to know about one kind of phase; computed once per launch into shared memory.
+struct KindInfo {
+  int r0, r1;     // rows of the [N,K] matrix this CTA owns
+  int rps;        // rows per chunk (ring slot)
+  int K, N;
+  int pitch;      // bytes between rows in a slot: K * 2 + 16
+  int steps;      // K / 16
+  int pad;
+};
+
+__device__ __forceinline__ void rows_of(int cta, int G, int N, int& r0, int& r1) {
+  r0 = (int)(((unsigned)cta * (unsigned)N) / (unsigned)G);
+  r1 = (int)(((unsigned)(cta + 1) * (unsigned)N) / (unsigned)G);
+}
+
+struct Best {
+  float v;
+  int i;
+};
+__device__ __forceinline__ void best_merge(Best& a, float v, int i) {
+  if (v > a.v || (v == a.v && i < a.i)) { a.v = v; a.i = i; }
+}
+
+// everything a consumer thread carries through the phases
+template <bool TR> struct Ctx {
+  Ring rg;
+  uint8_t* xs_hi; uint8_t* xs_lo; int xrow;   // activation planes [BT][xrow bytes]; xs_lo == nullptr: rounding only
+  float *red, *lnred, *hloc, *h2loc;
+  int *s_ids, *s_pos, *s_slot;
+  volatile int* s_abort; const int* g_abort;
+  int B, H, V, n_pos, cta, c0;
+  float eps; float* logits_out;
+  long long* trace; int trace_cap; int n_stamp; bool tracing;
+  __device__ __forceinline__ void stamp(int tag) {
+    if constexpr (TR) {
+      if (tracing && threadIdx.x == 0 && n_stamp < trace_cap)
+        trace[n_stamp++] = (long long)(((u64)clock64() & 0x00FFFFFFFFFFFFFFull) | ((u64)tag << 56));
+    }
+  }
+  // called from inside spin loops: true once the host asked the kernel to stop waiting (watchdog); from then on
+  // every wait falls through and the launch runs to its end on whatever data is there (the host discards it)
+  __device__ __forceinline__ bool give_up(unsigned& spins) {
+    if (*s_abort) return true;
+    if ((++spins & kSpinCheck) == 0 && g_abort != nullptr) {
+      int a;
+      asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(a) : "l"(g_abort) : "memory");
+      if (a) { *s_abort = 1; return true; }
+    }
+    return false;
+  }
+};
+
+template <bool TR>
+__device__ __forceinline__ uint32_t wait_word_sys(Ctx<TR>& cx, const u64* p, uint32_t epoch) {
+  unsigned spins = 0;
+  u64 w = ll_load_sys(p);
+  while ((uint32_t)(w >> 32) != epoch) {
+    if (cx.give_up(spins)) break;
+    w = ll_load_sys(p);
+  }
+  return (uint32_t)w;
+}
+template <bool TR>
+__device__ __forceinline__ uint32_t wait_word(Ctx<TR>& cx, const u64* p, uint32_t epoch) {
+  unsigned spins = 0;
+  u64 w = ll_load(p);
+  while ((uint32_t)(w >> 32) != epoch) {
+    if (cx.give_up(spins)) break;
+    w = ll_load(p);
+  }
+  return (uint32_t)w;
+}
+
+// ---- producer: stream rows [r0,r1) of W[N,K] (+ their biases) through the ring, one bulk copy per row so that
+// rows sit `pitch` bytes apart in the slot.  All 32 lanes issue copies; lane 0 owns the barrier bookkeeping.
+__device__ __forceinline__ void produce_phase(Ring& rg, const void* W, const float* bias, const KindInfo& ki, int slot_data,
+                                              uint64_t policy, int lane) {
+  const int rowbytes = ki.K * 2;
+  const int rps = ki.rps, r1 = ki.r1, pitch = ki.pitch;
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(W);
+  for (int r = ki.r0; r < r1; r += rps) {
+    const int n = min(rps, r1 - r);
+    const int s = rg.slot;
+    uint8_t* slot = rg.slots + (size_t)s * rg.slot_bytes;
+    const int b0 = r & ~3, b1 = (r + n + 3) & ~3;
+    const uint32_t bias_bytes = bias ? (uint32_t)(b1 - b0) * 4u : 0u;
+    if (lane == 0) {
+      mbar_wait(&rg.empty[s], rg.par ^ 1u);
+      mbar_expect_tx(&rg.full[s], (uint32_t)(n * rowbytes) + bias_bytes);
+    }
+    __syncwarp();
+    for (int i = lane; i < n; i += 32)
+      bulk_g2s(slot + (size_t)i * pitch, base + (size_t)(r + i) * rowbytes, (uint32_t)rowbytes, &rg.full[s], policy);
+    if (bias && lane == 31) bulk_g2s(slot + slot_data, bias + b0, bias_bytes, &rg.full[s], policy);
+    rg.advance();
+  }
+}
+
+// barrier: the previous phase is fully done in this CTA (its shared-memory operands may be overwritten)
+template <bool TR>
+__device__ __forceinline__ void stage_enter(Ctx<TR>& cx, const u64* sentinel, uint32_t sentinel_epoch) {
+  consumer_sync();
+  if (sentinel != nullptr) {   // input from the previous pipeline stage: one thread watches one inbox word first
+    if (threadIdx.x == 0) wait_word_sys(cx, sentinel, sentinel_epoch);
+    consumer_sync();
+  }
+}
+
+struct PhaseIn {
+  int src_kind;
+  const u64* src_ll;        // SRC_LL / SRC_INBOX: [B][K] words
+  const float* src_plain;   // SRC_PLAIN: [B][K]
+  uint32_t src_epoch;
+  const u64* sentinel;
+  const bf16 *wte, *wpe;    // SRC_EMBED
+};
+
+// ---- staging, plain copy: x[B][K] (flag-in-data words) -> bf16 hi (+ lo) planes.  Thread t owns the element pairs
+// q = t + 480 i of every sequence; 8 sixteen-byte loads are in flight per round, words whose epoch is still old
+// are re-read as one batch.
+template <int BT, bool TR>
+__device__ __forceinline__ void stage_copy(Ctx<TR>& cx, const PhaseIn& in, int K, int tag) {
+  const int tid = threadIdx.x, B = cx.B;
+  const int halfK = K >> 1;
+  stage_enter(cx, nullptr, 0);
+  cx.stamp(tag + 0);
+  constexpr int PER_I = 8 / BT;   // 8 loads per batch
+  for (int i0 = 0; i0 * kConsumers < halfK; i0 += PER_I) {
+    u64 wa[8], wb[8];
+    unsigned pending = 0;
+#pragma unroll
+    for (int ii = 0; ii < PER_I; ++ii)
+#pragma unroll
+      for (int b = 0; b < BT; ++b) {
+        const int q = tid + (i0 + ii) * kConsumers;
+        if (q < halfK && b < B) pending |= 1u << (ii * BT + b);
+      }
+    unsigned spins = 0;
+    while (pending) {
+      const unsigned want = pending;
+#pragma unroll
+      for (int ii = 0; ii < PER_I; ++ii)
+#pragma unroll
+        for (int b = 0; b < BT; ++b) {
+          const int j = ii * BT + b;
+          const int q = tid + (i0 + ii) * kConsumers;
+          ll_load2_if(in.src_ll + (size_t)b * K + 2 * q, (want >> j) & 1u, false, wa[j], wb[j]);
+        }
+#pragma unroll
+      for (int ii = 0; ii < PER_I; ++ii)
+#pragma unroll
+        for (int b = 0; b < BT; ++b) {
+          const int j = ii * BT + b;
+          if (((want >> j) & 1u) && (uint32_t)(wa[j] >> 32) == in.src_epoch && (uint32_t)(wb[j] >> 32) == in.src_epoch) {
+            const int q = tid + (i0 + ii) * kConsumers;
+            uint32_t hi, lo;
+            split_hi_lo(__uint_as_float((uint32_t)wa[j]), __uint_as_float((uint32_t)wb[j]), hi, lo);
+            *reinterpret_cast<uint32_t*>(cx.xs_hi + (size_t)b * cx.xrow + 4 * q) = hi;
+            if (cx.xs_lo) *reinterpret_cast<uint32_t*>(cx.xs_lo + (size_t)b * cx.xrow + 4 * q) = lo;
+            pending &= ~(1u << j);
+          }
+        }
+      if (pending && cx.give_up(spins)) break;
+    }
+  }
+  cx.stamp(tag + 1);
+  consumer_sync();
+}
+
+// one element pair of the LayerNorm input
+template <bool TR>
+__device__ __forceinline__ bool fetch_pair(const Ctx<TR>& cx, const PhaseIn& in, int b, int q, int K, bool live, float& x0,
+                                           float& x1) {
+  if (in.src_kind == SRC_LL || in.src_kind == SRC_INBOX) {
+    u64 a, c;
+    ll_load2_if(in.src_ll + (size_t)b * K + 2 * q, live, in.src_kind == SRC_INBOX, a, c);
+    x0 = __uint_as_float((uint32_t)a);
+    x1 = __uint_as_float((uint32_t)c);
+    return (uint32_t)(a >> 32) == in.src_epoch && (uint32_t)(c >> 32) == in.src_epoch;
+  }
+  if (!live) { x0 = x1 = 0.f; return true; }
+  if (in.src_kind == SRC_PLAIN) {
+    const float2 v = __ldcg(reinterpret_cast<const float2*>(in.src_plain + (size_t)b * K + 2 * q));
+    x0 = v.x; x1 = v.y;
+    return true;
+  }
+  const uint32_t e = *reinterpret_cast<const uint32_t*>(in.wte + (size_t)cx.s_ids[b] * cx.H + 2 * q);
+  const uint32_t pz = *reinterpret_cast<const uint32_t*>(in.wpe + (size_t)min(cx.s_pos[b], cx.n_pos - 1) * cx.H + 2 * q);
+  x0 = bf16lo(e) + bf16lo(pz);
+  x1 = bf16hi(e) + bf16hi(pz);
+  return true;
+}
+
+// ---- staging with LayerNorm (K = H <= 1920): the row lives in registers; every warp reduces its part to
+// (count, mean, M2), the 15 partials are merged with Chan's formula after ONE block barrier
+// ([hf] modeling_gpt2.py:252,254,505: biased variance, eps inside the square root).
+template <int BT, bool TR>
+__device__ __forceinline__ void stage_ln(Ctx<TR>& cx, const PhaseIn& in, const float* ln_g, const float* ln_b, int K, int tag) {
+  const int tid = threadIdx.x, w = tid >> 5, l = tid & 31, B = cx.B;
+  const int halfK = K >> 1;
+  float v[BT][kLnPairs][2], gg[kLnPairs][2], bb[kLnPairs][2];
+#pragma unroll
+  for (int i = 0; i < kLnPairs; ++i) {
+    const int q = tid + i * kConsumers;
+    gg[i][0] = gg[i][1] = bb[i][0] = bb[i][1] = 0.f;
+    if (q < halfK) {
+      const float2 g2 = *reinterpret_cast<const float2*>(ln_g + 2 * q), b2 = *reinterpret_cast<const float2*>(ln_b + 2 * q);
+      gg[i][0] = g2.x; gg[i][1] = g2.y; bb[i][0] = b2.x; bb[i][1] = b2.y;
+    }
+  }
+  stage_enter(cx, in.sentinel, in.src_epoch);
+  cx.stamp(tag + 0);
+  unsigned pending = 0;
+#pragma unroll
+  for (int i = 0; i < kLnPairs; ++i)
+#pragma unroll
+    for (int b = 0; b < BT; ++b) {
+      const int q = tid + i * kConsumers;
+      const bool live = q < halfK && b < B;
+      v[b][i][0] = v[b][i][1] = 0.f;
+      if (i * kConsumers < halfK) {
+        const bool ok = fetch_pair(cx, in, min(b, B - 1), min(q, halfK - 1), K, live, v[b][i][0], v[b][i][1]);
+        if (live && !ok) pending |= 1u << (b * kLnPairs + i);
+        if (!live) v[b][i][0] = v[b][i][1] = 0.f;
+      }
+    }
+  unsigned spins = 0;
+  while (pending) {
+    const unsigned want = pending;
+    float t0[BT * kLnPairs], t1[BT * kLnPairs];
+    bool okk[BT * kLnPairs];
+#pragma unroll
+    for (int i = 0; i < kLnPairs; ++i)
+#pragma unroll
+      for (int b = 0; b < BT; ++b) {
+        const int j = b * kLnPairs + i;
+        okk[j] = false;
+        if (i * kConsumers < halfK)
+          okk[j] = fetch_pair(cx, in, min(b, B - 1), min(tid + i * kConsumers, halfK - 1), K, (want >> j) & 1u, t0[j], t1[j]);
+      }
+#pragma unroll
+    for (int i = 0; i < kLnPairs; ++i)
+#pragma unroll
+      for (int b = 0; b < BT; ++b) {
+        const int j = b * kLnPairs + i;
+        if (((want >> j) & 1u) && okk[j]) { v[b][i][0] = t0[j]; v[b][i][1] = t1[j]; pending &= ~(1u << j); }
+      }
+    if (pending && cx.give_up(spins)) break;
+  }
+  cx.stamp(tag + 1);
+  // elements this thread holds per row (the same for every row)
+  float cnt = 0.f;
+#pragma unroll
+  for (int i = 0; i < kLnPairs; ++i) cnt += (tid + i * kConsumers < halfK) ? 2.f : 0.f;
+  float s[BT];
+#pragma unroll
+  for (int b = 0; b < BT; ++b) {
+    s[b] = 0.f;
+#pragma unroll
+    for (int i = 0; i < kLnPairs; ++i) s[b] += v[b][i][0] + v[b][i][1];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(FULL_MASK, cnt, o);
+#pragma unroll
+    for (int b = 0; b < BT; ++b) s[b] += __shfl_xor_sync(FULL_MASK, s[b], o);
+  }
+  float mw[BT], m2[BT];
+  const float inv_cnt = cnt > 0.f ? 1.f / cnt : 0.f;
+#pragma unroll
+  for (int b = 0; b < BT; ++b) {
+    mw[b] = s[b] * inv_cnt;
+    float qd = 0.f;
+#pragma unroll
+    for (int i = 0; i < kLnPairs; ++i)
+      if (tid + i * kConsumers < halfK) {
+        const float d0 = v[b][i][0] - mw[b], d1 = v[b][i][1] - mw[b];
+        qd += d0 * d0 + d1 * d1;
+      }
+    m2[b] = qd;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int b = 0; b < BT; ++b) m2[b] += __shfl_xor_sync(FULL_MASK, m2[b], o);
+  float* lr = cx.lnred;   // [BT][kNW][2] (mean, M2) then [kNW] counts
+  if (l == 0) {
+#pragma unroll
+    for (int b = 0; b < BT; ++b) { lr[(b * kNW + w) * 2 + 0] = mw[b]; lr[(b * kNW + w) * 2 + 1] = m2[b]; }
+    lr[BT * kNW * 2 + w] = cnt;
+  }
+  consumer_sync();
+  const float invK = 1.f / (float)K;
+#pragma unroll
+  for (int b = 0; b < BT; ++b) {
+    float mean = 0.f;
+#pragma unroll
+    for (int i = 0; i < kNW; ++i) mean += lr[BT * kNW * 2 + i] * lr[(b * kNW + i) * 2 + 0];
+    mean *= invK;
+    float M2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < kNW; ++i) {
+      const float dm = lr[(b * kNW + i) * 2 + 0] - mean;
+      M2 += lr[(b * kNW + i) * 2 + 1] + lr[BT * kNW * 2 + i] * dm * dm;
+    }
+    const float rstd = rsqrtf(M2 * invK + cx.eps);
+#pragma unroll
+    for (int i = 0; i < kLnPairs; ++i) {
+      const int q = tid + i * kConsumers;
+      if (q < halfK && b < B) {
+        const float y0 = (v[b][i][0] - mean) * rstd * gg[i][0] + bb[i][0];
+        const float y1 = (v[b][i][1] - mean) * rstd * gg[i][1] + bb[i][1];
+        uint32_t hi, lo;
+        split_hi_lo(y0, y1, hi, lo);
+        *reinterpret_cast<uint32_t*>(cx.xs_hi + (size_t)b * cx.xrow + 4 * q) = hi;
+        if (cx.xs_lo) *reinterpret_cast<uint32_t*>(cx.xs_lo + (size_t)b * cx.xrow + 4 * q) = lo;
+      }
+    }
+  }
+  consumer_sync();
+}
+
+struct PhaseOut {
+  int kind;
+  int has_bias;
+  u64* dst_ll; float* dst_plain; uint32_t dst_epoch; int dst_sys;
+};
+
+// ---- rows: this CTA's rows of W[N,K] times the staged activations, chunk by chunk.
+// Chunk = n <= 24 rows = g_c groups of 8.  Warp w < g_c * nsl (nsl = 15 / g_c) owns group g = w % g_c and the k16
+// steps [sl S / nsl, (sl + 1) S / nsl) with sl = w / g_c.  mma: A = activations (row m: rounding of sequence m, row
+// m + 8: its residual), B = 8 weight rows.  Lane (gid = lane / 4, tig = lane % 4) ends up with sequence gid's
+// partial sums for rows 2 tig, 2 tig + 1 of the group; the partial tiles go to red[buf][w][64] and, after ONE block
+// barrier, thread t < 64 g_c sums the nsl partials of (group t / 64, sequence (t % 64) / 8, row t % 8) in a fixed
+// order and applies the epilogue.  `red` is double-buffered, so the next chunk's partials never meet a reader.
+template <int BT, bool TR>
+__device__ __forceinline__ void run_rows(Ctx<TR>& cx, const PhaseOut& po, const KindInfo& ki, int slot_data, Best& best) {
+  Ring& rg = cx.rg;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
+  const int B = cx.B, r1 = ki.r1, rps = ki.rps, pitch = ki.pitch, S = ki.steps;
+  const bool a_live = gid < B;
+  const uint8_t* a_hi = cx.xs_hi + (size_t)gid * cx.xrow + tig * 4;
+  const uint8_t* a_lo = cx.xs_lo ? cx.xs_lo + (size_t)gid * cx.xrow + tig * 4 : nullptr;
+  int buf = 0;
+  for (int r = ki.r0; r < r1; r += rps) {
+    const int n = min(rps, r1 - r);
+    const int s = rg.slot;
+    const uint8_t* slot = rg.slots + (size_t)s * rg.slot_bytes;
+    const int g_c = (n + 7) >> 3;
+    const int nsl = (g_c == 1) ? kNW : (g_c == 2 ? kNW / 2 : kNW / 3);
+    if (lane == 0) mbar_wait(&rg.full[s], rg.par);
+    __syncwarp();
+    if (r == ki.r0) cx.stamp(po.kind * 8 + 3);
+    float* redw = cx.red + (size_t)buf * kNW * 64 + warp * 64;
+    if (warp < g_c * nsl) {
+      const int sl = (g_c == 1) ? warp : (g_c == 2 ? warp >> 1 : warp / 3);
+      const int g = warp - sl * g_c;
+      const int s_begin = (sl * S) / nsl, s_end = ((sl + 1) * S) / nsl;
+      const uint8_t* wp = slot + (size_t)min(g * 8 + gid, n - 1) * pitch + tig * 4;
+      float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+      int st = s_begin;
+#pragma unroll 2
+      for (; st + 1 < s_end; st += 2) {
+        const uint32_t b00 = lds32(wp + st * 32), b01 = lds32(wp + st * 32 + 16);
+        const uint32_t b10 = lds32(wp + st * 32 + 32), b11 = lds32(wp + st * 32 + 48);
+        uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+        if (a_live) {
+          a0 = lds32(a_hi + st * 32); a2 = lds32(a_hi + st * 32 + 16);
+          c0 = lds32(a_hi + st * 32 + 32); c2 = lds32(a_hi + st * 32 + 48);
+          if (a_lo) {
+            a1 = lds32(a_lo + st * 32); a3 = lds32(a_lo + st * 32 + 16);
+            c1 = lds32(a_lo + st * 32 + 32); c3 = lds32(a_lo + st * 32 + 48);
+          }
+        }
+        mma16816(acc0, a0, a1, a2, a3, b00, b01);
+        mma16816(acc1, c0, c1, c2, c3, b10, b11);
+      }
+      if (st < s_end) {
+        const uint32_t b00 = lds32(wp + st * 32), b01 = lds32(wp + st * 32 + 16);
+        uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        if (a_live) {
+          a0 = lds32(a_hi + st * 32); a2 = lds32(a_hi + st * 32 + 16);
+          if (a_lo) { a1 = lds32(a_lo + st * 32); a3 = lds32(a_lo + st * 32 + 16); }
+        }
+        mma16816(acc0, a0, a1, a2, a3, b00, b01);
+      }
+      // rows 0..7 of D: x_hi . w, rows 8..15: x_lo . w
+      const float v0 = (acc0[0] + acc1[0]) + (acc0[2] + acc1[2]);
+      const float v1 = (acc0[1] + acc1[1]) + (acc0[3] + acc1[3]);
+      *reinterpret_cast<float2*>(redw + gid * 8 + tig * 2) = make_float2(v0, v1);
+    }
+    cx.stamp(po.kind * 8 + 5);
+    consumer_sync();
+    cx.stamp(po.kind * 8 + 6);
+    if (tid < g_c * 64) {
+      const int g = tid >> 6, idx = tid & 63, seq = idx >> 3, nn = idx & 7;
+      const int local = g * 8 + nn;
+      const float* rp = cx.red + (size_t)buf * kNW * 64 + g * 64 + idx;
+      float v = 0.f;
+      for (int sl = 0; sl < nsl; ++sl) v += rp[sl * g_c * 64];
+      if (seq < B && local < n) {
+        const int row = r + local;
+        if (po.kind == K_HEAD) {
+          best_merge(best, v, row);
+          if (cx.logits_out != nullptr) cx.logits_out[(size_t)seq * cx.V + row] = v;
+        } else {
+          if (po.has_bias) v += reinterpret_cast<const float*>(slot + slot_data)[(r & 3) + local];
+          const int own = seq * kOwnMax + (row - cx.c0);
+          if (po.kind == K_PROJ) { v += cx.hloc[own]; cx.h2loc[own] = v; }
+          else if (po.kind == K_FC) v = gelu_new(v);
+          else if (po.kind == K_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
+          if (po.dst_plain != nullptr) po.dst_plain[(size_t)seq * ki.N + row] = v;
+          else if (po.dst_sys) ll_store_sys(po.dst_ll + (size_t)seq * ki.N + row, __float_as_uint(v), po.dst_epoch);
+          else ll_store(po.dst_ll + (size_t)seq * ki.N + row, __float_as_uint(v), po.dst_epoch);
+        }
+      }
+    }
+    // the slot goes back to the producer only now: the epilogue above still read the chunk's bias window from it
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&rg.empty[s]);
+    rg.advance();
+    cx.stamp(po.kind * 8 + 7);
+    buf ^= 1;
+  }
+}
+
+struct AttnArgs {
+  bf16 *kc, *vc; const u64* qkv_ll; u64* attn_ll; uint32_t ep_qkv, ep_attn;
+  int nh, max_ctx; float *part, *pm, *pl, *qkv_s;
+};
+
+// ---- decode attention for one (sequence, head) task, "scores first".
+// Key j belongs to warp j % 15, lane (j / 15) % 32, round j / 480: a thread owns one key per round, a warp's valid
+// lanes are contiguous.  Cached rows do not depend on this step, so the thread's K row of round 0 (128 bytes) and
+// the first kVPre V values of the warp's keys are in registers before q is waited for.  Per warp: scores -> warp
+// max -> weights -> P.V over the warp's keys (weights broadcast by shuffle, V rows read coalesced, lane = output
+// dimensions 2 lane, 2 lane + 1), online across rounds; the 15 (max, sum, acc) partials merge through shared memory.
+template <bool TR>
+__device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, int b, int head, int slot) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int H = cx.H;
+  const size_t base = ((size_t)slot * a.nh + head) * (size_t)a.max_ctx * kD;
+  bf16* Kc = a.kc + base;
+  bf16* Vc = a.vc + base;
+  const int pos = cx.s_pos[b];                      // the new token's position = number of cached rows
+  const int j0 = lane * kNW + warp;                 // my key of round 0
+  uint4 kr[8];
+  if (j0 < pos) {
+    const uint4* src = reinterpret_cast<const uint4*>(Kc + (size_t)j0 * kD);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) kr[i] = src[i];
+  }
+  uint32_t vpre[kVPre];
+#pragma unroll
+  for (int i = 0; i < kVPre; ++i) {
+    const int j = i * kNW + warp;
+    vpre[i] = (j < pos) ? *reinterpret_cast<const uint32_t*>(Vc + (size_t)j * kD + 2 * lane) : 0u;
+  }
+  stage_enter(cx, nullptr, 0);
+  cx.stamp(K_ATTN * 8 + 0);
+  // q, k_new, v_new of this head: 192 words, one per thread
+  if (tid < 3 * kD) {
+    const int which = tid >> 6, i = tid & 63;
+    const float val = __uint_as_float(wait_word(cx, a.qkv_ll + (size_t)b * 3 * H + which * H + head * kD + i, a.ep_qkv));
+    if (which == 0) {
+      a.qkv_s[i] = val * 0.125f;                    // 64^-0.5
+    } else {
+      const bf16 r = __float2bfloat16_rn(val);      // the new row joins the cache storage-rounded like every row
+      if (pos < a.max_ctx) (which == 1 ? Kc : Vc)[(size_t)pos * kD + i] = r;
+      a.qkv_s[which * kD + i] = __bfloat162float(r);
+    }
+  }
+  consumer_sync();
+  cx.stamp(K_ATTN * 8 + 1);
+  float m_run = -INFINITY, l_run = 0.f, acc0 = 0.f, acc1 = 0.f;
+  for (int rnd = 0; rnd * kConsumers <= pos; ++rnd) {
+    const int j = rnd * kConsumers + j0;
+    float sc = -INFINITY;
+    if (j <= pos) {
+      float d = 0.f;
+      if (j == pos) {
+#pragma unroll
+        for (int i = 0; i < kD; i += 4) {
+          const float4 q4 = *reinterpret_cast<const float4*>(a.qkv_s + i);
+          const float4 k4 = *reinterpret_cast<const float4*>(a.qkv_s + kD + i);
+          d = fmaf(q4.x, k4.x, d); d = fmaf(q4.y, k4.y, d); d = fmaf(q4.z, k4.z, d); d = fmaf(q4.w, k4.w, d);
+        }
+      } else {
+        if (rnd > 0) {
+          const uint4* src = reinterpret_cast<const uint4*>(Kc + (size_t)j * kD);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) kr[i] = src[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 qa = *reinterpret_cast<const float4*>(a.qkv_s + i * 8);
+          const float4 qb = *reinterpret_cast<const float4*>(a.qkv_s + i * 8 + 4);
+          d = fmaf(qa.x, bf16lo(kr[i].x), d); d = fmaf(qa.y, bf16hi(kr[i].x), d);
+          d = fmaf(qa.z, bf16lo(kr[i].y), d); d = fmaf(qa.w, bf16hi(kr[i].y), d);
+          d = fmaf(qb.x, bf16lo(kr[i].z), d); d = fmaf(qb.y, bf16hi(kr[i].z), d);
+          d = fmaf(qb.z, bf16lo(kr[i].w), d); d = fmaf(qb.w, bf16hi(kr[i].w), d);
+        }
+      }
+      sc = d;
+    }
+    // keys of this warp in this round: lanes [0, nl)
+    const int first = rnd * kConsumers + warp;      // lane 0's key
+    const int nl = (first <= pos) ? min(32, (pos - first) / kNW + 1) : 0;
+    if (nl > 0) {
+      float mx = sc;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(FULL_MASK, mx, o));
+      const float m_new = fmaxf(m_run, mx);
+      const float scale = __expf(m_run - m_new);    // 0 on the first round (m_run = -inf)
+      const float pme = (j <= pos) ? __expf(sc - m_new) : 0.f;
+      l_run *= scale; acc0 *= scale; acc1 *= scale;
+      m_run = m_new;
+      // P.V over this warp's keys: weight of lane li's key by shuffle, its V row read coalesced
+      auto accum = [&](int li, uint32_t vbits) {
+        const float pl = __shfl_sync(FULL_MASK, pme, li);
+        const int jj = first + li * kNW;
+        float v0 = bf16lo(vbits), v1 = bf16hi(vbits);
+        if (jj == pos) { v0 = a.qkv_s[2 * kD + 2 * lane]; v1 = a.qkv_s[2 * kD + 2 * lane + 1]; }
+        acc0 = fmaf(pl, v0, acc0); acc1 = fmaf(pl, v1, acc1);
+        l_run += pl;
+      };
+      int li0 = 0;
+      if (rnd == 0) {
+#pragma unroll
+        for (int z = 0; z < kVPre; ++z)
+          if (z < nl) accum(z, vpre[z]);
+        li0 = kVPre;
+      }
+      for (int l0 = li0; l0 < nl; l0 += 4) {
+        uint32_t vv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int jj = first + (l0 + u) * kNW;
+          vv[u] = (l0 + u < nl && jj < pos) ? *reinterpret_cast<const uint32_t*>(Vc + (size_t)jj * kD + 2 * lane) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (l0 + u < nl) accum(l0 + u, vv[u]);
+      }
+    }
+  }
+  cx.stamp(K_ATTN * 8 + 2);
+  *reinterpret_cast<float2*>(a.part + warp * kD + 2 * lane) = make_float2(acc0, acc1);
+  if (lane == 0) { a.pm[warp] = m_run; a.pl[warp] = l_run; }
+  consumer_sync();
+  if (tid < kD) {
+    float M = a.pm[0];
+#pragma unroll
+    for (int ww = 1; ww < kNW; ++ww) M = fmaxf(M, a.pm[ww]);
+    float Lsum = 0.f, o = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < kNW; ++ww) {
+      const float c = (a.pm[ww] == -INFINITY) ? 0.f : __expf(a.pm[ww] - M);
+      Lsum = fmaf(a.pl[ww], c, Lsum);
+      o = fmaf(a.part[ww * kD + tid], c, o);
+    }
+    ll_store(a.attn_ll + (size_t)b * H + head * kD + tid, __float_as_uint(o / Lsum), a.ep_attn);
+  }
+}
+
+template <int BT, bool TR>
+__global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int G = gridDim.x, cta = blockIdx.x;
+  const int H = p.H, F = 4 * p.H, nh = p.nh, B = p.B, L = p.L;
+  const int slot_bytes = p.slot_data + kSlotBias;
+  // ---- shared memory carve-up (mirrored by fixed_smem2() on the host)
+  constexpr int NP = (BT <= 4) ? 2 : 1;
+  const int xrow = F * 2 + 16;                                                   // bytes per activation row
+  uint8_t* ring_base = smem;
+  uint8_t* xs = smem + (size_t)p.n_slots * slot_bytes;                          // [NP][BT][xrow]
+  float* red = reinterpret_cast<float*>(xs + (size_t)NP * BT * xrow);           // [2][kNW][64]; attention scratch aliases it
+  float* lnred = red + 2 * kNW * 64;                                            // [BT][kNW][2] + [kNW]
+  float* hloc = lnred + BT * kNW * 2 + 16;                                      // [BT][kOwnMax]
+  float* h2loc = hloc + BT * kOwnMax;                                           // [BT][kOwnMax]
+  float* sbv = h2loc + BT * kOwnMax;                                            // [192] head candidates
+  int* sbi = reinterpret_cast<int*>(sbv + 192);                                 // [192]
+  int* s_ids = sbi + 192;                                                       // [8]
+  int* s_pos = s_ids + 8;                                                       // [8]
+  int* s_pos0 = s_pos + 8;                                                      // [64] cache lengths at launch
+  int* s_slot = s_pos0 + 64;                                                    // [64] KV slot of every sequence
+  int* s_misc = s_slot + 64;                                                    // [8]: 0 abort flag, 1 argmax counter base
+  uint64_t* full = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(s_misc + 8) + 15) & ~(uintptr_t)15);
+  uint64_t* empty = full + kMaxSlots;
+  KindInfo* s_kind = reinterpret_cast<KindInfo*>(empty + kMaxSlots);            // [8] (6 used)
+  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_kind + 8);               // [L]
+  // attention scratch inside `red` (the two are never live together)
+  float* at_part = red;                 // [kNW][64]
+  float* at_pm = red + kNW * kD;        // [kNW]
+  float* at_pl = at_pm + 16;            // [kNW]
+  float* at_qkv = at_pl + 16;           // [3*64]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  uint32_t* const argmax_ctr = reinterpret_cast<uint32_t*>(p.part_ll + (size_t)16 * kFlagStride);   // the row after the 8 x 2 partial rows
+  if (tid == 0) {
+    s_misc[0] = 0;
+    s_misc[1] = (int)ld_relaxed_u32(argmax_ctr);   // its value when this launch starts: nobody bumps it before every CTA got here
+    for (int s = 0; s < p.n_slots; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kNW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (tid >= 32 && tid < 38) {
+    const int kind = tid - 32;
+    KindInfo ki;
+    ki.N = (kind == K_QKV) ? 3 * H : (kind == K_FC) ? F : (kind == K_HEAD) ? p.V : H;
+    ki.K = (kind == K_PROJ2) ? F : H;
+    rows_of(cta, G, ki.N, ki.r0, ki.r1);
+    ki.pitch = ki.K * 2 + 16;
+    int rps = p.slot_data / ki.pitch;
+    if (rps > kMaxRows) rps = kMaxRows;
+    if (rps > 8) rps &= ~7;                 // whole groups of 8 while more than one group fits
+    ki.rps = rps;
+    ki.steps = ki.K >> 4;
+    ki.pad = 0;
+    s_kind[kind] = ki;
+  }
+  {
+    const int n_words = L * (int)(sizeof(MegaLayer) / 8);
+    const u64* src = reinterpret_cast<const u64*>(p.layers);
+    u64* dst = reinterpret_cast<u64*>(s_layers);
+    for (int i = tid; i < n_words; i += kThreads) dst[i] = src[i];
+  }
+  __syncthreads();
+
+  const int n_items = p.n_steps * p.n_streams;
+  if (warp == kNW) {
+    // =============================== PRODUCER ===============================
+    Ring rg{ring_base, full, empty, p.n_slots, slot_bytes, 0, 0u};
+    const uint64_t policy = l2_stream_policy(p.l2_stream_hint != 0);
+    for (int item = 0; item < n_items; ++item) {
+      for (int li = 0; li < L; ++li) {
+        const void* const* wl = reinterpret_cast<const void* const*>(&s_layers[li]);
+#pragma unroll 1
+        for (int m = 0; m < 4; ++m) {
+          const int kind = (m == 0) ? K_QKV : m + 1;
+          produce_phase(rg, wl[m], reinterpret_cast<const float*>(wl[4 + m]), s_kind[kind], p.slot_data, policy, lane);
+        }
+      }
+      if (p.has_head) produce_phase(rg, p.wte, nullptr, s_kind[K_HEAD], p.slot_data, policy, lane);
+    }
+    return;
+  }
+
+  // ================================= CONSUMERS =================================
+  Ctx<TR> cx;
+  cx.trace = p.trace ? p.trace + (size_t)cta * p.trace_cap : nullptr; cx.trace_cap = p.trace_cap; cx.n_stamp = 0;
+  cx.tracing = false;
+  if (tid < 64) {
+    const int n_seq = p.n_streams * B;
+    const int sl = (tid < n_seq) ? (p.slot_map ? p.slot_map[tid] : p.slot0 + tid) : 0;
+    s_slot[tid] = sl;
+    s_pos0[tid] = (tid < n_seq) ? p.lens[sl] : 0;
+  }
+  if (tid < 8) { s_pos[tid] = 0; s_ids[tid] = 0; }
+  if (cta == 0 && tid == 0 && p.step_clock != nullptr) p.step_clock[n_items] = globaltimer();  // start stamp
+  consumer_sync();
+
+  cx.rg = Ring{ring_base, full, empty, p.n_slots, slot_bytes, 0, 0u};
+  cx.xs_hi = xs; cx.xs_lo = (NP == 2) ? xs + (size_t)BT * xrow : nullptr; cx.xrow = xrow;
+  cx.red = red; cx.lnred = lnred; cx.hloc = hloc; cx.h2loc = h2loc; cx.s_ids = s_ids; cx.s_pos = s_pos; cx.s_slot = s_slot;
+  cx.s_abort = s_misc; cx.g_abort = p.abort_flag;
+  cx.B = B; cx.H = H; cx.V = p.V; cx.n_pos = p.n_pos; cx.cta = cta; cx.eps = p.eps; cx.logits_out = p.logits_out;
+  int c0, c1;                                        // residual rows this CTA owns (same split as the N = H phases)
+  rows_of(cta, G, H, c0, c1);
+  cx.c0 = c0;
+  const int n_ph = 5 * L + (p.has_head ? 1 : 0);
+  const uint32_t ep_per_item = (uint32_t)(5 * L + 2);
+
+  for (int item = 0; item < n_items; ++item) {
+    const int round = item / p.n_streams, strm = item - round * p.n_streams;
+    const uint32_t cep = p.comm_epoch0 + (uint32_t)round;   // epoch of this item's words on the stage boundary
+    const uint32_t ep_item = p.epoch0 + (uint32_t)item * ep_per_item;
+    const u64* in_hid = p.inbox_hid ? p.inbox_hid + (size_t)strm * B * H : nullptr;
+    // ---- position and (stage 0) token of every sequence of this item
+    if (tid < B) {
+      s_pos[tid] = min(s_pos0[strm * B + tid] + round, p.max_ctx - 1);
+      if (p.has_embed) {
+        int id = s_ids[tid];   // single-stage loop: this CTA's own argmax of the previous step
+        if (p.inbox_ids != nullptr && round > 0) {
+          id = (int)wait_word_sys(cx, p.inbox_ids + strm * B + tid, cep - 1u);
+          if (cta == 0 && p.tok_out != nullptr) p.tok_out[(size_t)(strm * B + tid) * p.tok_stride + (round - 1)] = id;
+        } else if (round == 0) {
+          id = __ldcg(p.ids + strm * B + tid);
+        }
+        s_ids[tid] = min(max(id, 0), p.V - 1);
+      }
+    }
+    consumer_sync();
+    // ---- the residual slice this CTA owns: embedding rows (stage 0) or the incoming hidden state
+    for (int i = tid; i < B * (c1 - c0); i += kConsumers) {
+      const int b = i / (c1 - c0), col = c0 + i % (c1 - c0);
+      float hv;
+      if (p.has_embed) {
+        const bf16* wte = reinterpret_cast<const bf16*>(p.wte);
+        const bf16* wpe = reinterpret_cast<const bf16*>(p.wpe);
+        hv = to_f(wte[(size_t)s_ids[b] * H + col]) + to_f(wpe[(size_t)min(s_pos[b], p.n_pos - 1) * H + col]);
+      } else if (in_hid != nullptr) {
+        hv = __uint_as_float(wait_word_sys(cx, in_hid + (size_t)b * H + col, cep));
+      } else {
+        hv = __ldcg(p.hidden_in + (size_t)b * H + col);
+      }
+      hloc[b * kOwnMax + (col - c0)] = hv;
+    }
+    cx.tracing = (p.trace != nullptr && item == n_items - 1);
+    cx.stamp(7 * 8 + 0);
+    Best best{-INFINITY, 0x7fffffff};
+    int li = 0, kind = (L > 0) ? K_QKV : K_HEAD;
+    for (int ph = 0; ph < n_ph; ++ph) {
+      const uint32_t ep_dst = ep_item + (uint32_t)ph + 1u;     // data produced by phase ph; consumed by phase ph + 1
+      const MegaLayer& w = s_layers[li];
+      if (kind == K_ATTN) {
+        if (cta < B * nh) {
+          AttnArgs a;
+          a.kc = reinterpret_cast<bf16*>(w.kc); a.vc = reinterpret_cast<bf16*>(w.vc); a.qkv_ll = p.qkv_ll; a.attn_ll = p.attn_ll;
+          a.ep_qkv = ep_dst - 1u; a.ep_attn = ep_dst; a.nh = nh; a.max_ctx = p.max_ctx;
+          a.part = at_part; a.pm = at_pm; a.pl = at_pl; a.qkv_s = at_qkv;
+          for (int task = cta; task < B * nh; task += G) {
+            const int b = task / nh, head = task - b * nh;
+            attention_task(cx, a, b, head, s_slot[strm * B + b]);
+          }
+        }
+        cx.stamp(K_ATTN * 8 + 3);
+        kind = K_PROJ;
+        continue;
+      }
+      const KindInfo& ki = s_kind[kind];
+      PhaseIn in;
+      in.src_kind = SRC_LL; in.src_plain = nullptr; in.sentinel = nullptr; in.src_epoch = ep_dst - 1u;
+      in.wte = reinterpret_cast<const bf16*>(p.wte); in.wpe = reinterpret_cast<const bf16*>(p.wpe);
+      // source buffer: qkv <- h, proj <- attn, fc <- h2, proj2 <- act, head <- h
+      in.src_ll = (kind == K_PROJ) ? p.attn_ll : (kind == K_FC) ? p.h2_ll : (kind == K_PROJ2) ? p.act_ll : p.h_ll;
+      if (ph == 0) {   // first phase of the item: the stage's input
+        if (p.has_embed) in.src_kind = SRC_EMBED;
+        else if (in_hid != nullptr) { in.src_kind = SRC_INBOX; in.src_ll = in_hid; in.src_epoch = cep; in.sentinel = in_hid + (H - 1); }
+        else { in.src_kind = SRC_PLAIN; in.src_plain = p.hidden_in; }
+      }
+      PhaseOut po;
+      po.kind = kind; po.has_bias = (kind != K_HEAD); po.dst_plain = nullptr; po.dst_sys = 0; po.dst_epoch = ep_dst;
+      // destination: qkv -> qkv, proj -> h2, fc -> act, proj2 -> h
+      po.dst_ll = (kind == K_QKV) ? p.qkv_ll : (kind == K_PROJ) ? p.h2_ll : (kind == K_FC) ? p.act_ll : p.h_ll;
+      if (kind == K_PROJ2 && li == L - 1 && !p.has_head) {
+        if (p.peer_hid != nullptr) { po.dst_ll = p.peer_hid + (size_t)strm * B * H; po.dst_epoch = cep; po.dst_sys = 1; }
+        else po.dst_plain = p.hidden_out;
+      }
+      if (kind == K_QKV || kind == K_FC || kind == K_HEAD) {
+        const float* g = (kind == K_QKV) ? w.ln1_g : (kind == K_FC) ? w.ln2_g : p.lnf_g;
+        const float* bt = (kind == K_QKV) ? w.ln1_b : (kind == K_FC) ? w.ln2_b : p.lnf_b;
+        stage_ln<BT, TR>(cx, in, g, bt, ki.K, kind * 8);
+      } else {
+        stage_copy<BT, TR>(cx, in, ki.K, kind * 8);
+      }
+      cx.stamp(kind * 8 + 2);
+      run_rows<BT, TR>(cx, po, ki, p.slot_data, best);
+      cx.stamp(kind * 8 + 4);
+      // next phase
+      if (kind == K_PROJ2) { ++li; kind = (li < L) ? K_QKV : K_HEAD; }
+      else ++kind;
+    }
+    if (p.has_head) {
+      const uint32_t ep_arg = ep_item + (uint32_t)n_ph + 1u;
+      // ---- argmax: candidates of this CTA (thread t < 192 holds the best of sequence (t % 64) / 8 over its rows)
+      consumer_sync();
+      if (tid < 192) { sbv[tid] = best.v; sbi[tid] = best.i; }
+      consumer_sync();
+      if (tid < B) {
+        Best r{-INFINITY, 0x7fffffff};
+        for (int g = 0; g < 3; ++g)
+          for (int nn = 0; nn < 8; ++nn) best_merge(r, sbv[g * 64 + tid * 8 + nn], sbi[g * 64 + tid * 8 + nn]);
+        ll_store(p.part_ll + ((size_t)tid * 2 + 0) * kFlagStride + cta, __float_as_uint(r.v), ep_arg);
+        ll_store(p.part_ll + ((size_t)tid * 2 + 1) * kFlagStride + cta, (uint32_t)r.i, ep_arg);
+      }
+      cx.stamp(7 * 8 + 2);
+      // every CTA reduces all partials itself (index tie-break => deterministic).  One counter sits in front of the
+      // data: 148 warps polling the 19 lines that 148 producers are still writing delayed those writes.
+      if (warp == 0) {
+        __syncwarp();
+        if (lane == 0) red_add_u32(argmax_ctr, 1u);
+      }
+      for (int b = warp; b < B; b += kNW) {
+        if (lane == 0) {
+          const uint32_t target = (uint32_t)s_misc[1] + (uint32_t)(item + 1) * (uint32_t)G;
+          unsigned spins = 0;
+          while ((int32_t)(ld_relaxed_u32(argmax_ctr) - target) < 0) {
+            if (cx.give_up(spins)) break;
+          }
+        }
+        __syncwarp();
+        Best r{-INFINITY, 0x7fffffff};
+        const u64* pv = p.part_ll + ((size_t)b * 2 + 0) * kFlagStride;
+        const u64* pi = p.part_ll + ((size_t)b * 2 + 1) * kFlagStride;
+#pragma unroll 1
+        for (int j0 = 0; j0 < G; j0 += 128) {
+          u64 wv[4], wi[4];
+          unsigned pend = 0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            wv[j] = 0; wi[j] = 0;
+            if (j0 + j * 32 + lane < G) pend |= 3u << (2 * j);
+          }
+          unsigned spins = 0;
+          while (pend) {
+            const unsigned want = pend;
+            u64 nv[4], ni[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int g = j0 + j * 32 + lane;
+              nv[j] = ll_load_if(pv + g, (want >> (2 * j)) & 1u);
+              ni[j] = ll_load_if(pi + g, (want >> (2 * j + 1)) & 1u);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (((want >> (2 * j)) & 1u) && (uint32_t)(nv[j] >> 32) == ep_arg) { wv[j] = nv[j]; pend &= ~(1u << (2 * j)); }
+              if (((want >> (2 * j + 1)) & 1u) && (uint32_t)(ni[j] >> 32) == ep_arg) { wi[j] = ni[j]; pend &= ~(2u << (2 * j)); }
+            }
+            if (pend && cx.give_up(spins)) break;
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (j0 + j * 32 + lane < G) best_merge(r, __uint_as_float((uint32_t)wv[j]), (int)(uint32_t)wi[j]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const float ov = __shfl_xor_sync(FULL_MASK, r.v, o);
+          const int oi = __shfl_xor_sync(FULL_MASK, r.i, o);
+          best_merge(r, ov, oi);
+        }
+        if (lane == 0) {
+          const int tok = min(max(r.i, 0), p.V - 1);
+          if (cta == 0) {
+            p.ids_out[strm * B + b] = tok;
+            if (p.seq != nullptr) p.seq[(size_t)(strm * B + b) * p.seq_stride + s_pos[b] + 1] = tok;
+            if (p.peer_ids != nullptr) ll_store_sys(p.peer_ids + strm * B + b, (uint32_t)tok, cep);
+          }
+          s_ids[b] = tok;
+        }
+      }
+      cx.stamp(7 * 8 + 1);
+    }
+    // ---- bookkeeping: the cache grew by one position
+    if (cta == 0 && tid < B) p.lens[s_slot[strm * B + tid]] = s_pos[tid] + 1;
+    if (cta == 0 && tid == 0) {
+      if (p.step_clock != nullptr) p.step_clock[item] = globaltimer();
+      if (p.progress != nullptr) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p.progress), "r"((uint32_t)(item + 1)) : "memory");
+    }
+    consumer_sync();
+  }
+  // pipeline, stage 0: the tokens of the last round never come back as inputs; collect them here
+  if (p.has_embed && p.inbox_ids != nullptr && p.tok_out != nullptr && cta == 0 && tid < p.n_streams * B) {
+    const int id = (int)wait_word_sys(cx, p.inbox_ids + tid, p.comm_epoch0 + (uint32_t)p.n_steps - 1u);
+    p.tok_out[(size_t)tid * p.tok_stride + (p.n_steps - 1)] = id;
+  }
+}
+
+int padded2(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : (B <= 4 ? 4 : 8)); }
+
+size_t fixed_smem2(int BT, int H, int L) {
+  const int NP = BT <= 4 ? 2 : 1;
+  const size_t xrow = (size_t)4 * H * 2 + 16;
+  return (size_t)NP * BT * xrow + (size_t)2 * kNW * 64 * 4 /*red*/ + ((size_t)BT * kNW * 2 + 16) * 4 /*lnred*/ +
+         (size_t)2 * BT * kOwnMax * 4 /*hloc,h2loc*/ + 192 * 8 /*sbv,sbi*/ + (8 + 8 + 64 + 64 + 8) * 4 + 16 + 2 * kMaxSlots * 8 +
+         8 * sizeof(KindInfo) + (size_t)L * sizeof(MegaLayer) + 128;
+}
+
+// largest slot (multiple of 128 bytes, <= 40 KB) that leaves at least 3 slots; 0 if even 2 slots of two rows do not fit
+int pick_slot(int BT, int H, int L, int* n_slots) {
+  const size_t avail = (size_t)227 * 1024 - fixed_smem2(BT, H, L);
+  const int widest = 4 * H * 2 + 16;
+  for (int want = 5; want >= 2; --want) {
+    long data = (long)(avail / want) - kSlotBias;
+    data &= ~127L;
+    if (data > 40 * 1024) data = 40 * 1024;
+    if (want > 3 && data < 40 * 1024) continue;   // prefer full-size slots; go below 40 KB only to keep 3 (then 2)
+    if (data >= 2L * widest || (want == 2 && data >= widest)) {
+      int n = (int)(avail / (size_t)(data + kSlotBias));
+      if (n > kMaxSlots) n = kMaxSlots;
+      *n_slots = n;
+      return (int)data;
+    }
+  }
+  return 0;
+}
+
+template <int BT>
+cudaError_t launch2_t(const MegaParams& p, int grid, size_t smem, cudaStream_t s) {
+  void* args[] = {const_cast<MegaParams*>(&p)};
+  const void* fn = (p.trace != nullptr) ? (const void*)decode_mega2_kernel<BT, true> : (const void*)decode_mega2_kernel<BT, false>;
+  return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, smem, s);
+}
+template <int BT> cudaError_t set_attr2() {
+  cudaError_t e = cudaFuncSetAttribute(decode_mega2_kernel<BT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(decode_mega2_kernel<BT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  return e;
+}
+
+}  // namespace
+
+bool mega2_supported(int B, int H, int nh, int L, int dtype, int num_sms) {
+  if (dtype != GP_BF16 || B < 1 || B > 8 || H % 16 != 0 || nh <= 0 || H % nh != 0 || H / nh != kD || L < 0) return false;
+  if (H > 2 * kLnPairs * kConsumers) return false;
+  if (num_sms < 1 || num_sms > kFlagStride || B * nh > 64 * kFlagStride) return false;
+  if ((H + num_sms - 1) / num_sms + 1 > kOwnMax) return false;
+  if (fixed_smem2(padded2(B), H, L) + 2 * 1024 > (size_t)227 * 1024) return false;
+  int n_slots = 0;
+  return pick_slot(padded2(B), H, L, &n_slots) > 0 && n_slots >= 2;
+}
+
+uint32_t mega2_epochs_per_launch(int L, int n_items) { return (uint32_t)n_items * (uint32_t)(5 * L + 2) + 8u; }
+
+cudaError_t init_mega2_attrs() {
+  cudaError_t e;
+  if ((e = set_attr2<1>()) != cudaSuccess) return e;
+  if ((e = set_attr2<2>()) != cudaSuccess) return e;
+  if ((e = set_attr2<4>()) != cudaSuccess) return e;
+  return set_attr2<8>();
+}
+
+int mega2_max_coresident(int B, int H, int L) {
+  const int BT = padded2(B);
+  int n_slots = 0;
+  const int data = pick_slot(BT, H, L, &n_slots);
+  if (data <= 0) return 0;
+  const size_t smem = fixed_smem2(BT, H, L) + (size_t)n_slots * (data + kSlotBias);
+  int per_sm = 0;
+  const void* fn = BT == 1 ? (const void*)decode_mega2_kernel<1, false> : BT == 2 ? (const void*)decode_mega2_kernel<2, false>
+                 : BT == 4 ? (const void*)decode_mega2_kernel<4, false> : (const void*)decode_mega2_kernel<8, false>;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kThreads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return per_sm;
+}
+
+cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s) {
+  if (!mega2_supported(p.B, p.H, p.nh, p.L, GP_BF16, num_sms) || p.n_steps < 1 || p.epoch0 == 0 || p.n_streams < 1 ||
+      p.n_streams * p.B > 64)
+    return cudaErrorInvalidValue;
+  const int BT = padded2(p.B);
+  int n_slots = 0;
+  int data = pick_slot(BT, p.H, p.L, &n_slots);
+  if (const char* env = getenv("GP_MEGA_SLOTS")) { int v = atoi(env); if (v >= 2 && v < n_slots) n_slots = v; }
+  p.n_slots = n_slots;
+  p.slot_data = data;
+  const size_t smem = fixed_smem2(BT, p.H, p.L) + (size_t)n_slots * (data + kSlotBias);
+  if (BT == 1) return launch2_t<1>(p, num_sms, smem, s);
+  if (BT == 2) return launch2_t<2>(p, num_sms, smem, s);
+  if (BT == 4) return launch2_t<4>(p, num_sms, smem, s);
+  return launch2_t<8>(p, num_sms, smem, s);
+}
+
+}  // namespace gp

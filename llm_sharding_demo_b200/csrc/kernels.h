@@ -109,12 +109,23 @@ struct MegaParams {
   int n_slots = 0;                                           // filled by the launcher
   int l2_stream_hint = 1;                                    // weight copies carry an L2 evict-first policy
   long long* trace = nullptr; int trace_cap = 0;             // debug: clock64 of CTA 0 per phase boundary
+  // second-generation kernel (k_mega2.cu) only:
+  int slot_data = 0;                                         // bytes of weight rows per ring slot (filled by the launcher)
+  const int32_t* slot_map = nullptr;                         // [n_streams*B] KV slot of every sequence (NULL: slot0 + index)
+  const int* abort_flag = nullptr;                           // device word the host sets to make every wait fall through
+  unsigned int* progress = nullptr;                          // device word: items finished by this launch
 };
 bool mega_supported(int B, int H, int nh, int L, int dtype, int num_sms);
 uint32_t mega_epochs_per_launch(int L, int n_steps);
 size_t mega_part_words();
 cudaError_t init_mega_attrs();
 cudaError_t launch_decode_mega(MegaParams p, int dtype, int num_sms, cudaStream_t s);
+// k_mega2.cu: bf16 storage, B <= 8, tensor-core rows
+bool mega2_supported(int B, int H, int nh, int L, int dtype, int num_sms);
+uint32_t mega2_epochs_per_launch(int L, int n_items);
+cudaError_t init_mega2_attrs();
+int mega2_max_coresident(int B, int H, int L);   // CTAs per SM the runtime would co-schedule (0: launch impossible)
+cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s);
 
 // stores `msg` as this thread's last error (what gp_last_error(NULL) returns); engine.cu
 void record_error(const char* msg);

@@ -153,6 +153,32 @@ class StageEngine:
             out["next_ids"] = next_ids
         return out
 
+    def decode_slots(self, x: torch.Tensor, slots, want_logits: bool = False):
+        """One cached step for the sequences living in KV slots `slots` (any distinct slot numbers; continuous
+        batching).  x: int32 ids [B] on stage 0, else fp32 hidden [B,H]; row b belongs to slots[b]."""
+        H, V = self.dims.n_embd, self.dims.vocab_size
+        B = x.shape[0]
+        assert len(slots) == B
+        ids, hid = (x, None) if self.has_embed else (None, x)
+        hidden_out = logits = next_ids = None
+        if not self.has_head:
+            hidden_out = torch.empty((B, H), dtype=torch.float32, device=self.device)
+        else:
+            if want_logits:
+                logits = torch.empty((B, V), dtype=torch.float32, device=self.device)
+            next_ids = torch.empty((B,), dtype=torch.int32, device=self.device)
+        sl = (C.c_int32 * B)(*[int(v) for v in slots])
+        check(self.lib.gp_stage_decode_slots(self._h, _ptr(ids), _ptr(hid), B, sl, _ptr(hidden_out), _ptr(logits),
+                                             _ptr(next_ids), _stream_ptr(self.device)), self._h)
+        out = {}
+        if hidden_out is not None:
+            out["hidden"] = hidden_out
+        if logits is not None:
+            out["logits"] = logits
+        if next_ids is not None:
+            out["next_ids"] = next_ids
+        return out
+
     def generate(self, prompt_ids: torch.Tensor, n_new: int, timings: bool = False):
         """Decode on a single-stage engine (greedy unless set_sampler switched it). prompt_ids: CPU int32 [B,P] (pinned memory
         avoids a staging copy).  Returns CPU int32 [B,P+n_new] (+ timings dict)."""
@@ -176,6 +202,11 @@ class StageEngine:
     def comm_connect(self, peer_handle: bytes):
         buf = (C.c_ubyte * 64).from_buffer_copy(peer_handle)
         check(self.lib.gp_comm_connect(self._h, buf), self._h)
+
+    def comm_connect_local(self, peer: "StageEngine"):
+        """Same-process variant of comm_connect: `peer` is the engine this stage feeds."""
+        check(self.lib.gp_comm_connect_local(self._h, peer._h), self._h)
+        self._peer_keepalive = peer
 
     def pipeline_decode(self, first_ids, n_rounds: int, n_streams: int, B: int, comm_epoch0: int,
                         timeout_ms: int = 20000):

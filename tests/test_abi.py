@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_version_and_error_channel():
     lib = L.load_library()
-    assert lib.gp_version() == 100
+    assert lib.gp_version() == 200
     cfg = _lib.GPConfig(n_layer=0)
     h = ctypes.c_void_p()
     rc = lib.gp_engine_create(ctypes.byref(cfg), ctypes.byref(h))
