@@ -26,6 +26,8 @@ struct LayerW {
   float *ln2_g = nullptr, *ln2_b = nullptr, *fc_b = nullptr, *mproj_b = nullptr;
   void *attn_w = nullptr, *proj_w = nullptr, *fc_w = nullptr, *mproj_w = nullptr;  // [N,K] in cfg.dtype
   void *kc = nullptr, *vc = nullptr;  // [max_batch, nh, max_ctx, d]
+  // LayerNorm folded into the following matrix for the bf16 persistent kernel: u = W.gamma, c = W.beta + bias
+  float *attn_u = nullptr, *attn_c = nullptr, *fc_u = nullptr, *fc_c = nullptr;
 };
 }  // namespace
 
@@ -36,6 +38,7 @@ struct gp_engine {
   std::vector<LayerW> layers;
   void *wte = nullptr, *wpe = nullptr;
   float *lnf_g = nullptr, *lnf_b = nullptr;
+  float *lnf_u = nullptr, *lnf_c = nullptr;   // ln_f folded into the tied lm_head (bf16 persistent kernel)
   std::set<std::string> required, loaded;
   std::vector<void*> allocs;
   int32_t* lens = nullptr;
@@ -78,6 +81,7 @@ struct gp_engine {
   MegaLayer* mega_layers = nullptr;
   unsigned long long *qkv_ll = nullptr, *attn_ll = nullptr, *h2_ll = nullptr, *act_ll = nullptr, *h_ll = nullptr;
   unsigned long long* part_ll = nullptr;
+  size_t ll_bytes[5] = {0, 0, 0, 0, 0};
   // pipeline stage boundary: this stage's inbox (peers write into it) and the mapped inbox of the peer it feeds
   unsigned char* inbox = nullptr;       // [1024 B ids words][64*H hidden words]
   unsigned char* peer_inbox = nullptr;  // next stage's inbox (stage 0's for the last stage), cudaIpcOpenMemHandle
@@ -223,13 +227,23 @@ bool use_mega(const gp_engine* e, int B) {
 
 int upload_mega_layers(gp_engine* e) {
   if (e->mega_uploaded) return GP_OK;
+  if (e->cfg.dtype == GP_BF16) {
+    // per-row constants of the folded LayerNorms (k_mega2.cu, stage_ln): recomputed whenever a weight was (re)loaded
+    const int H = e->H;
+    for (int i = 0; i < e->L; ++i) {
+      const LayerW& w = e->layers[i];
+      CK(e, launch_ln_fold(w.attn_w, w.ln1_g, w.ln1_b, w.attn_b, w.attn_u, w.attn_c, 3 * H, H, e->stream));
+      CK(e, launch_ln_fold(w.fc_w, w.ln2_g, w.ln2_b, w.fc_b, w.fc_u, w.fc_c, e->F, H, e->stream));
+    }
+    if (e->cfg.has_head) CK(e, launch_ln_fold(e->wte, e->lnf_g, e->lnf_b, nullptr, e->lnf_u, e->lnf_c, e->V, H, e->stream));
+  }
   std::vector<MegaLayer> h(e->L);
   for (int i = 0; i < e->L; ++i) {
     const LayerW& w = e->layers[i];
     h[i] = MegaLayer{w.attn_w, w.proj_w, w.fc_w, w.mproj_w, w.attn_b, w.proj_b, w.fc_b, w.mproj_b,
-                     w.ln1_g,  w.ln1_b,  w.ln2_g, w.ln2_b,  w.kc,     w.vc};
+                     w.ln1_g,  w.ln1_b,  w.ln2_g, w.ln2_b,  w.kc,     w.vc,      w.attn_u, w.attn_c, w.fc_u, w.fc_c};
   }
-  CK(e, cudaMemcpyAsync(e->mega_layers, h.data(), sizeof(MegaLayer) * e->L, cudaMemcpyHostToDevice, e->stream));
+  if (e->L > 0) CK(e, cudaMemcpyAsync(e->mega_layers, h.data(), sizeof(MegaLayer) * e->L, cudaMemcpyHostToDevice, e->stream));
   CK(e, cudaStreamSynchronize(e->stream));
   e->mega_uploaded = true;
   return GP_OK;
@@ -251,7 +265,8 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   MegaParams p;
   p.layers = e->mega_layers; p.L = e->L; p.H = e->H; p.nh = e->nh; p.V = e->V; p.n_pos = c.n_positions;
   p.max_ctx = c.max_ctx; p.eps = c.ln_eps; p.B = B; p.slot0 = slot0; p.has_embed = c.has_embed; p.has_head = c.has_head;
-  p.wte = e->wte; p.wpe = e->wpe; p.lnf_g = e->lnf_g; p.lnf_b = e->lnf_b; p.ids = ids; p.hidden_in = hidden_in;
+  p.wte = e->wte; p.wpe = e->wpe; p.lnf_g = e->lnf_g; p.lnf_b = e->lnf_b; p.lnf_u = e->lnf_u; p.lnf_c = e->lnf_c;
+  p.ids = ids; p.hidden_in = hidden_in;
   p.hidden_out = hidden_out; p.lens = e->lens; p.qkv_ll = e->qkv_ll; p.attn_ll = e->attn_ll; p.h2_ll = e->h2_ll;
   p.act_ll = e->act_ll; p.h_ll = e->h_ll; p.part_ll = e->part_ll; p.ids_out = next_ids ? next_ids : e->mailbox;
   p.seq = seq; p.seq_stride = e->seq_stride; p.logits_out = logits; p.n_steps = n_steps;
@@ -268,10 +283,9 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   const uint32_t span = v2 ? mega2_epochs_per_launch(e->L, n_steps * pipe.n_streams) : mega_epochs_per_launch(e->L, n_steps * pipe.n_streams);
   if (e->mega_epoch > 0xFFFFFFFFu - span - 8u) {
     // epoch counter about to wrap: start over on zeroed exchange buffers
-    const size_t MBx = c.max_batch;
-    CK(e, cudaMemsetAsync(e->qkv_ll, 0, MBx * 3 * e->H * 8, s)); CK(e, cudaMemsetAsync(e->attn_ll, 0, MBx * e->H * 8, s));
-    CK(e, cudaMemsetAsync(e->h2_ll, 0, MBx * e->H * 8, s)); CK(e, cudaMemsetAsync(e->act_ll, 0, MBx * e->F * 8, s));
-    CK(e, cudaMemsetAsync(e->h_ll, 0, MBx * e->H * 8, s)); CK(e, cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, s));
+    CK(e, cudaMemsetAsync(e->qkv_ll, 0, e->ll_bytes[0], s)); CK(e, cudaMemsetAsync(e->attn_ll, 0, e->ll_bytes[1], s));
+    CK(e, cudaMemsetAsync(e->h2_ll, 0, e->ll_bytes[2], s)); CK(e, cudaMemsetAsync(e->act_ll, 0, e->ll_bytes[3], s));
+    CK(e, cudaMemsetAsync(e->h_ll, 0, e->ll_bytes[4], s)); CK(e, cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, s));
     e->mega_epoch = 8;
   }
   p.epoch0 = e->mega_epoch;
@@ -289,7 +303,7 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   p.step_clock = clock ? e->step_clock : nullptr;
   const char* trace_path = getenv("GP_MEGA_TRACE");
   const bool trace = trace_path != nullptr && n_steps > 1;
-  const int kTraceCap = 512;
+  const int kTraceCap = use_mega2(e, B) ? 1024 : 512;   // the second-generation kernel stamps more events per phase
   if (trace) {  // debug aid: per-CTA %globaltimer at every phase boundary of the last step -> raw int64 file
     if (!e->trace) CK(e, cudaMalloc((void**)&e->trace, (size_t)e->num_sms * kTraceCap * sizeof(long long)));
     CK(e, cudaMemsetAsync(e->trace, 0, (size_t)e->num_sms * kTraceCap * sizeof(long long), s));
@@ -298,6 +312,8 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   if (v2) {
     p.slot_map = pipe.slot_indexed ? e->slot_map : nullptr;
     p.abort_flag = e->ctrl; p.progress = reinterpret_cast<unsigned int*>(e->ctrl + 1);
+    p.ll_shift = kLLShiftMax;
+    if (const char* env = getenv("GP_MEGA_LLSHIFT")) { int v = atoi(env); if (v >= 2 && v <= kLLShiftMax) p.ll_shift = v; }
     CK(e, cudaMemsetAsync(e->ctrl, 0, 2 * sizeof(int), s));
     cudaError_t le = launch_decode_mega2(p, e->num_sms, s);
     if (le == cudaErrorCooperativeLaunchTooLarge || le == cudaErrorLaunchOutOfResources) {
@@ -563,6 +579,10 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
     TRY(alloc(&w.attn_w, 3 * H * H * esz)); TRY(alloc(&w.proj_w, H * H * esz));
     TRY(alloc(&w.fc_w, F * H * esz)); TRY(alloc(&w.mproj_w, H * F * esz));
     TRY(alloc(&w.kc, kv_elems * esz)); TRY(alloc(&w.vc, kv_elems * esz));
+    if (cfg->dtype == GP_BF16) {
+      TRY(alloc((void**)&w.attn_u, 3 * H * 4)); TRY(alloc((void**)&w.attn_c, 3 * H * 4));
+      TRY(alloc((void**)&w.fc_u, F * 4)); TRY(alloc((void**)&w.fc_c, F * 4));
+    }
     for (const char* n : {"ln_1.weight", "ln_1.bias", "attn.c_attn.weight", "attn.c_attn.bias", "attn.c_proj.weight",
                           "attn.c_proj.bias", "ln_2.weight", "ln_2.bias", "mlp.c_fc.weight", "mlp.c_fc.bias",
                           "mlp.c_proj.weight", "mlp.c_proj.bias"})
@@ -578,6 +598,7 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   }
   if (cfg->has_head) {
     TRY(alloc((void**)&e->lnf_g, H * 4)); TRY(alloc((void**)&e->lnf_b, H * 4));
+    if (cfg->dtype == GP_BF16) { TRY(alloc((void**)&e->lnf_u, V * 4)); TRY(alloc((void**)&e->lnf_c, V * 4)); }
     e->required.insert("ln_f.weight"); e->required.insert("ln_f.bias");
     TRY(alloc(&e->lm_scratch, (size_t)gp_lmhead_scratch_bytes(kGemvMaxBatch, e->V)));
     TRYCK(cudaMemsetAsync(e->lm_scratch, 0, kLmheadScratchHeader, e->stream));
@@ -602,12 +623,24 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   TRY(alloc((void**)&e->seq, MB * (size_t)e->seq_stride * sizeof(int32_t)));
   TRY(alloc((void**)&e->prompt, MB * (size_t)cfg->n_positions * sizeof(int32_t)));
   TRY(alloc((void**)&e->mailbox, MB * sizeof(int32_t)));
-  TRY(alloc((void**)&e->mega_layers, sizeof(MegaLayer) * e->L));
-  TRY(alloc((void**)&e->qkv_ll, MB * 3 * H * 8)); TRYCK(cudaMemsetAsync(e->qkv_ll, 0, MB * 3 * H * 8, e->stream));
-  TRY(alloc((void**)&e->attn_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->attn_ll, 0, MB * H * 8, e->stream));
-  TRY(alloc((void**)&e->h2_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->h2_ll, 0, MB * H * 8, e->stream));
-  TRY(alloc((void**)&e->act_ll, MB * F * 8)); TRYCK(cudaMemsetAsync(e->act_ll, 0, MB * F * 8, e->stream));
-  TRY(alloc((void**)&e->h_ll, MB * H * 8)); TRYCK(cudaMemsetAsync(e->h_ll, 0, MB * H * 8, e->stream));
+  TRY(alloc((void**)&e->mega_layers, sizeof(MegaLayer) * (e->L > 0 ? e->L : 1)));
+  {
+    // exchange buffers: dense [max_batch][width] words for the fp32 kernel; the bf16 kernel spreads the words of at
+    // most 8 sequences over L2 slices (one 32-byte sector per (4 << (shift - 2)) words, k_mega2.cu ll_off)
+    auto ll_bytes = [&](size_t width) {
+      const size_t dense = MB * width * 8;
+      const size_t rows = MB < 8 ? MB : 8;
+      const size_t spread = cfg->dtype == GP_BF16 ? ((rows * width + 3) / 4 << kLLShiftMax) * 8 + 64 : 0;
+      return dense > spread ? dense : spread;
+    };
+    e->ll_bytes[0] = ll_bytes(3 * H); e->ll_bytes[1] = ll_bytes(H); e->ll_bytes[2] = ll_bytes(H); e->ll_bytes[3] = ll_bytes(F);
+    e->ll_bytes[4] = ll_bytes(H);
+    TRY(alloc((void**)&e->qkv_ll, e->ll_bytes[0])); TRYCK(cudaMemsetAsync(e->qkv_ll, 0, e->ll_bytes[0], e->stream));
+    TRY(alloc((void**)&e->attn_ll, e->ll_bytes[1])); TRYCK(cudaMemsetAsync(e->attn_ll, 0, e->ll_bytes[1], e->stream));
+    TRY(alloc((void**)&e->h2_ll, e->ll_bytes[2])); TRYCK(cudaMemsetAsync(e->h2_ll, 0, e->ll_bytes[2], e->stream));
+    TRY(alloc((void**)&e->act_ll, e->ll_bytes[3])); TRYCK(cudaMemsetAsync(e->act_ll, 0, e->ll_bytes[3], e->stream));
+    TRY(alloc((void**)&e->h_ll, e->ll_bytes[4])); TRYCK(cudaMemsetAsync(e->h_ll, 0, e->ll_bytes[4], e->stream));
+  }
   TRY(alloc((void**)&e->part_ll, mega_part_words() * 8)); TRYCK(cudaMemsetAsync(e->part_ll, 0, mega_part_words() * 8, e->stream));
   TRY(alloc((void**)&e->step_clock, (size_t)(cfg->n_positions + 2) * 64 * sizeof(unsigned long long)));
   TRYCK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
@@ -705,6 +738,7 @@ int gp_load_weight(gp_engine* e, const char* name, const float* data_host, const
     CK(e, cudaStreamSynchronize(e->stream));
   }
   e->loaded.insert(nm);
+  e->mega_uploaded = false;   // derived constants (folded LayerNorms) follow the weights
   return GP_OK;
 }
 

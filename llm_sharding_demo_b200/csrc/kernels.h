@@ -12,6 +12,7 @@ constexpr int kMaxTopK = 64;            // candidates the sampling kernel can ho
 constexpr int kGemvMaxSmem = 200 * 1024;  // bytes of x staged in shared memory
 constexpr int kLmheadMaxGrid = 1184;    // 148 SMs x 8 CTAs
 constexpr int kLmheadScratchHeader = 256;
+constexpr int kLLShiftMax = 7;          // exchange buffers of the bf16 persistent kernel: one 32-byte sector per 1 KB at most
 
 // out[b,n] = epi(sum_k LN?(x)[b,k] Wt[n,k] + bias[n]) (+ residual[b,n]), or the c_attn
 // variant (mode 1) whose epilogue scatters q to `q_out` and k/v into the KV cache.
@@ -82,6 +83,8 @@ struct MegaLayer {
   const void *attn_w, *proj_w, *fc_w, *mproj_w;              // [N,K] storage dtype
   const float *attn_b, *proj_b, *fc_b, *mproj_b, *ln1_g, *ln1_b, *ln2_g, *ln2_b;
   void *kc, *vc;                                             // [slots, nh, max_ctx, 64]
+  // k_mega2.cu: per-row constants of the LayerNorm folded into c_attn / c_fc: u = W.gamma, c = W.beta + bias
+  const float *attn_u, *attn_c, *fc_u, *fc_c;
 };
 struct MegaParams {
   const MegaLayer* layers = nullptr; int L = 0;              // device array of this stage's layers
@@ -114,6 +117,9 @@ struct MegaParams {
   const int32_t* slot_map = nullptr;                         // [n_streams*B] KV slot of every sequence (NULL: slot0 + index)
   const int* abort_flag = nullptr;                           // device word the host sets to make every wait fall through
   unsigned int* progress = nullptr;                          // device word: items finished by this launch
+  const float *lnf_u = nullptr, *lnf_c = nullptr;            // ln_f folded into the tied lm_head: [V] each
+  int ll_shift = 2;                                          // spread of the exchange buffers: sector s at word s << ll_shift (2 = dense)
+  int poll_ns = 0;                                           // back-off between polls of the exchange words (0: spin)
 };
 bool mega_supported(int B, int H, int nh, int L, int dtype, int num_sms);
 uint32_t mega_epochs_per_launch(int L, int n_steps);
@@ -126,6 +132,9 @@ uint32_t mega2_epochs_per_launch(int L, int n_items);
 cudaError_t init_mega2_attrs();
 int mega2_max_coresident(int B, int H, int L);   // CTAs per SM the runtime would co-schedule (0: launch impossible)
 cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s);
+// u[n] = W[n,:].gamma, c[n] = W[n,:].beta (+ bias[n]) for a bf16 matrix W[N,K]
+cudaError_t launch_ln_fold(const void* W, const float* g, const float* b, const float* bias, float* u, float* c, int N, int K,
+                           cudaStream_t s);
 
 // stores `msg` as this thread's last error (what gp_last_error(NULL) returns); engine.cu
 void record_error(const char* msg);
