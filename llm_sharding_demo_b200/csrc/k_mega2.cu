@@ -43,6 +43,7 @@ constexpr int kMaxSlots = 6;
 constexpr int kSlotWin = 128;              // one fp32 side window of a chunk (<= 24 rows + alignment slack); a slot has two
 constexpr int kMaxRows = 24;               // rows per chunk = 3 groups of 8
 constexpr int kOwnMax = 16;                // residual rows one CTA owns
+constexpr int kPad = 16;                   // bytes between the end of a row and the next one in shared memory (see run_rows)
 constexpr int kLnPairs = 2;                // LayerNorm: element pairs per thread and sequence (H <= 1920)
 constexpr int kFlagStride = 256;
 constexpr int kD = 64;                     // head dimension
@@ -180,8 +181,13 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
   return v;
 }
-__device__ __forceinline__ void ldsm4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+__device__ __forceinline__ void lds64(uint32_t addr, uint32_t& r0, uint32_t& r1) {
+  asm volatile("ld.shared.v2.b32 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(addr));
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
 }
 
 // D(16x8, fp32) += A(16x16, bf16, row) * B(16x8, bf16, col)
@@ -218,15 +224,16 @@ struct KindInfo {
   int r0, r1;     // rows of the [N,K] matrix this CTA owns
   int rps;        // rows per chunk (ring slot)
   int K, N;
-  int pitch;      // bytes between rows in a slot: K * 2 + 16
-  int steps;      // K / 16
+  int pitch;      // bytes between rows in a slot: K * 2 + kPad
   int ln;         // 1: LayerNorm is folded into this phase (side windows hold u, c), 0: plain bias
+  int copy_items; // stage_copy: ceil(K / 2 / 480)
 };
-// a warp's share of a chunk: group of 8 rows `g`, k16 steps [s_begin, s_end).  Entry 15 of a row of the table holds
-// (groups in the chunk, K slices) instead.
-struct WarpCfg {
-  short s_begin, s_end, g, on;
-};
+__device__ __forceinline__ KindInfo load_kind(uint32_t addr) {   // 32 bytes of shared memory -> registers
+  const uint4 a = lds128(addr), b = lds128(addr + 16);
+  KindInfo k;
+  k.r0 = (int)a.x; k.r1 = (int)a.y; k.rps = (int)a.z; k.K = (int)a.w; k.N = (int)b.x; k.pitch = (int)b.y; k.ln = (int)b.z; k.copy_items = (int)b.w;
+  return k;
+}
 
 __device__ __forceinline__ void rows_of(int cta, int G, int N, int& r0, int& r1) {
   r0 = (int)(((unsigned)cta * (unsigned)N) / (unsigned)G);
@@ -249,7 +256,7 @@ template <bool TR> struct Ctx {
   int *s_ids, *s_pos, *s_slot;
   volatile int* s_abort; const int* g_abort;
   int B, H, V, c0;
-  float eps; float* logits_out; int poll_ns; int dbg_layer; int ll_shift;
+  float eps; float* logits_out; int poll_ns; int dbg_layer; int ll_shift; int ablate;
   long long* trace; int trace_cap; int n_stamp; bool tracing;
   // trace (GP_MEGA_TRACE): %globaltimer (ns, one clock for the whole GPU) | tag << 56, tag = kind * 16 + event;
   // `dep` makes the read wait for a value (e.g. something loaded after a barrier: BAR.SYNC does not block at issue)
@@ -338,11 +345,11 @@ __device__ __forceinline__ void produce_phase(Ring& rg, const void* W, const flo
 // block i = j / BT, sequence b = j % BT); thread t takes the element pair q = t + 480 i.  Four 16-byte loads are in
 // flight per round; a round is simply repeated until all four carry the expected epoch.
 template <int BT, bool TR>
-__device__ __forceinline__ void stage_copy(Ctx<TR>& cx, const u64* src, uint32_t epoch, int K, int tag) {
+__device__ __forceinline__ void stage_copy(Ctx<TR>& cx, const u64* src, uint32_t epoch, int K, int copy_items, int tag) {
   constexpr int LOG = (BT == 1) ? 0 : (BT == 2) ? 1 : (BT == 4) ? 2 : 3;
   const int tid = threadIdx.x, B = cx.B;
   const int halfK = K >> 1;
-  const int n_items = ((halfK + kConsumers - 1) / kConsumers) << LOG;
+  const int n_items = copy_items << LOG;
   cx.stamp(tag + 0);
   for (int j0 = 0; j0 < n_items; j0 += 4) {
     u64 wa[4], wb[4];
@@ -448,73 +455,89 @@ struct PhaseOut {
   u64* dst_ll; float* dst_plain; uint32_t dst_epoch; int dst_sys;
 };
 
+// 64-element k blocks [q_begin, q_end) of G row groups.  Inside a block lane tig owns the 16 CONSECUTIVE elements
+// [16 tig, 16 tig + 16) of its row: two 16-byte shared loads per operand bring the fragments of four mma steps
+// (step s of the block multiplies elements [16 tig + 4 s, + 4) of A and B - the order of the 16 k-elements of a step
+// is free as long as A and B agree).  Shared memory moves 128 bytes per clock for all 15 warps together and is what
+// bounds this loop, so fewer, wider loads matter: 12 wavefronts per block and group instead of 24.
+template <int G, bool LO>
+__device__ __forceinline__ void mma_blocks(float (&acc)[3][4], const uint32_t (&wrow)[3], uint32_t a_hi, uint32_t a_lo, uint32_t a_step,
+                                           int q_begin, int q_end) {
+#pragma unroll 1
+  for (int q = q_begin; q < q_end; ++q) {
+    const uint4 h0 = lds128(a_hi + q * a_step), h1 = lds128(a_hi + q * a_step + (a_step >> 3));
+    uint4 l0 = make_uint4(0, 0, 0, 0), l1 = l0;
+    if (LO) { l0 = lds128(a_lo + q * a_step); l1 = lds128(a_lo + q * a_step + (a_step >> 3)); }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const uint4 w0 = lds128(wrow[g] + q * 128), w1 = lds128(wrow[g] + q * 128 + 16);
+      mma16816(acc[g], h0.x, l0.x, h0.y, l0.y, w0.x, w0.y);
+      mma16816(acc[g], h0.z, l0.z, h0.w, l0.w, w0.z, w0.w);
+      mma16816(acc[g], h1.x, l1.x, h1.y, l1.y, w1.x, w1.y);
+      mma16816(acc[g], h1.z, l1.z, h1.w, l1.w, w1.z, w1.w);
+    }
+  }
+}
+
 // ---- rows: this CTA's rows of W[N,K] times the staged activations, chunk by chunk.
-// Chunk = n <= 24 rows = g_c groups of 8.  Warp w < g_c * nsl (nsl = 15 / g_c) owns group g = w % g_c and the k16
-// steps [sl S / nsl, (sl + 1) S / nsl) with sl = w / g_c (table in shared memory).  mma: A = activations (row m:
-// rounding of sequence m, row m + 8: its residual; rows of absent sequences read a 16-byte block of zeros),
-// B = 8 weight rows; both fragments come from ldmatrix.x4.  Lane (gid = lane / 4, tig = lane % 4) ends up with
-// sequence gid's partial sums for rows 2 tig, 2 tig + 1 of the group; the partial tiles go to red[buf][w][64] and,
-// after ONE block barrier, thread t < 64 g_c sums the nsl partials of (group t / 64, sequence (t % 64) / 8, row t % 8)
-// in a fixed order and applies the epilogue.  `red` is double-buffered, so the next chunk's partials never meet a
-// reader.  The slot returns to the producer after the epilogue (it still reads the side windows).
+// Chunk = n <= 24 rows = g_c groups of 8.  Warp w owns the 64-element k blocks [w Q / 15, (w + 1) Q / 15) of EVERY
+// group (Q = K / 64), so an activation fragment is read from shared memory once and the chunk's weights exactly once.
+// mma m16n8k16: A = activations (row m: bf16 rounding of sequence m, row m + 8: its bf16 residual), B = 8 weight rows
+// (see mma_blocks for the element order; loads are conflict-free because rows sit K * 2 + 16 bytes apart).
+// Lane (gid = lane / 4, tig = lane % 4) ends up with sequence gid's partial sums for rows 2 tig, 2 tig + 1 of each group; partial
+// tiles go to red[buf][w][g][seq][8] and, after ONE block barrier, thread t < 8 BT g_c sums the 15 partials of
+// (group, sequence, row) in a fixed order and applies the epilogue.  `red` is double-buffered, so the next chunk's
+// partials never meet a reader.  The slot returns to the producer after the epilogue (it reads the side windows).
 template <int BT, bool TR>
-__device__ __forceinline__ void run_rows(Ctx<TR>& cx, const PhaseOut& po, const KindInfo& ki, const WarpCfg* wtab, int slot_data,
+__device__ __forceinline__ void run_rows(Ctx<TR>& cx, const PhaseOut& po, const KindInfo& ki, int s_begin, int s_end, int slot_data,
                                          Best& best) {
   Ring& rg = cx.rg;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
   const int B = cx.B, r1 = ki.r1, rps = ki.rps;
-  // ldmatrix row addresses.  A: matrix mid = lane / 8 -> (plane = mid & 1, k half = mid / 2), row = sequence lane % 8
-  const int mid = lane >> 3, rr = lane & 7;
-  const bool a_on = rr < B && (BT <= 4 || (mid & 1) == 0);
-  const uint32_t a_base = a_on ? (((mid & 1) ? cx.xs_lo : cx.xs_hi) + rr * cx.xrow + (mid >> 1) * 16) : cx.zero16;
-  const uint32_t a_step = a_on ? 32u : 0u;
-  // B: matrix mid -> (k half = mid & 1, step = mid / 2), row = weight row lane % 8 of the group
-  const uint32_t b_off = (mid & 1) * 16 + (mid >> 1) * 32;
+  const bool a_on = gid < B;
+  const uint32_t a_hi = a_on ? cx.xs_hi + gid * cx.xrow + tig * 32 : cx.zero16;
+  const uint32_t a_lo = a_on ? cx.xs_lo + gid * cx.xrow + tig * 32 : cx.zero16;
+  const uint32_t a_step = a_on ? 128u : 0u;   // bytes per 64-element block; lanes of absent sequences keep reading the zero block
   float mean = 0.f, rstd = 1.f;
   int buf = 0;
   for (int r = ki.r0; r < r1; r += rps) {
     const int n = min(rps, r1 - r);
     const int s = rg.slot;
     const uint32_t slot = smem_u32(rg.slots + (size_t)s * rg.slot_bytes);
-    const WarpCfg* wrow = wtab + ((n == rps) ? 0 : 16);
-    const WarpCfg wc = wrow[warp];
-    const int g_c = wrow[15].s_begin, nsl = wrow[15].s_end;
+    const int g_c = (n + 7) >> 3;
     if (r != ki.r0) {   // the first chunk's wait was done before the staging barrier (by the caller)
       if (lane == 0) mbar_wait(&rg.full[s], rg.par);
       __syncwarp();
     }
-    if (r == ki.r0) cx.stamp(po.kind * 16 + 8, (uint32_t)wc.on);
-    if (wc.on) {
-      const uint32_t wp = slot + min(wc.g * 8 + rr, n - 1) * ki.pitch + b_off;
-      float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
-      int st = wc.s_begin;
-      const int s_end = wc.s_end;
-#pragma unroll 2
-      for (; st + 1 < s_end; st += 2) {
-        uint32_t b0, b1, b2, b3, a0, a1, a2, a3, c0, c1, c2, c3;
-        ldsm4(wp + st * 32, b0, b1, b2, b3);
-        ldsm4(a_base + st * a_step, a0, a1, a2, a3);
-        ldsm4(a_base + (st + 1) * a_step, c0, c1, c2, c3);
-        mma16816(acc0, a0, a1, a2, a3, b0, b1);
-        mma16816(acc1, c0, c1, c2, c3, b2, b3);
-      }
-      if (st < s_end) {
-        uint32_t b0, b1, b2, b3, a0, a1, a2, a3;
-        ldsm4(wp + st * 32, b0, b1, b2, b3);       // the second half reads 32 bytes further: inside the row's pad at worst
-        ldsm4(a_base + st * a_step, a0, a1, a2, a3);
-        mma16816(acc0, a0, a1, a2, a3, b0, b1);
-      }
-      // rows 0..7 of D: x_hi . w, rows 8..15: x_lo . w
-      const float v0 = (acc0[0] + acc1[0]) + (acc0[2] + acc1[2]);
-      const float v1 = (acc0[1] + acc1[1]) + (acc0[3] + acc1[3]);
-      *reinterpret_cast<float2*>(cx.red + (size_t)buf * kNW * 64 + warp * 64 + (lane >> 2) * 8 + (lane & 3) * 2) = make_float2(v0, v1);
+    if (TR && r == ki.r0) cx.stamp(po.kind * 16 + 8, __float_as_uint(lds_f32(cx.zero16)));   // a shared load: issues once the barrier has released
+    float acc[3][4];
+#pragma unroll
+    for (int g = 0; g < 3; ++g) acc[g][0] = acc[g][1] = acc[g][2] = acc[g][3] = 0.f;
+    {
+      uint32_t wrow[3];
+#pragma unroll
+      for (int g = 0; g < 3; ++g) wrow[g] = slot + min(g * 8 + gid, n - 1) * ki.pitch + tig * 32;
+      // branch-free body: lanes of absent sequences read the zero block (stride 0), the group count picks one of
+      // three straight-line loops
+      if (cx.ablate & 1) {}   // timing experiment: no mma
+      else if (g_c == 1) mma_blocks<1, (BT <= 4)>(acc, wrow, a_hi, a_lo, a_step, s_begin, s_end);
+      else if (g_c == 2) mma_blocks<2, (BT <= 4)>(acc, wrow, a_hi, a_lo, a_step, s_begin, s_end);
+      else mma_blocks<3, (BT <= 4)>(acc, wrow, a_hi, a_lo, a_step, s_begin, s_end);
     }
-    if (ki.ln && r == ki.r0 && tid < 192) {
-      // LayerNorm statistics of this thread's sequence: the 8 threads of a sequence (t % 8) fold the 15 per-warp
+    // rows 0..7 of D: x_hi . w, rows 8..15: x_lo . w
+    float* redw = cx.red + ((size_t)(buf * kNW + warp) * 3) * (BT * 8);
+    if (gid < BT) {
+#pragma unroll
+      for (int g = 0; g < 3; ++g)
+        if (g < g_c)
+          *reinterpret_cast<float2*>(redw + g * (BT * 8) + gid * 8 + tig * 2) = make_float2(acc[g][0] + acc[g][2], acc[g][1] + acc[g][3]);
+    }
+    if (ki.ln && r == ki.r0 && warp < (3 * BT * 8 + 31) / 32) {
+      // LayerNorm statistics of this thread's sequence: the 8 threads of a (group, sequence) fold the 15 per-warp
       // (sum, sum of squares) pairs - two each, then a 3-level butterfly
-      const int seq = (tid & 63) >> 3, nn = tid & 7;
-      float2 p0 = cx.lnred[nn * BT + min(seq, BT - 1)];
-      const float2 p1 = (nn + 8 < kNW) ? cx.lnred[(nn + 8) * BT + min(seq, BT - 1)] : make_float2(0.f, 0.f);
+      const int seq = min((tid % (BT * 8)) >> 3, BT - 1), nn = tid & 7;
+      float2 p0 = cx.lnred[nn * BT + seq];
+      const float2 p1 = (nn + 8 < kNW) ? cx.lnred[(nn + 8) * BT + seq] : make_float2(0.f, 0.f);
       p0.x += p1.x; p0.y += p1.y;
 #pragma unroll
       for (int o = 1; o < 8; o <<= 1) {
@@ -525,15 +548,16 @@ __device__ __forceinline__ void run_rows(Ctx<TR>& cx, const PhaseOut& po, const 
       mean = p0.x * invK;
       rstd = rsqrtf(fmaxf(p0.y * invK - mean * mean, 0.f) + cx.eps);
     }
-    cx.stamp(po.kind * 16 + 5);
+    cx.stamp(po.kind * 16 + 5, __float_as_uint(acc[0][0]));
     consumer_sync();
     cx.stamp(po.kind * 16 + 6);
-    if (tid < g_c * 64) {
-      const int g = tid >> 6, idx = tid & 63, seq = idx >> 3, nn = idx & 7;
+    if (tid < g_c * (BT * 8)) {
+      const int g = tid / (BT * 8), rem = tid - g * (BT * 8), seq = rem >> 3, nn = rem & 7;
       const int local = g * 8 + nn;
-      const float* rp = cx.red + (size_t)buf * kNW * 64 + g * 64 + idx;
+      const float* rp = cx.red + ((size_t)buf * kNW * 3 + g) * (BT * 8) + rem;
       float v = 0.f;
-      for (int sl = 0; sl < nsl; ++sl) v += rp[sl * g_c * 64];
+#pragma unroll
+      for (int w = 0; w < kNW; ++w) v += rp[w * 3 * (BT * 8)];
       cx.stamp(po.kind * 16 + 9, __float_as_uint(v));
       if (seq < B && local < n) {
         const int row = r + local;
@@ -546,11 +570,12 @@ __device__ __forceinline__ void run_rows(Ctx<TR>& cx, const PhaseOut& po, const 
         } else {
           const int own = seq * kOwnMax + (row - cx.c0);
           if (po.kind == K_PROJ) { v += cx.hloc[own]; cx.h2loc[own] = v; }
-          else if (po.kind == K_FC) v = gelu_new(v);
+          else if (po.kind == K_FC && !(cx.ablate & 2)) v = gelu_new(v);
           else if (po.kind == K_PROJ2) { v += cx.h2loc[own]; cx.hloc[own] = v; }
-          if (po.dst_plain != nullptr) po.dst_plain[(size_t)seq * ki.N + row] = v;
-          else if (po.dst_sys) ll_store_sys(po.dst_ll + (size_t)seq * ki.N + row, __float_as_uint(v), po.dst_epoch);
-          else ll_store(po.dst_ll + ll_off((size_t)seq * ki.N + row, cx.ll_shift), __float_as_uint(v), po.dst_epoch);
+          const size_t idx = (size_t)(seq * ki.N + row);
+          if (po.dst_plain != nullptr) po.dst_plain[idx] = v;
+          else if (po.dst_sys) ll_store_sys(po.dst_ll + idx, __float_as_uint(v), po.dst_epoch);
+          else ll_store(po.dst_ll + ll_off(idx, cx.ll_shift), __float_as_uint(v), po.dst_epoch);
         }
       }
     }
@@ -612,7 +637,7 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
   cx.stamp(K_ATTN * 16 + 1);
   float m_run = -INFINITY, l_run = 0.f, acc0 = 0.f, acc1 = 0.f;
   const uint32_t vnew = a.kv_s[32 + lane];          // dimensions 2 lane, 2 lane + 1 of the new V row
-  for (int rnd = 0; rnd * kConsumers <= pos; ++rnd) {
+  for (int rnd = 0; rnd * kConsumers <= ((cx.ablate & 4) ? -1 : pos); ++rnd) {
     const int j = rnd * kConsumers + j0;
     if (j == pos) {
 #pragma unroll
@@ -648,10 +673,11 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
       const float pme = (j <= pos) ? __expf(sc - m_new) : 0.f;
       l_run *= scale; acc0 *= scale; acc1 *= scale;
       m_run = m_new;
-      // P.V over this warp's keys: weight of lane li's key by shuffle, its V row read coalesced
+      // P.V over this warp's keys: weight of lane li's key by shuffle, its V row read coalesced.  The new token's V
+      // row is not in the cache copy the prefetch saw: patch it in once instead of testing every key.
+      const int li_new = (pos >= first && (pos - first) % kNW == 0) ? (pos - first) / kNW : -1;   // lane slot of key `pos`
       auto accum = [&](int li, uint32_t vbits) {
         const float pl = __shfl_sync(FULL_MASK, pme, li);
-        if (first + li * kNW == pos) vbits = vnew;
         acc0 = fmaf(pl, bf16lo(vbits), acc0); acc1 = fmaf(pl, bf16hi(vbits), acc1);
         l_run += pl;
       };
@@ -659,7 +685,7 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
       if (rnd == 0) {
 #pragma unroll
         for (int z = 0; z < kVPre; ++z)
-          if (z < nl) accum(z, vpre[z]);
+          if (z < nl) accum(z, (z == li_new) ? vnew : vpre[z]);
         li0 = kVPre;
       }
       for (int l0 = li0; l0 < nl; l0 += 4) {
@@ -671,7 +697,7 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          if (l0 + u < nl) accum(l0 + u, vv[u]);
+          if (l0 + u < nl) accum(l0 + u, (l0 + u == li_new) ? vnew : vv[u]);
       }
     }
   }
@@ -706,14 +732,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
   const int slot_bytes = p.slot_data + 2 * kSlotWin;
   // ---- shared memory carve-up (mirrored by fixed_smem2() on the host)
   constexpr int NP = (BT <= 4) ? 2 : 1;
-  const int xrow = F * 2 + 16;                                                   // bytes per activation row
+  const int xrow = F * 2 + kPad;                                                 // bytes per activation row
   uint8_t* ring_base = smem;
   uint8_t* xs = smem + (size_t)p.n_slots * slot_bytes;                          // [NP][BT][xrow]
-  float* red = reinterpret_cast<float*>(xs + (size_t)NP * BT * xrow);           // [2][kNW][64]; attention scratch aliases it
-  float2* lnred = reinterpret_cast<float2*>(red + 2 * kNW * 64);                // [16][BT] (sum, sum of squares) per warp
+  float* red = reinterpret_cast<float*>(xs + (size_t)NP * BT * xrow);           // [2][kNW][3][BT][8] partial tiles, >= 1280 floats; attention scratch aliases it
+  constexpr int kRedFloats = (2 * kNW * 3 * BT * 8 > 1280) ? 2 * kNW * 3 * BT * 8 : 1280;
+  float2* lnred = reinterpret_cast<float2*>(red + kRedFloats);                // [16][BT] (sum, sum of squares) per warp
   float* hloc = reinterpret_cast<float*>(lnred + 16 * BT);                     // [BT][kOwnMax]
   float* h2loc = hloc + BT * kOwnMax;                                           // [BT][kOwnMax]
-  float* sbv = h2loc + BT * kOwnMax;                                            // [192] head candidates
+  float* sbv = h2loc + BT * kOwnMax;                                            // [192] head candidates (3 BT 8 used)
   int* sbi = reinterpret_cast<int*>(sbv + 192);                                 // [192]
   int* s_ids = sbi + 192;                                                       // [8]
   int* s_pos = s_ids + 8;                                                       // [8]
@@ -723,8 +750,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
   uint64_t* full = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(s_misc + 8) + 15) & ~(uintptr_t)15);
   uint64_t* empty = full + kMaxSlots;
   KindInfo* s_kind = reinterpret_cast<KindInfo*>(empty + kMaxSlots);            // [8] (6 used)
-  WarpCfg* s_wcfg = reinterpret_cast<WarpCfg*>(s_kind + 8);                     // [6][2][16]
-  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_wcfg + 6 * 32);          // [L]
+  int* s_slice = reinterpret_cast<int*>(s_kind + 8);                            // [6][16] 64-element k blocks of each warp: begin | end << 16
+  MegaLayer* s_layers = reinterpret_cast<MegaLayer*>(s_slice + 6 * 16);         // [L]
   // attention scratch inside `red` (the two are never live together)
   float* at_part = red;                                   // [kNW][64]
   float* at_pm = red + kNW * kD;                          // [16]
@@ -750,13 +777,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
     ki.N = (kind == K_QKV) ? 3 * H : (kind == K_FC) ? F : (kind == K_HEAD) ? p.V : H;
     ki.K = (kind == K_PROJ2) ? F : H;
     rows_of(cta, G, ki.N, ki.r0, ki.r1);
-    ki.pitch = ki.K * 2 + 16;
+    ki.pitch = ki.K * 2 + kPad;
     int rps = p.slot_data / ki.pitch;
     if (rps > kMaxRows) rps = kMaxRows;
     if (rps > 8) rps &= ~7;                 // whole groups of 8 while more than one group fits
     ki.rps = rps;
-    ki.steps = ki.K >> 4;
     ki.ln = (kind == K_QKV || kind == K_FC || kind == K_HEAD) ? 1 : 0;
+    ki.copy_items = ((ki.K >> 1) + kConsumers - 1) / kConsumers;
     s_kind[kind] = ki;
   }
   {
@@ -766,25 +793,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
     for (int i = tid; i < n_words; i += kThreads) dst[i] = src[i];
   }
   __syncthreads();
-  if (tid < 6 * 32) {
-    // who does what in a chunk of n rows: table[kind][full chunk | tail chunk][warp]
-    const int kind = tid >> 5, cfgi = (tid >> 4) & 1, w = tid & 15;
-    const KindInfo ki = s_kind[kind];
-    const int rows = ki.r1 - ki.r0;
-    const int n = (kind == K_ATTN) ? 0 : (cfgi == 0 ? min(ki.rps, rows) : rows % max(ki.rps, 1));
-    const int g_c = (n + 7) >> 3;
-    const int nsl = g_c > 0 ? kNW / g_c : 0;
-    WarpCfg wc;
-    if (w == 15) {
-      wc.s_begin = (short)g_c; wc.s_end = (short)nsl; wc.g = 0; wc.on = 0;
-    } else {
-      const int sl = g_c > 0 ? w / g_c : 0;
-      wc.g = (short)(g_c > 0 ? w - sl * g_c : 0);
-      wc.on = (short)((g_c > 0 && w < g_c * nsl) ? 1 : 0);
-      wc.s_begin = (short)(wc.on ? (sl * ki.steps) / nsl : 0);
-      wc.s_end = (short)(wc.on ? ((sl + 1) * ki.steps) / nsl : 0);
-    }
-    s_wcfg[kind * 32 + cfgi * 16 + w] = wc;
+  if (tid < 6 * 16) {
+    const int kind = tid >> 4, w = tid & 15;
+    const int S = s_kind[kind].K >> 6;   // 64-element blocks
+    s_slice[tid] = (w < kNW) ? ((w * S) / kNW) | ((((w + 1) * S) / kNW) << 16) : 0;
   }
   __syncthreads();
 
@@ -824,7 +836,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
   cx.xs_hi = smem_u32(xs); cx.xs_lo = smem_u32(xs + (size_t)BT * xrow); cx.xrow = (uint32_t)xrow; cx.zero16 = smem_u32(s_misc + 4);
   cx.red = red; cx.lnred = lnred; cx.hloc = hloc; cx.h2loc = h2loc; cx.s_ids = s_ids; cx.s_pos = s_pos; cx.s_slot = s_slot;
   cx.s_abort = s_misc; cx.g_abort = p.abort_flag;
-  cx.B = B; cx.H = H; cx.V = p.V; cx.eps = p.eps; cx.logits_out = p.logits_out; cx.poll_ns = p.poll_ns; cx.dbg_layer = 0; cx.ll_shift = p.ll_shift;
+  cx.B = B; cx.H = H; cx.V = p.V; cx.eps = p.eps; cx.logits_out = p.logits_out; cx.poll_ns = p.poll_ns; cx.dbg_layer = 0; cx.ll_shift = p.ll_shift; cx.ablate = p.ablate;
   int c0, c1;                                        // residual rows this CTA owns (same split as the N = H phases)
   rows_of(cta, G, H, c0, c1);
   cx.c0 = c0;
@@ -892,7 +904,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
         continue;
       }
       cx.dbg_layer = (li == L / 2);
-      const KindInfo& ki = s_kind[kind];
+      const KindInfo ki = load_kind(smem_u32(s_kind + kind));
+      const int slice = s_slice[kind * 16 + warp];
       const u64* src = (kind == K_PROJ) ? p.attn_ll : (kind == K_FC) ? p.h2_ll : (kind == K_PROJ2) ? p.act_ll : p.h_ll;
       PhaseOut po;
       po.kind = kind; po.dst_plain = nullptr; po.dst_sys = 0; po.dst_epoch = ep_dst;
@@ -905,14 +918,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
         const float* g = (kind == K_QKV) ? w.ln1_g : (kind == K_FC) ? w.ln2_g : p.lnf_g;
         stage_ln<BT, TR>(cx, src, ep_dst - 1u, g, ki.K, kind * 16);
       } else {
-        stage_copy<BT, TR>(cx, src, ep_dst - 1u, ki.K, kind * 16);
+        stage_copy<BT, TR>(cx, src, ep_dst - 1u, ki.K, ki.copy_items, kind * 16);
       }
       // the weights of the first chunk have been in shared memory for a while: take the wait before the barrier
       if (ki.r0 < ki.r1 && lane == 0) mbar_wait(&cx.rg.full[cx.rg.slot], cx.rg.par);
       cx.stamp(kind * 16 + 2);
       consumer_sync();
       cx.stamp(kind * 16 + 3);
-      run_rows<BT, TR>(cx, po, ki, s_wcfg + kind * 32, p.slot_data, best);
+      run_rows<BT, TR>(cx, po, ki, slice & 0xffff, slice >> 16, p.slot_data, best);
       cx.stamp(kind * 16 + 4);
       // next phase
       if (kind == K_PROJ2) { ++li; kind = (li < L) ? K_QKV : K_HEAD; }
@@ -920,13 +933,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
     }
     if (p.has_head) {
       const uint32_t ep_arg = ep_item + (uint32_t)n_ph + 1u;
-      // ---- argmax: candidates of this CTA (thread t < 192 holds the best of sequence (t % 64) / 8 over its rows)
-      if (tid < 192) { sbv[tid] = best.v; sbi[tid] = best.i; }
+      // ---- argmax: candidates of this CTA (thread t < 24 BT holds the best of one (group, sequence, row % 8) over its rows)
+      if (tid < 3 * BT * 8) { sbv[tid] = best.v; sbi[tid] = best.i; }
       consumer_sync();
       if (tid < B) {
         Best r{-INFINITY, 0x7fffffff};
         for (int g = 0; g < 3; ++g)
-          for (int nn = 0; nn < 8; ++nn) best_merge(r, sbv[g * 64 + tid * 8 + nn], sbi[g * 64 + tid * 8 + nn]);
+          for (int nn = 0; nn < 8; ++nn) best_merge(r, sbv[g * BT * 8 + tid * 8 + nn], sbi[g * BT * 8 + tid * 8 + nn]);
         ll_store(p.part_ll + ((size_t)tid * 2 + 0) * kFlagStride + cta, __float_as_uint(r.v), ep_arg);
         ll_store(p.part_ll + ((size_t)tid * 2 + 1) * kFlagStride + cta, (uint32_t)r.i, ep_arg);
       }
@@ -1018,16 +1031,17 @@ int padded2(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : (B <= 4 ? 4 : 8)); }
 
 size_t fixed_smem2(int BT, int H, int L) {
   const int NP = BT <= 4 ? 2 : 1;
-  const size_t xrow = (size_t)4 * H * 2 + 16;
-  return (size_t)NP * BT * xrow + (size_t)2 * kNW * 64 * 4 /*red*/ + (size_t)16 * BT * 8 /*lnred*/ +
+  const size_t xrow = (size_t)4 * H * 2 + kPad;
+  const size_t red_floats = (size_t)2 * kNW * 3 * BT * 8 > 1280 ? (size_t)2 * kNW * 3 * BT * 8 : 1280;
+  return (size_t)NP * BT * xrow + red_floats * 4 /*red*/ + (size_t)16 * BT * 8 /*lnred*/ +
          (size_t)2 * BT * kOwnMax * 4 /*hloc,h2loc*/ + 192 * 8 /*sbv,sbi*/ + (8 + 8 + 64 + 64 + 8) * 4 + 16 + 2 * kMaxSlots * 8 +
-         8 * sizeof(KindInfo) + 6 * 32 * sizeof(WarpCfg) + (size_t)L * sizeof(MegaLayer) + 128;
+         8 * sizeof(KindInfo) + 6 * 16 * 4 /*slices*/ + (size_t)L * sizeof(MegaLayer) + 128;
 }
 
 // largest slot (multiple of 128 bytes, <= 40 KB) that leaves at least 3 slots; 0 if even 2 slots of two rows do not fit
 int pick_slot(int BT, int H, int L, int* n_slots) {
   const size_t avail = (size_t)227 * 1024 - fixed_smem2(BT, H, L);
-  const int widest = 4 * H * 2 + 16;
+  const int widest = 4 * H * 2 + kPad;
   for (int want = 5; want >= 2; --want) {
     long data = (long)(avail / want) - (2 * kSlotWin);
     data &= ~127L;
@@ -1064,7 +1078,7 @@ cudaError_t launch_ln_fold(const void* W, const float* g, const float* b, const 
 }
 
 bool mega2_supported(int B, int H, int nh, int L, int dtype, int num_sms) {
-  if (dtype != GP_BF16 || B < 1 || B > 8 || H % 16 != 0 || nh <= 0 || H % nh != 0 || H / nh != kD || L < 0) return false;
+  if (dtype != GP_BF16 || B < 1 || B > 8 || H % 64 != 0 || nh <= 0 || H % nh != 0 || H / nh != kD || L < 0) return false;
   if (H > 2 * kLnPairs * kConsumers) return false;
   if (num_sms < 1 || num_sms > kFlagStride || B * nh > 64 * kFlagStride) return false;
   if ((H + num_sms - 1) / num_sms + 1 > kOwnMax) return false;
@@ -1107,6 +1121,7 @@ cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s) {
   p.n_slots = n_slots;
   p.slot_data = data;
   if (const char* env = getenv("GP_MEGA_POLL_NS")) p.poll_ns = atoi(env);
+  if (const char* env = getenv("GP_MEGA_ABLATE")) p.ablate = atoi(env);   // timing experiments only: results are wrong
   const size_t smem = fixed_smem2(BT, p.H, p.L) + (size_t)n_slots * (data + (2 * kSlotWin));
   if (BT == 1) return launch2_t<1>(p, num_sms, smem, s);
   if (BT == 2) return launch2_t<2>(p, num_sms, smem, s);

@@ -14,7 +14,7 @@ from typing import List, Optional, Tuple
 import torch
 
 from ._lib import GP_BF16
-from .weights import GPT2Dims, init_weights, split_layers, stage_weight_names
+from .weights import GPT2Dims, balanced_split, init_weights, split_layers, stage_weight_names
 
 
 def tick_schedule(n_stages: int, n_streams: int, n_rounds: int) -> List[List[Optional[Tuple[int, int]]]]:
@@ -70,12 +70,19 @@ def run_ticks(rank: int, n_stages: int, n_streams: int, n_rounds: int, exchange,
 class PipelineRunner:
     def __init__(self, dims: GPT2Dims, seed: int = 0, dtype: int = GP_BF16, batch_per_stream: int = 1,
                  max_ctx: Optional[int] = None, rank: int = 0, world: int = 1, device: int = 0, recipe: str = "hf",
-                 weights=None, flags: int = 0, transport: str = "p2p"):
+                 weights=None, flags: int = 0, transport: str = "p2p", split: str = "auto"):
+        """split: "even" = equal block counts (the reference's SPLIT_AT rule generalised), "balanced" = block counts
+        chosen so that the stage that also carries ln_f + lm_head is not the slowest (it may get no block at all),
+        "auto" = balanced where the bf16 persistent kernel runs (it is what executes a head-only stage), else even."""
         from .engine import StageEngine
         self.dims, self.rank, self.world, self.B = dims, rank, world, batch_per_stream
         self.n_streams = world
         self.device = torch.device("cuda", device)
-        b, e = split_layers(dims.n_layer, world)[rank]
+        if split == "auto":
+            ok = dtype == GP_BF16 and dims.head_dim == 64 and dims.n_embd % 64 == 0 and batch_per_stream <= 8 and transport == "p2p"
+            split = "balanced" if ok else "even"
+        self.stages = balanced_split(dims, world) if split == "balanced" else split_layers(dims.n_layer, world)
+        b, e = self.stages[rank]
         self.first, self.last = rank == 0, rank == world - 1
         self.engine = StageEngine(dims, b, e, has_embed=self.first, has_head=self.last, dtype=dtype,
                                   max_batch=batch_per_stream * self.n_streams, max_ctx=max_ctx,

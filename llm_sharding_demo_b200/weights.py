@@ -75,6 +75,45 @@ def split_layers(n_layer: int, n_stages: int) -> List[Tuple[int, int]]:
     return out
 
 
+def stage_costs_us(dims: GPT2Dims, esz: int = 2) -> Tuple[float, float]:
+    """(one block, ln_f + lm_head) in microseconds of a batch-1 decode step on one B200: a fixed part for the
+    dependent phases (5 exchanges per block, the argmax exchange of the head) plus the weight stream at ~5.5-6 TB/s.
+    Calibrated on the phase trace of the persistent kernel (profiles/r02_results.md: 124M 11.5 / 17 us); only the
+    RATIO matters for the split."""
+    H, V = dims.n_embd, dims.vocab_size
+    return 9.0 + esz * (12 * H * H + 13 * H) / 5.5e6, 4.0 + esz * V * H / 6.0e6
+
+
+def balanced_split(dims: GPT2Dims, n_stages: int, esz: int = 2) -> List[Tuple[int, int]]:
+    """Contiguous block ranges per stage that minimise the slowest stage of a decode pipeline.  The last stage also
+    carries ln_f and the tied lm_head (1.5 blocks' worth of time at 124M), so it gets fewer blocks - none at all when
+    that balances best (a head-only stage: (n_layer, n_layer)).  The reference's two-shard split (server.py:51-105,
+    SPLIT_AT = n_layer // 2) is `split_layers(n_layer, 2)`; this is its time-balanced generalisation."""
+    L = dims.n_layer
+    if n_stages == 1:
+        return [(0, L)]
+    if not 2 <= n_stages <= L + 1:
+        raise ValueError(f"cannot split {L} layers into {n_stages} stages")
+    t_layer, t_head = stage_costs_us(dims, esz)
+    best = None
+    for n_last in range(0, L - (n_stages - 1) + 1):
+        front = L - n_last
+        per = -(-front // (n_stages - 1))           # ceil: the largest front stage
+        cost = max(per * t_layer, n_last * t_layer + t_head)
+        if best is None or cost < best[0] - 1e-9:
+            best = (cost, n_last)
+    n_last = best[1]
+    out, b = [], 0
+    base, rem = divmod(L - n_last, n_stages - 1)
+    for s in range(n_stages - 1):
+        # the heavier front stages come last: stage 0 also gathers the embeddings
+        e = b + base + (1 if s >= n_stages - 1 - rem else 0)
+        out.append((b, e))
+        b = e
+    out.append((b, L))
+    return out
+
+
 def stage_weight_names(dims: GPT2Dims, layer_begin: int, layer_end: int, has_embed: bool, has_head: bool) -> List[str]:
     names = []
     for name, _, _ in weight_names(dims):
