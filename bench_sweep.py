@@ -18,9 +18,9 @@ import llm_sharding_demo_b200 as L  # noqa: E402
 from bench import algorithmic_bytes_per_step, measured_peaks, synthetic_prompts  # noqa: E402
 
 CASES = [  # model, B, P, n_new
-    ("gpt2", 1, 32, 64), ("gpt2", 1, 512, 64), ("gpt2", 4, 32, 64), ("gpt2", 8, 32, 64), ("gpt2", 32, 32, 64),
-    ("gpt2", 32, 512, 32), ("gpt2-medium", 1, 32, 64), ("gpt2-medium", 8, 512, 32),
-    ("gpt2-xl", 1, 32, 32), ("gpt2-xl", 4, 32, 32), ("gpt2-xl", 32, 128, 16),
+    ("gpt2", 1, 32, 64), ("gpt2", 1, 512, 64), ("gpt2", 2, 32, 64), ("gpt2", 4, 32, 64), ("gpt2", 8, 32, 64), ("gpt2", 32, 32, 64),
+    ("gpt2", 32, 512, 32), ("gpt2-medium", 1, 32, 64), ("gpt2-medium", 2, 512, 32), ("gpt2-medium", 8, 512, 32),
+    ("gpt2-xl", 1, 32, 32), ("gpt2-xl", 4, 32, 32), ("gpt2-xl", 4, 896, 32), ("gpt2-xl", 8, 32, 32), ("gpt2-xl", 32, 128, 16),
 ]
 
 
@@ -38,7 +38,7 @@ def main():
         if key not in engines:
             engines.clear()          # one model resident at a time
             torch.cuda.empty_cache()
-            eng = L.StageEngine(dims, dtype=L.GP_BF16, max_batch=32, max_ctx=640, max_tokens=32 * 512)
+            eng = L.StageEngine(dims, dtype=L.GP_BF16, max_batch=32, max_ctx=1024, max_tokens=32 * 512)
             eng.load_weights(L.init_weights(dims, 1234, "hf"))
             engines[key] = eng
         eng = engines[key]
@@ -56,8 +56,7 @@ def main():
                           "launches_per_request": eng.last_launch_count(),
                           "algorithmic_mb_per_step": round(bytes_step / 1e6, 1), "achieved_gbs": round(achieved, 1),
                           "roofline_frac": round(achieved / peak, 4), "peak": peak, "peak_kind": kind,
-                          "decode_path": "persistent kernel" if B <= 4 else ("gemv kernels + graph" if B <= 8 else
-                                                                                "tcgen05 GEMM + graph")}), flush=True)
+                          "decode_path": "persistent kernel (mma.sync rows)" if B <= 8 else "tcgen05 GEMM + graph"}), flush=True)
 
 
 if __name__ == "__main__":

@@ -19,6 +19,21 @@ using namespace gp;
 namespace {
 thread_local std::string g_err;
 
+// Every entry point works on its engine's device but leaves the CALLER's current device as it found it: a host
+// that owns several GPUs (or torch, which caches what it believes the current device to be) must not see it move.
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int dev) {
+    err = cudaGetDevice(&prev);
+    if (err != cudaSuccess) { prev = -1; return; }
+    if (prev != dev) err = cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
 void set_err(gp_engine* e, const char* fmt, ...);
 
 struct LayerW {
@@ -559,7 +574,8 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   auto fail = [&](int rc) { gp_engine_destroy(e); return rc; };
 #define TRY(x) do { int _r = (x); if (_r != GP_OK) return fail(_r); } while (0)
 #define TRYCK(call) do { cudaError_t _c = (call); if (_c != cudaSuccess) { set_err(nullptr, "%s: %s", #call, cudaGetErrorString(_c)); return fail(GP_ECUDA); } } while (0)
-  TRYCK(cudaSetDevice(cfg->device));
+  DeviceGuard dev_guard(cfg->device);
+  TRYCK(dev_guard.err);
   TRYCK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   TRYCK(init_gemv_attrs());
   TRYCK(init_attn_attrs());
@@ -670,7 +686,7 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
 
 int gp_engine_destroy(gp_engine* e) {
   if (!e) return GP_OK;
-  cudaSetDevice(e->cfg.device);
+  DeviceGuard dev_guard(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& kv : e->decode_graphs) cudaGraphExecDestroy(kv.second);
   for (auto& kv : e->prefill_graphs) cudaGraphExecDestroy(kv.second);
@@ -689,7 +705,8 @@ int gp_engine_destroy(gp_engine* e) {
 
 int gp_load_weight(gp_engine* e, const char* name, const float* data_host, const int64_t* shape, int32_t ndim) {
   if (!e || !name || !data_host || !shape || ndim < 1 || ndim > 2) { set_err(e, "gp_load_weight: bad argument"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   const int64_t H = e->H, F = e->F;
   void* dst = nullptr;
   int64_t R = shape[0], C = ndim == 2 ? shape[1] : 1, eR = 0, eC = 1;
@@ -751,7 +768,8 @@ int gp_weights_ready(gp_engine* e) {
 
 int gp_kv_reset(gp_engine* e, int32_t slot, void* stream) {
   if (!e || slot >= e->cfg.max_batch) { set_err(e, "gp_kv_reset: bad slot"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   cudaStream_t s = (cudaStream_t)stream;
   if (slot < 0) {
     CK(e, cudaMemsetAsync(e->lens, 0, e->cfg.max_batch * sizeof(int32_t), s));
@@ -765,7 +783,8 @@ int gp_kv_reset(gp_engine* e, int32_t slot, void* stream) {
 
 int gp_kv_lengths(gp_engine* e, int32_t* lens_host, int32_t n, void* stream) {
   if (!e || !lens_host || n < 0 || n > e->cfg.max_batch) { set_err(e, "gp_kv_lengths: bad argument"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   CK(e, cudaMemcpyAsync(lens_host, e->lens, n * sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   CK(e, cudaStreamSynchronize((cudaStream_t)stream));
   return GP_OK;
@@ -775,7 +794,8 @@ int gp_stage_prefill(gp_engine* e, const int32_t* ids, const float* hidden_in, i
                      int32_t use_cache, float* hidden_out, float* logits, int32_t logits_all, int32_t* next_ids,
                      void* stream) {
   if (!e) return GP_EINVAL;
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   e->launches = 0;
   int r = prefill_impl(e, ids, hidden_in, B, T, slot0, use_cache, hidden_out, logits, logits_all, next_ids, nullptr,
                        (cudaStream_t)stream);
@@ -787,7 +807,8 @@ int gp_stage_prefill(gp_engine* e, const int32_t* ids, const float* hidden_in, i
 int gp_stage_decode(gp_engine* e, const int32_t* ids, const float* hidden_in, int32_t B, int32_t slot0,
                     float* hidden_out, float* logits, int32_t* next_ids, void* stream) {
   if (!e) return GP_EINVAL;
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   e->launches = 0;
   if (B > 0 && slot0 >= 0 && slot0 + B <= e->cfg.max_batch) {
     int room = slot_room(e, "gp_stage_decode", slot0, B, 1);
@@ -850,7 +871,8 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
       set_err(e, "gp_generate: token id %d out of range [0,%d)", prompt_ids_host[i], e->V);
       return GP_EINVAL;
     }
-  CK(e, cudaSetDevice(c.device));
+  DeviceGuard dev_guard(c.device);
+  CK(e, dev_guard.err);
   cudaStream_t s = e->stream;
   e->launches = 0;
   const int total = P + n_new;
@@ -981,7 +1003,8 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
 // ------------------------------------------------------------------- pipeline stage boundary
 int gp_comm_export(gp_engine* e, void* handle_host) {
   if (!e || !handle_host) { set_err(e, "gp_comm_export: NULL argument"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   if (!e->inbox) {
     CK(e, cudaMalloc((void**)&e->inbox, inbox_bytes(e)));
     CK(e, cudaMemset(e->inbox, 0, inbox_bytes(e)));
@@ -995,7 +1018,8 @@ int gp_comm_export(gp_engine* e, void* handle_host) {
 
 int gp_comm_connect(gp_engine* e, const void* peer_handle_host) {
   if (!e || !peer_handle_host) { set_err(e, "gp_comm_connect: NULL argument"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   if (e->peer_inbox && e->peer_is_ipc) { cudaIpcCloseMemHandle(e->peer_inbox); e->peer_inbox = nullptr; }
   cudaIpcMemHandle_t h;
   memcpy(&h, peer_handle_host, sizeof h);
@@ -1008,14 +1032,16 @@ int gp_comm_connect(gp_engine* e, const void* peer_handle_host) {
 
 int gp_comm_connect_local(gp_engine* e, gp_engine* peer) {
   if (!e || !peer) { set_err(e, "gp_comm_connect_local: NULL argument"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(peer->cfg.device));
   if (!peer->inbox) {
+    DeviceGuard peer_guard(peer->cfg.device);
+    CK(e, peer_guard.err);
     CK(e, cudaMalloc((void**)&peer->inbox, inbox_bytes(peer)));
     CK(e, cudaMemset(peer->inbox, 0, inbox_bytes(peer)));
     CK(e, cudaDeviceSynchronize());
   }
   if (inbox_bytes(peer) != inbox_bytes(e)) { set_err(e, "gp_comm_connect_local: the two stages have different hidden sizes"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(e->cfg.device));
+  DeviceGuard dev_guard(e->cfg.device);
+  CK(e, dev_guard.err);
   if (peer->cfg.device != e->cfg.device) {
     int can = 0;
     CK(e, cudaDeviceCanAccessPeer(&can, e->cfg.device, peer->cfg.device));
@@ -1044,7 +1070,8 @@ int gp_stage_decode_slots(gp_engine* e, const int32_t* ids, const float* hidden_
   }
   if (c.has_embed ? ids == nullptr : hidden_in == nullptr) { set_err(e, "gp_stage_decode_slots: missing input pointer"); return GP_EINVAL; }
   if (!c.has_head && hidden_out == nullptr) { set_err(e, "gp_stage_decode_slots: hidden_out is NULL"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(c.device));
+  DeviceGuard dev_guard(c.device);
+  CK(e, dev_guard.err);
   int r = check_ready(e);
   if (r != GP_OK) return r;
   if (!use_mega(e, B) || !use_mega2(e, B)) {
@@ -1075,7 +1102,8 @@ int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds,
   if (c.has_embed && (!first_ids || !tokens_out)) { set_err(e, "gp_pipeline_decode: stage 0 needs first_ids and tokens_out"); return GP_EINVAL; }
   if (e->sampler_on) { set_err(e, "gp_pipeline_decode: the device-resident pipeline selects greedily; sampled decoding runs per step (gp_stage_decode)"); return GP_ESTATE; }
   if (!use_mega(e, B)) { set_err(e, "gp_pipeline_decode: outside the persistent kernel's envelope (head_dim 64; B <= 8 in bf16 storage, <= 4 in fp32; cooperative launch available)"); return GP_EINVAL; }
-  CK(e, cudaSetDevice(c.device));
+  DeviceGuard dev_guard(c.device);
+  CK(e, dev_guard.err);
   int r = check_ready(e);
   if (r != GP_OK) return r;
   r = slot_room(e, "gp_pipeline_decode", 0, n_streams * B, n_rounds);

@@ -26,6 +26,7 @@
 // Arithmetic per element restates [hf] modeling_gpt2.py:262-309 (GPT2Block), :144-226 (attention over the cache),
 // pytorch_utils.py:119-123 (Conv1D), activations.py:59-66 (gelu_new); greedy selection = server.py:187-205 with
 // lowest index winning ties.
+#include <algorithm>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -47,7 +48,7 @@ constexpr int kPad = 16;                   // bytes between the end of a row and
 constexpr int kLnPairs = 2;                // LayerNorm: element pairs per thread and sequence (H <= 1920)
 constexpr int kFlagStride = 256;
 constexpr int kD = 64;                     // head dimension
-constexpr int kVPre = 12;                  // V values of a warp's keys prefetched before q arrives
+constexpr int kVPre = 3;                   // P.V iterations (4 keys each) of a warp prefetched before q arrives: contexts up to 180
 constexpr int kSpinCheck = 255;            // spin loops look at the abort word every 256 polls
 
 enum { K_QKV = 0, K_ATTN = 1, K_PROJ = 2, K_FC = 3, K_PROJ2 = 4, K_HEAD = 5 };
@@ -613,11 +614,14 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
 #pragma unroll
     for (int i = 0; i < 8; ++i) kr[i] = src[i];
   }
-  uint32_t vpre[kVPre];
+  // P.V mapping: lane = (sub = lane / 8, dg = lane % 8) takes dimensions [8 dg, 8 dg + 8) of the keys in lane slots
+  // li = 4 it + sub: one 16-byte load covers 8 dimensions, one warp instruction covers 4 keys
+  const int sub = lane >> 3, dg = lane & 7;
+  uint4 vq[kVPre];
 #pragma unroll
-  for (int i = 0; i < kVPre; ++i) {
-    const int j = i * kNW + warp;
-    vpre[i] = (j < pos) ? *reinterpret_cast<const uint32_t*>(Vc + (size_t)j * kD + 2 * lane) : 0u;
+  for (int it = 0; it < kVPre; ++it) {
+    const int jj = warp + (it * 4 + sub) * kNW;
+    vq[it] = (jj < pos) ? *reinterpret_cast<const uint4*>(Vc + (size_t)jj * kD + dg * 8) : make_uint4(0, 0, 0, 0);
   }
   consumer_sync();          // the previous user of the scratch area (red) is done
   cx.stamp(K_ATTN * 16 + 0);
@@ -635,8 +639,10 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
   }
   consumer_sync();
   cx.stamp(K_ATTN * 16 + 1);
-  float m_run = -INFINITY, l_run = 0.f, acc0 = 0.f, acc1 = 0.f;
-  const uint32_t vnew = a.kv_s[32 + lane];          // dimensions 2 lane, 2 lane + 1 of the new V row
+  float m_run = -INFINITY, l_run = 0.f, acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  const uint4 vnew = reinterpret_cast<const uint4*>(a.kv_s)[8 + dg];   // dimensions [8 dg, 8 dg + 8) of the new V row
   for (int rnd = 0; rnd * kConsumers <= ((cx.ablate & 4) ? -1 : pos); ++rnd) {
     const int j = rnd * kConsumers + j0;
     if (j == pos) {
@@ -661,8 +667,8 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
       }
       sc = d0 + d1;
     }
-    // keys of this warp in this round: lanes [0, nl)
-    const int first = rnd * kConsumers + warp;      // lane 0's key
+    // keys of this warp in this round: lane slots [0, nl)
+    const int first = rnd * kConsumers + warp;      // lane slot 0's key
     const int nl = (first <= pos) ? min(32, (pos - first) / kNW + 1) : 0;
     if (nl > 0) {
       float mx = sc;
@@ -671,38 +677,54 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
       const float m_new = fmaxf(m_run, mx);
       const float scale = __expf(m_run - m_new);    // 0 on the first round (m_run = -inf)
       const float pme = (j <= pos) ? __expf(sc - m_new) : 0.f;
-      l_run *= scale; acc0 *= scale; acc1 *= scale;
+      l_run *= scale;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] *= scale;
       m_run = m_new;
-      // P.V over this warp's keys: weight of lane li's key by shuffle, its V row read coalesced.  The new token's V
-      // row is not in the cache copy the prefetch saw: patch it in once instead of testing every key.
-      const int li_new = (pos >= first && (pos - first) % kNW == 0) ? (pos - first) / kNW : -1;   // lane slot of key `pos`
-      auto accum = [&](int li, uint32_t vbits) {
-        const float pl = __shfl_sync(FULL_MASK, pme, li);
-        acc0 = fmaf(pl, bf16lo(vbits), acc0); acc1 = fmaf(pl, bf16hi(vbits), acc1);
+      // P.V: iteration `it` handles lane slots 4 it .. 4 it + 3 (one per sub); the weight comes from that slot's lane
+      auto accum = [&](int it, uint4 v) {
+        const int li = it * 4 + sub;
+        const float pl = __shfl_sync(FULL_MASK, pme, li & 31);   // 0 for slots >= nl (their lanes hold pme = 0)
+        if (first + li * kNW == pos) v = vnew;                    // the new token's row is not in the cache copy yet
+        acc[0] = fmaf(pl, bf16lo(v.x), acc[0]); acc[1] = fmaf(pl, bf16hi(v.x), acc[1]);
+        acc[2] = fmaf(pl, bf16lo(v.y), acc[2]); acc[3] = fmaf(pl, bf16hi(v.y), acc[3]);
+        acc[4] = fmaf(pl, bf16lo(v.z), acc[4]); acc[5] = fmaf(pl, bf16hi(v.z), acc[5]);
+        acc[6] = fmaf(pl, bf16lo(v.w), acc[6]); acc[7] = fmaf(pl, bf16hi(v.w), acc[7]);
         l_run += pl;
       };
-      int li0 = 0;
+      const int n_it = (nl + 3) >> 2;
+      int it0 = 0;
       if (rnd == 0) {
 #pragma unroll
         for (int z = 0; z < kVPre; ++z)
-          if (z < nl) accum(z, (z == li_new) ? vnew : vpre[z]);
-        li0 = kVPre;
+          if (z < n_it) accum(z, vq[z]);
+        it0 = kVPre;
       }
-      for (int l0 = li0; l0 < nl; l0 += 4) {
-        uint32_t vv[4];
+      for (int i0 = it0; i0 < n_it; i0 += 4) {
+        uint4 vv[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          const int jj = first + (l0 + u) * kNW;
-          vv[u] = (l0 + u < nl && jj < pos) ? *reinterpret_cast<const uint32_t*>(Vc + (size_t)jj * kD + 2 * lane) : 0u;
+          const int jj = first + ((i0 + u) * 4 + sub) * kNW;
+          vv[u] = (i0 + u < n_it && jj < pos) ? *reinterpret_cast<const uint4*>(Vc + (size_t)jj * kD + dg * 8) : make_uint4(0, 0, 0, 0);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          if (l0 + u < nl) accum(l0 + u, (l0 + u == li_new) ? vnew : vv[u]);
+          if (i0 + u < n_it) accum(i0 + u, vv[u]);
       }
     }
   }
+  // fold the four key subsets of the warp: lanes 0..7 end up with the 64 output dimensions
+#pragma unroll
+  for (int o = 8; o <= 16; o <<= 1) {
+    l_run += __shfl_xor_sync(FULL_MASK, l_run, o);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += __shfl_xor_sync(FULL_MASK, acc[i], o);
+  }
   cx.stamp(K_ATTN * 16 + 2);
-  *reinterpret_cast<float2*>(a.part + warp * kD + 2 * lane) = make_float2(acc0, acc1);
+  if (sub == 0) {
+    *reinterpret_cast<float4*>(a.part + warp * kD + dg * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(a.part + warp * kD + dg * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
   if (lane == 0) { a.pm[warp] = m_run; a.pl[warp] = l_run; }
   consumer_sync();
   if (tid < kD) {
@@ -780,7 +802,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
     ki.pitch = ki.K * 2 + kPad;
     int rps = p.slot_data / ki.pitch;
     if (rps > kMaxRows) rps = kMaxRows;
-    if (rps > 8) rps &= ~7;                 // whole groups of 8 while more than one group fits
     ki.rps = rps;
     ki.ln = (kind == K_QKV || kind == K_FC || kind == K_HEAD) ? 1 : 0;
     ki.copy_items = ((ki.K >> 1) + kConsumers - 1) / kConsumers;
@@ -1038,17 +1059,28 @@ size_t fixed_smem2(int BT, int H, int L) {
          8 * sizeof(KindInfo) + 6 * 16 * 4 /*slices*/ + (size_t)L * sizeof(MegaLayer) + 128;
 }
 
-// largest slot (multiple of 128 bytes, <= 40 KB) that leaves at least 3 slots; 0 if even 2 slots of two rows do not fit
-int pick_slot(int BT, int H, int L, int* n_slots) {
+// Bytes of weight rows per ring slot.  A chunk costs a block barrier + a reduction + an epilogue, so a phase should
+// be as few chunks as possible: the slot is made large enough for the biggest chunk any phase can use (at most 24
+// rows, at most the rows a CTA owns), but never so large that fewer than 3 slots remain for the producer to run ahead
+// (2 when even that does not fit).  Multiple of 128 bytes; 0 if two slots of one widest row do not fit.
+int pick_slot(int BT, int H, int L, int* n_slots, int V = 50257, int G = 148) {
   const size_t avail = (size_t)227 * 1024 - fixed_smem2(BT, H, L);
-  const int widest = 4 * H * 2 + kPad;
-  for (int want = 5; want >= 2; --want) {
-    long data = (long)(avail / want) - (2 * kSlotWin);
-    data &= ~127L;
-    if (data > 40 * 1024) data = 40 * 1024;
-    if (want > 3 && data < 40 * 1024) continue;   // prefer full-size slots; go below 40 KB only to keep 3 (then 2)
-    if (data >= 2L * widest || (want == 2 && data >= widest)) {
-      int n = (int)(avail / (size_t)(data + (2 * kSlotWin)));
+  const long widest = 4L * H * 2 + kPad;
+  auto chunk = [&](long N, long K) {
+    long rows = (N + G - 1) / G;
+    if (rows > kMaxRows) rows = kMaxRows;
+    return rows * (K * 2 + kPad);
+  };
+  long useful = chunk(3L * H, H);
+  useful = std::max(useful, chunk(4L * H, H));
+  useful = std::max(useful, chunk(H, 4L * H));
+  useful = std::max(useful, chunk(V, H));
+  useful = (useful + 127) & ~127L;
+  for (int want = 3; want >= 2; --want) {
+    long cap = ((long)(avail / want) - 2 * kSlotWin) & ~127L;
+    long data = std::min(useful, cap);
+    if (data >= 2 * widest || (want == 2 && data >= widest)) {
+      int n = (int)(avail / (size_t)(data + 2 * kSlotWin));
       if (n > kMaxSlots) n = kMaxSlots;
       *n_slots = n;
       return (int)data;

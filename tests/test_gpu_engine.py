@@ -393,3 +393,100 @@ def test_full_size_cached_decode_agrees_with_stateless_prefill(L, B, P, n_new):
     # beyond the context: refused with a message, not a fault (the reference raises IndexError -> 500)
     with pytest.raises(L.GPError):
         eng.generate(prompt, n_new + 2)
+
+
+# ------------------------------------------------------------------ slot-indexed batches
+def test_decode_slots_matches_contiguous_decode(L):
+    """gp_stage_decode_slots: the sequences of a step live in arbitrary KV slots (requests joining and leaving between
+    steps).  Three sequences prefetched into slots 5, 0, 3 of an 8-slot engine and decoded together must give, step by
+    step, the logits each gives when decoded alone in contiguous slots - and the oracle's ids where the margin allows."""
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 41, "dense")
+    (eng,) = make_stages(L, dims, w, 1, L.GP_BF16, max_batch=8)
+    (solo,) = make_stages(L, dims, w, 1, L.GP_BF16, max_batch=1)
+    g = torch.Generator().manual_seed(9)
+    lens = [4, 9, 6]
+    slots = [5, 0, 3]
+    prompts = [torch.randint(0, dims.vocab_size, (1, n), generator=g) for n in lens]
+    n_new = 5
+    refs = [O.generate_cached(w, dims, p, n_new, return_logits=True) for p in prompts]
+    nxt = []
+    for p, s in zip(prompts, slots):
+        out = eng.prefill(p.to(DEV, torch.int32), slot0=s, use_cache=True, want_ids=True)
+        nxt.append(int(out["next_ids"][0]))
+    solo_logits = []
+    for p, (ref_ids, _) in zip(prompts, refs):
+        solo.kv_reset(-1)
+        solo.prefill(p.to(DEV, torch.int32), use_cache=True)
+        rows = []
+        for t in range(1, n_new):
+            rows.append(solo.decode(ref_ids[:, p.shape[1] + t - 1].to(DEV, torch.int32), want_logits=True)["logits"][0].cpu())
+        solo_logits.append(rows)
+    for t in range(1, n_new):
+        ids = torch.tensor([int(refs[i][0][0, lens[i] + t - 1]) for i in range(3)], dtype=torch.int32, device=DEV)
+        out = eng.decode_slots(ids, slots, want_logits=True)
+        for i in range(3):
+            assert float((out["logits"][i].cpu() - solo_logits[i][t - 1]).abs().max()) <= 2e-3, (t, i)
+            margin = float(O.top2_margin(refs[i][1])[0, t])
+            if margin > 2 * TOL_BF16:
+                assert int(out["next_ids"][i]) == int(refs[i][0][0, lens[i] + t]), (t, i)
+    kv = eng.kv_lengths()
+    assert [kv[s] for s in slots] == [n + n_new - 1 for n in lens] and kv[1] == kv[2] == 0
+    with pytest.raises(L.GPError, match="twice"):
+        eng.decode_slots(torch.zeros(2, dtype=torch.int32, device=DEV), [3, 3])
+    with pytest.raises(L.GPError, match="outside"):
+        eng.decode_slots(torch.zeros(1, dtype=torch.int32, device=DEV), [8])
+
+
+def test_head_only_stage_and_balanced_split(L):
+    """A time-balanced split may leave the last stage with ln_f + lm_head only (weights.balanced_split); such a stage
+    runs prefill and cached decode like any other and the pipeline's logits equal the single-stage engine's."""
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 52, "dense")
+    pd = L.GPT2Dims(**dims.to_dict())
+    ranges = [(0, 2), (2, 4), (4, 4)]
+    engines = [L.StageEngine(pd, b, e, has_embed=(i == 0), has_head=(i == 2), dtype=L.GP_BF16) for i, (b, e) in enumerate(ranges)]
+    for e in engines:
+        e.load_weights(w)
+    (single,) = make_stages(L, dims, w, 1, L.GP_BF16)
+    prompt = torch.tensor([[7, 99, 1040, 3, 512]])
+    a, _ = run_prefill(engines, prompt)
+    b, _ = run_prefill([single], prompt)
+    assert torch.equal(a["logits"], b["logits"])
+    for _ in range(3):
+        tok = b["next_ids"].cpu()
+        a = run_decode(engines, tok)
+        b = run_decode([single], tok)
+        assert float((a["logits"] - b["logits"]).abs().max()) <= 2e-3
+    assert L.balanced_split(L.PRESETS["gpt2"], 8)[-1] == (12, 12) and L.balanced_split(L.PRESETS["gpt2"], 2) == [(0, 7), (7, 12)]
+    with pytest.raises(L.GPError):
+        L.StageEngine(pd, 2, 2, has_embed=False, has_head=False, dtype=L.GP_BF16)      # an empty middle stage is refused
+
+
+def test_pipeline_watchdog_aborts_a_stalled_stage_and_leaves_the_engine_usable(L):
+    """gp_pipeline_decode waits for words a peer stage writes; when none arrive (peer missing) the watchdog must
+    return an error within the timeout, with the kernel gone from the GPU, and the same engine must then serve an
+    ordinary request correctly (the reference's counterpart: timeout=30 + raise_for_status, server.py:173-180)."""
+    import time
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 61, "dense")
+    pd = L.GPT2Dims(**dims.to_dict())
+    stage_b = L.StageEngine(pd, 2, 4, has_embed=False, has_head=True, dtype=L.GP_BF16, max_batch=2)
+    stage_b.load_weights(w)
+    stage_b.comm_export()
+    stage_b.comm_connect_local(stage_b)        # wired to itself: nobody ever writes the hidden state it waits for
+    t0 = time.perf_counter()
+    with pytest.raises(L.GPError, match="no progress"):
+        stage_b.pipeline_decode(None, 4, 2, 1, comm_epoch0=1, timeout_ms=300)
+    assert time.perf_counter() - t0 < 5.0
+    torch.cuda.synchronize()
+    # still usable: a stateless forward of the same stage equals a fresh engine's
+    stage_b.kv_reset(-1)
+    fresh = L.StageEngine(pd, 2, 4, has_embed=False, has_head=True, dtype=L.GP_BF16, max_batch=2)
+    fresh.load_weights(w)
+    hidden = torch.randn(1, 6, dims.n_embd, generator=torch.Generator().manual_seed(1)).to(DEV)
+    a = stage_b.prefill(hidden, use_cache=True, want_logits="last", want_ids=True)
+    b = fresh.prefill(hidden, use_cache=True, want_logits="last", want_ids=True)
+    assert torch.equal(a["logits"], b["logits"])
+    x = torch.randn(1, dims.n_embd, generator=torch.Generator().manual_seed(2)).to(DEV)
+    assert torch.equal(stage_b.decode(x, want_logits=True)["logits"], fresh.decode(x, want_logits=True)["logits"])

@@ -19,3 +19,44 @@ def test_pipeline_across_gpus(world):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "MULTI_GPU_CHECK_OK" in r.stdout
+
+
+def test_two_stages_in_one_process():
+    """A host that owns several GPUs in ONE process connects its stages with gp_comm_connect_local (CUDA IPC handles
+    cannot be opened by the exporting process): two stages on two GPUs, driven from two host threads, must produce the
+    tokens of the single-stage engine."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import threading
+    import llm_sharding_demo_b200 as L
+    from oracle import gpt2_oracle as O
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 71, "dense")
+    pd = L.GPT2Dims(**dims.to_dict())
+    s0 = L.StageEngine(pd, 0, 2, has_embed=True, has_head=False, dtype=L.GP_BF16, max_batch=2, device=0)
+    s1 = L.StageEngine(pd, 2, 4, has_embed=False, has_head=True, dtype=L.GP_BF16, max_batch=2, device=1)
+    single = L.StageEngine(pd, dtype=L.GP_BF16, max_batch=2, device=0)
+    for e in (s0, s1, single):
+        e.load_weights(w)
+    s0.comm_export(); s1.comm_export()
+    s0.comm_connect_local(s1); s1.comm_connect_local(s0)
+    prompts = torch.randint(0, dims.vocab_size, (2, 6), generator=torch.Generator().manual_seed(3), dtype=torch.int32)
+    n_new = 8
+    want = single.generate(prompts, n_new)
+    # prefill through both stages (host-side hop), then the device-resident decode on two threads
+    with torch.cuda.device(0):
+        h = s0.prefill(prompts.to("cuda:0"), use_cache=True)["hidden"]
+    with torch.cuda.device(1):
+        first = s1.prefill(h.to("cuda:1"), use_cache=True, want_ids=True)["next_ids"]
+    first0 = first.to("cuda:0")
+    res = {}
+
+    def run(eng, dev, ids):
+        with torch.cuda.device(dev):
+            res[dev] = eng.pipeline_decode(ids, n_new - 1, 2, 1, comm_epoch0=1, timeout_ms=5000)
+    t0 = threading.Thread(target=run, args=(s0, 0, first0))
+    t1 = threading.Thread(target=run, args=(s1, 1, None))
+    t0.start(); t1.start(); t0.join(); t1.join()
+    tokens = res[0][0].cpu()
+    got = torch.cat([prompts, first.cpu().view(2, 1), tokens], dim=1)
+    assert torch.equal(got, want)
