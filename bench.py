@@ -31,6 +31,7 @@ import torch  # noqa: E402
 
 WORKLOADS = {
     # name: (preset, B per stream, P, n_new, weight seed).  N GPUs = N stages x N streams of B sequences.
+    "tiny-gpt2-hi-n20": ("tiny-gpt2", 1, 4, 20, 0),               # BASELINE.json configs[0]: prompt "Hi, " (byte ids), 20 tokens
     "gpt2-124m-b1-p32-n128": ("gpt2", 1, 32, 128, 1234),          # BASELINE.json configs[1] (the metric's config)
     "gpt2-medium-b8-p512-n128": ("gpt2-medium", 2, 512, 128, 1234),  # configs[2]: 4 stages x 4 streams x 2 = batch 8
     "gpt2-xl-b32-p896-n128": ("gpt2-xl", 4, 896, 128, 1234),      # configs[3]: 8 stages x 8 streams x 4 = batch 32, ctx 1024
@@ -128,16 +129,46 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------------------
 _REF_WEIGHTS = {}
+_REF_MODULES = {}
 
 
-def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_probe=False):
-    """The reference's path on the host cores: full recompute of Shard A then Shard B per token
-    (server.py:169-206) via the oracle port, compute only (no HTTP/JSON).  The reference's cost per
-    token grows with the sequence, so `n_samples` steps evenly spread over the n_new-token run are
-    timed (each one token at its true sequence length) and averaged.  Returns (tokens/s, p50 s/token, info)."""
+def workload_prompts(workload, n_seq, P, vocab):
+    if workload == "tiny-gpt2-hi-n20":           # the reference README's example prompt under the byte tokenizer
+        return torch.tensor([list("Hi, ".encode())] * n_seq, dtype=torch.int32)
+    return synthetic_prompts(n_seq, P, vocab)
+
+
+def reference_modules(preset, seed):
+    """The reference's own ShardA / ShardB (server.py:68-103) built from oracle/_ref/server.py (or /root/reference)
+    on the oracle's seeded weights, or None when the file is not there (then the oracle port is timed)."""
+    from oracle import gpt2_oracle as O
+    from oracle import ref_harness as RH
+    key = (preset, seed)
+    if key in _REF_MODULES:
+        return _REF_MODULES[key]
+    mods = None
+    if RH.reference_available():
+        dims = O.PRESETS[preset]
+        if key not in _REF_WEIGHTS:
+            _REF_WEIGHTS[key] = O.init_weights(dims, seed, "hf")
+        split = O.split_layers(dims.n_layer, 2)[0][1]
+        a = RH.load_reference_server("a", split, dims, _REF_WEIGHTS[key], tag=f"_{preset}")
+        b = RH.load_reference_server("b", split, dims, _REF_WEIGHTS[key], tag=f"_{preset}")
+        mods = (a, b)
+    _REF_MODULES[key] = mods
+    return mods
+
+
+def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_probe=False, workload=None):
+    """The reference's path on the host cores: full recompute of Shard A then Shard B per token (server.py:169-206),
+    compute only (no HTTP/JSON): the reference's own ShardA / ShardB modules when oracle/_ref/server.py is present
+    (kind "reference"), else the oracle port.  The reference's cost per token grows with the sequence, so `n_samples`
+    steps evenly spread over the n_new-token run are timed (each one token at its true sequence length) and
+    averaged.  Returns (tokens/s, p50 s/token, info)."""
     from oracle import gpt2_oracle as O
     dims = O.PRESETS[preset]
     key = (preset, seed)
+    mods = reference_modules(preset, seed)
     if key not in _REF_WEIGHTS:
         _REF_WEIGHTS[key] = O.init_weights(dims, seed, "hf")
     w = _REF_WEIGHTS[key]
@@ -151,11 +182,16 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_p
         for t in steps:
             ids = synthetic_prompts(B, P + t, dims.vocab_size, seed=7 + t).long()
             t0 = time.perf_counter()
-            hidden = O.shard_a_forward(w, dims, ids, split)
-            logits = O.shard_b_forward(w, dims, hidden, split)
+            if mods is not None:
+                hidden = mods[0].shard_a(ids)
+                logits = mods[1].shard_b(hidden)
+            else:
+                hidden = O.shard_a_forward(w, dims, ids, split)
+                logits = O.shard_b_forward(w, dims, hidden, split)
             O.greedy_select(logits[:, -1])
             lat.append(time.perf_counter() - t0)
-    info = {"sampled_steps": steps, "sequences_timed": B, "sequences_in_workload": B_full}
+    info = {"kind": "reference" if mods is not None else "port", "sampled_steps": steps, "sequences_timed": B,
+            "sequences_per_stream": B_full}
     if full_path_probe and hidden.shape[1] <= 200:
         # one token of the reference's real wire format: hidden and ALL-position logits as JSON (one sequence;
         # skipped for long sequences, where it alone would take minutes)
@@ -168,6 +204,27 @@ def cpu_reference_tokens_per_s(preset, seed, B, P, n_new, n_samples, full_path_p
         info["json_overhead_s_per_token"] = round(time.perf_counter() - t0, 3)
         info["json_T"] = int(hidden2.shape[1])
     return B * len(lat) / sum(lat), statistics.median(lat), info
+
+
+def reference_full_path(preset, seed, prompt_text, n_new):
+    """the reference's REAL route path - coordinator /generate driving /forward and /forward_b
+    through FastAPI, JSON bodies and all (in-process TestClient instead of three pods), its own sampler included -
+    timed end to end.  Needs oracle/_ref/server.py.  Returns (tokens/s, seconds) or None."""
+    from oracle import gpt2_oracle as O
+    from oracle import ref_harness as RH
+    if not RH.reference_available():
+        return None
+    key = ("full", preset, seed)
+    if key not in _REF_MODULES:
+        dims = O.PRESETS[preset]
+        w = O.init_weights(dims, seed, "hf")
+        _REF_MODULES[key] = RH.ReferencePipeline(dims, w, O.split_layers(dims.n_layer, 2)[0][1], tag=f"_full_{preset}")
+        _REF_MODULES[key].generate(prompt_text, 2)   # warm-up
+    pipe = _REF_MODULES[key]
+    t0 = time.perf_counter()
+    pipe.generate(prompt_text, n_new)
+    dt = time.perf_counter() - t0
+    return n_new / dt, dt
 
 
 def ids_check(workload, dims, seed, dtype, out, P, n_new, device):
@@ -215,14 +272,15 @@ def ids_check(workload, dims, seed, dtype, out, P, n_new, device):
     return res
 
 
-def workload_config(workload, n_gpus):
-    """The `config` object of the JSON line - the same for both arms: N stages, N streams of `batch_per_stream`
-    sequences in flight (the reference arm works through the same sequences one request at a time)."""
+def workload_config(workload, n_gpus, n_streams=None):
+    """The `config` object of the JSON line - the same for both arms: N stages, `streams` micro-batches of
+    `batch_per_stream` sequences in flight (default: one per stage; the reference arm works through the same sequences
+    one request at a time)."""
     import llm_sharding_demo_b200.weights as W
     preset, B, P, n_new, _ = WORKLOADS[workload]
     dims = W.PRESETS[preset]
     bytes_step = algorithmic_bytes_per_step(dims, B, P + n_new // 2, 1, 2)
-    return {"workload": workload, "model": preset, "batch_per_stream": B, "streams": n_gpus, "prompt": P,
+    return {"workload": workload, "model": preset, "batch_per_stream": B, "streams": n_streams or n_gpus, "prompt": P,
             "new_tokens": n_new, "stages": n_gpus,
             "l2": "inputs larger than L2: %.0f MB of weights and KV cache are streamed every decode step" % (bytes_step / 1e6)}
 
@@ -234,7 +292,34 @@ def run_reference(args):
         return
     torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
     cores = torch.get_num_threads()
-    sample = min(n_new, 8)
+    n_streams = args.streams or args.gpus
+    if args.workload == "tiny-gpt2-hi-n20":
+        # configs[0] is small enough for the reference's FULL path: /generate -> /forward -> /forward_b over JSON
+        vals = []
+        for _ in range(args.warmup):
+            reference_full_path(preset, seed, "Hi, ", 2)
+        t_all = time.perf_counter()
+        for _ in range(args.steps):
+            r = reference_full_path(preset, seed, "Hi, ", n_new)
+            if r is None:
+                break
+            vals.append(r)
+        wall = time.perf_counter() - t_all
+        if vals:
+            value = n_new * len(vals) / sum(v[1] for v in vals)
+            line = {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": "tokens/s", "n_gpus": args.gpus,
+                    "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1000 * wall / args.steps, 3),
+                    "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                    "config": workload_config(args.workload, args.gpus, n_streams),
+                    "p50_token_ms": round(1000 * statistics.median(v[1] for v in vals) / n_new, 3),
+                    "cpu_baseline": {"value": round(value, 3), "unit": "tokens/s", "cores": cores, "kind": "reference",
+                                     "sample": f"the reference's own /generate (server.py:154-210, its sampler included) driving "
+                                               f"/forward and /forward_b through FastAPI + JSON in one process, {n_new} tokens per step"},
+                    "e2e": {"value": round(value, 3), "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    "gpu_launches": 0}
+            print(json.dumps(line))
+            return
+    sample = min(n_new, 8 if (P + n_new) <= 256 else 2)
     for _ in range(args.warmup):
         cpu_reference_tokens_per_s(preset, seed, B, P, n_new, 2)
     vals, lats = [], []
@@ -246,17 +331,21 @@ def run_reference(args):
         vals.append(v)
         lats.append(p50)
     wall = time.perf_counter() - t_all
-    value = B * sample * args.steps / sum(B * sample / v for v in vals)
+    value = len(vals) / sum(1.0 / v for v in vals)
+    info["sequences_in_workload"] = B * n_streams
     line = {
         "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1000 * wall / args.steps, 3),
+        "ms_per_step_is": f"wall time of one bench step = {sample} sampled tokens (not a {n_new}-token request)",
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.workload, args.gpus),
+        "config": workload_config(args.workload, args.gpus, n_streams),
         "p50_token_ms": round(1000 * statistics.median(lats), 3),
-        "cpu_baseline": {"value": round(value, 3), "unit": "tokens/s", "cores": cores, "kind": "port",
+        "cpu_baseline": {"value": round(value, 3), "unit": "tokens/s", "cores": cores, "kind": info.get("kind", "port"),
                          "sample": f"{sample} of the {n_new} decode steps per bench step, evenly spread over the run, "
                                    f"each one token at its true sequence length; full recompute of both shards "
-                                   f"per token (server.py:169-181), compute only (no HTTP/JSON); {info}"},
+                                   f"per token (server.py:169-181), compute only (no HTTP/JSON); the CPU serves the "
+                                   f"workload's {B * n_streams} sequences one after the other, so its aggregate rate is "
+                                   f"this per-sequence rate; {info}"},
         "e2e": {"value": round(value, 3), "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -269,6 +358,7 @@ def run_b200(args):
     from llm_sharding_demo_b200.pipeline import PipelineRunner
 
     preset, B, P, n_new, seed = WORKLOADS[args.workload]
+    B = args.batch_per_stream or B
     dims = L.PRESETS[preset]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -277,9 +367,9 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dtype = L.GP_BF16 if args.dtype == "bf16" else L.GP_F32
     runner = PipelineRunner(dims, seed=seed, dtype=dtype, batch_per_stream=B, max_ctx=P + n_new,
-                            rank=rank, world=world, device=local)
-    n_streams = runner.n_streams            # = world: one micro-batch per stage in flight
-    prompts = synthetic_prompts(B * n_streams, P, dims.vocab_size).pin_memory()
+                            rank=rank, world=world, device=local, n_streams=args.streams or None)
+    n_streams = runner.n_streams            # default = world: one micro-batch per stage in flight
+    prompts = workload_prompts(args.workload, B * n_streams, P, dims.vocab_size).pin_memory()
 
     for _ in range(args.warmup):
         runner.generate(prompts, n_new)
@@ -337,8 +427,9 @@ def run_b200(args):
         if world == 1:
             bytes_launch = bytes_step * (n_new - 1)
             achieved = bytes_launch / (decode_ms_mean / 1000.0) / 1e9
-            kern = ("decode_mega_kernel (persistent, %d decode steps per launch)" % (n_new - 1)) if B <= 4 else \
-                "decode step (tcgen05 GEMMs + attention kernels in a CUDA graph)"
+            mega = B <= 8 and dims.head_dim == 64 and dims.n_embd % 64 == 0
+            kern = ("decode_mega2_kernel (persistent, %d decode steps per launch)" % (n_new - 1)) if mega else \
+                "decode step (one kernel per op in a CUDA graph)"
         else:
             # one persistent launch per stage for the whole request: every round each stage streams its
             # share of the weights once per stream plus its share of the KV cache
@@ -348,7 +439,7 @@ def run_b200(args):
             bytes_round_all = n_streams * (w_bytes + kv_bytes)           # all stages together, per round
             bytes_launch = bytes_round_all * (n_new - 1) / world           # per stage launch
             achieved = bytes_launch / (decode_ms_mean / 1000.0) / 1e9
-            kern = "decode_mega_kernel (one persistent launch per stage, %d rounds x %d streams)" % (n_new - 1, n_streams)
+            kern = "decode_mega2_kernel (one persistent launch per stage, %d rounds x %d streams)" % (n_new - 1, n_streams)
         roof = {"bound": "hbm", "kernel": kern, "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind,
                 "unit": "GB/s", "frac": round(achieved / peak, 4),
                 "traffic": traffic if (world == 1 and args.workload == DEFAULT_WORKLOAD) else None,
@@ -361,7 +452,7 @@ def run_b200(args):
         torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
         sample = 16
         v, p50, info = cpu_reference_tokens_per_s(preset, seed, B, P, n_new, sample, full_path_probe=True)
-        cpu = {"value": round(v, 3), "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
+        cpu = {"value": round(v, 3), "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": info["kind"],
                "sample": f"{sample} of the {n_new} decode steps evenly spread over the run, each one token at its true "
                          f"sequence length, full recompute per token, compute only (no HTTP/JSON), p50 "
                          f"{1000 * p50:.1f} ms/token; the reference's JSON wire format would add "
@@ -371,13 +462,14 @@ def run_b200(args):
         "metric": METRIC, "value": round(value, 2), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(dev_total_ms / args.steps, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-        "config": workload_config(args.workload, world),
+        "config": dict(workload_config(args.workload, world, n_streams), batch_per_stream=B),
         "p50_token_ms": None if p50_tok_ms is None else round(p50_tok_ms, 4),
         "decode_tokens_per_s": None if not p50_tok_ms else round(B * n_streams * 1000.0 / p50_tok_ms, 1),
         "e2e": {"value": round(e2e, 2), "unit": "tokens/s", "h2d_bytes_per_step": int(prompts.numel() * 4),
                 "d2h_bytes_per_step": int(B * n_streams * (P + n_new) * 4)},
         "gpu_launches": int(launches),
         "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "ids_check": check,
+        "stage_split": [list(x) for x in runner.stages],
     }
     print(json.dumps(line), flush=True)
     if check is not None and check["mismatch"] > 0:
@@ -395,6 +487,10 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ids-check", action="store_true")
+    ap.add_argument("--batch-per-stream", type=int, default=0,
+                    help="override the workload's sequences per micro-batch (micro-batch sweeps of configs[2] / [3])")
+    ap.add_argument("--streams", type=int, default=0,
+                    help="micro-batches in flight (default: one per stage; more hide the stage-boundary latency)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3   # timing rule: at least 3 warm-up steps

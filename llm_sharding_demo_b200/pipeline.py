@@ -22,7 +22,7 @@ def tick_schedule(n_stages: int, n_streams: int, n_rounds: int) -> List[List[Opt
     Item (r, m) enters stage 0 at tick r*n_streams + m and stage s at that + s; with
     n_streams >= n_stages the ids a round produces are back at stage 0 before the next round
     needs them.  Pure function (unit-tested on CPU)."""
-    if n_streams < n_stages:
+    if n_streams < n_stages and n_rounds > 1:
         raise ValueError("need at least one stream per stage to close the token ring in time")
     n_ticks = n_rounds * n_streams + n_stages - 1
     sched = []
@@ -70,13 +70,15 @@ def run_ticks(rank: int, n_stages: int, n_streams: int, n_rounds: int, exchange,
 class PipelineRunner:
     def __init__(self, dims: GPT2Dims, seed: int = 0, dtype: int = GP_BF16, batch_per_stream: int = 1,
                  max_ctx: Optional[int] = None, rank: int = 0, world: int = 1, device: int = 0, recipe: str = "hf",
-                 weights=None, flags: int = 0, transport: str = "p2p", split: str = "auto"):
+                 weights=None, flags: int = 0, transport: str = "p2p", split: str = "auto", n_streams: Optional[int] = None):
         """split: "even" = equal block counts (the reference's SPLIT_AT rule generalised), "balanced" = block counts
         chosen so that the stage that also carries ln_f + lm_head is not the slowest (it may get no block at all),
         "auto" = balanced where the bf16 persistent kernel runs (it is what executes a head-only stage), else even."""
         from .engine import StageEngine
         self.dims, self.rank, self.world, self.B = dims, rank, world, batch_per_stream
-        self.n_streams = world
+        self.n_streams = n_streams or world
+        if self.n_streams < world and transport != "p2p":
+            raise ValueError("the host-driven (NCCL) transport needs at least one stream per stage to close the token ring in time")
         self.device = torch.device("cuda", device)
         if split == "auto":
             ok = dtype == GP_BF16 and dims.head_dim == 64 and dims.n_embd % 64 == 0 and batch_per_stream <= 8 and transport == "p2p"

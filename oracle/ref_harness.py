@@ -1,7 +1,9 @@
 """Runs the UNMODIFIED reference `server.py` in-process.  TEST INFRASTRUCTURE ONLY.
 
-Only usable where `/root/reference` exists (the build container); nothing that runs on
-the GPU box imports this.  `oracle/make_golden.py` uses it to produce `tests/golden/`.
+The file is taken from `/root/reference/server.py` (the build container) or from `oracle/_ref/server.py`, the
+git-ignored copy `oracle/build_ref.py` makes of it so that the CPU baseline can run the reference ITSELF on the GPU
+box's host cores (`bench.py --impl reference`, `cpu_baseline.kind = "reference"`).  `oracle/make_golden.py` uses this
+harness to produce `tests/golden/`.  Nothing under `llm_sharding_demo_b200/` imports it.
 
 `server.py` cannot be imported as is offline (`server.py:40-41` fetch from the HF hub) and
 its `block(h)[0]` (`server.py:85,100`) assumes transformers-4.x tuple returns.  Three stubs
@@ -23,7 +25,9 @@ from contextlib import contextmanager
 
 import torch
 
-REFERENCE_SERVER = "/root/reference/server.py"
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_CANDIDATES = ("/root/reference/server.py", os.path.join(_HERE, "_ref", "server.py"))
+REFERENCE_SERVER = next((c for c in _CANDIDATES if os.path.exists(c)), _CANDIDATES[0])
 
 
 class ByteTokenizer:

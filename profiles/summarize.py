@@ -78,5 +78,64 @@ def full():
     print("wrote full summary")
 
 
+def traffic():
+    """dram bytes per launch of the persistent decode kernel -> profiles/<tag>_traffic.json (bench.py reads the newest)."""
+    import json
+    fn = os.path.join(GO, f"prof_mega_{TAG}.ncu-rep")
+    if not os.path.exists(fn):
+        return
+    r = subprocess.run(["ncu", "-i", fn, "--page", "raw", "--csv"], capture_output=True, text=True)
+    rows = list(csv.reader(r.stdout.splitlines()))
+    if len(rows) < 3:
+        return
+    hdr, units, row = rows[0], rows[1], rows[2]
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+
+    def val(name):
+        i = hdr.index(name)
+        return float(row[i].replace(",", "")) * scale.get(units[i], 1)
+    rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+    i = hdr.index("gpu__time_duration.sum")
+    out = {"kernel": row[hdr.index("Kernel Name")][:80], "dram_bytes_per_launch": int(rd + wr), "dram_bytes_read": int(rd),
+           "dram_bytes_written": int(wr), "gpu_time_duration": row[i] + " " + units[i],
+           "source": f"ncu --set full --clock-control none, gpurun_out/prof_mega_{TAG}.ncu-rep (python bench.py --steps 1 --warmup 3)",
+           "steps_per_launch": 127}
+    with open(os.path.join(OUT, f"{TAG}_traffic.json"), "w") as f:
+        json.dump(out, f, indent=1)
+    print("wrote traffic json", out["dram_bytes_per_launch"])
+
+
+def sass():
+    """Opcode histogram of the built library: proves which kernels use tcgen05 / TMA / TMEM / mma.sync."""
+    so = os.path.join(ROOT, "llm_sharding_demo_b200", "libgpt2pipe.so")
+    if not os.path.exists(so):
+        return
+    r = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True)
+    cur, hist = None, collections.OrderedDict()
+    ops = ["UTCHMMA", "UTCQMMA", "UTMALDG", "UTMASTG", "LDTM", "STTM", "UBLKCP", "HMMA", "LDSM", "SYNCS", "UTCBAR"]
+    for ln in r.stdout.splitlines():
+        m = re.search(r"Function : (\S+)", ln)
+        if m:
+            cur = m.group(1)
+            continue
+        if cur is None:
+            continue
+        for o in ops:
+            if re.search(r"\b" + o + r"[\. ]", ln):
+                hist.setdefault(cur, collections.Counter())[o] += 1
+    with open(os.path.join(OUT, f"{TAG}_sass_histogram.txt"), "w") as f:
+        f.write("# cuobjdump -sass llm_sharding_demo_b200/libgpt2pipe.so: occurrences of tensor-core / TMA / TMEM / mbarrier opcodes per kernel\n")
+        f.write("# (UTCHMMA = tcgen05.mma, UTMALDG = cp.async.bulk.tensor, LDTM = tcgen05.ld, UBLKCP = cp.async.bulk, HMMA = mma.sync)\n")
+        tot = collections.Counter()
+        for k, c in hist.items():
+            name = subprocess.run(["c++filt", k], capture_output=True, text=True).stdout.strip()[:110]
+            f.write(f"{name}\n    " + "  ".join(f"{o}={n}" for o, n in sorted(c.items())) + "\n")
+            tot.update(c)
+        f.write("TOTAL  " + "  ".join(f"{o}={n}" for o, n in sorted(tot.items())) + "\n")
+    print("wrote sass histogram")
+
+
 launches()
 full()
+traffic()
+sass()
