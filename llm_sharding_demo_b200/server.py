@@ -120,6 +120,99 @@ def read_env(env=None) -> Dict:
 REF_TEMPERATURE, REF_TOP_K = 0.6, 40   # server.py:187-188
 
 
+class BatchScheduler:
+    """Continuous batching for the coordinator.  The reference serves one request per loop
+    (server.py:154-169: a sync handler that runs its n forward round trips to completion); here one scheduler thread
+    owns the engine and advances ALL admitted requests by one token per decode step (`gp_stage_decode_slots`: one
+    persistent-kernel launch for up to 8 sequences living in arbitrary KV slots).  A request joins between two steps -
+    its prompt is prefilled into a free slot - and leaves when it has its max_new_tokens; the others never wait for
+    it.  Greedy selection only (what the batched kernel fuses); each request's tokens are those of its solo run."""
+
+    def __init__(self, engine, max_batch: int):
+        import collections
+        self.eng = engine
+        self.max_batch = min(int(max_batch), 8)
+        self.free = list(range(self.max_batch))
+        self.active = {}                      # slot -> request dict
+        self.pending = collections.deque()
+        self.cv = threading.Condition()
+        self.stop = False
+        self.steps = 0
+        self.max_joined = 0                   # most requests ever decoded in one step (observability / tests)
+        self.thread = threading.Thread(target=self._run, name="gp-batch-scheduler", daemon=True)
+        self.thread.start()
+
+    def submit(self, ids, n_new):
+        req = {"ids": list(ids), "n_new": int(n_new), "out": list(ids), "done": threading.Event(), "error": None}
+        with self.cv:
+            self.pending.append(req)
+            self.cv.notify()
+        req["done"].wait()
+        if req["error"] is not None:
+            raise req["error"]
+        return req["out"]
+
+    def close(self):
+        with self.cv:
+            self.stop = True
+            self.cv.notify()
+        self.thread.join(timeout=5)
+
+    def _admit(self, req):
+        slot = self.free.pop()
+        eng = self.eng
+        ids = torch.tensor([req["ids"]], dtype=torch.int32, device=eng.device)
+        eng.kv_reset(slot)
+        out = eng.prefill(ids, slot0=slot, use_cache=True, want_ids=True)
+        tok = int(out["next_ids"][0])
+        req["out"].append(tok)
+        req["last"] = tok
+        self.active[slot] = req
+
+    def _retire_finished(self):
+        for slot in [s for s, r in self.active.items() if len(r["out"]) - len(r["ids"]) >= r["n_new"]]:
+            req = self.active.pop(slot)
+            self.free.append(slot)
+            req["done"].set()
+
+    def _run(self):
+        torch.cuda.set_device(self.eng.device)
+        while True:
+            with self.cv:
+                while not self.stop and not self.pending and not self.active:
+                    self.cv.wait()
+                if self.stop:
+                    for r in list(self.pending) + list(self.active.values()):
+                        r["error"] = RuntimeError("server shutting down")
+                        r["done"].set()
+                    return
+                joining = []
+                while self.pending and len(self.free) > len(joining):
+                    joining.append(self.pending.popleft())
+            try:
+                for req in joining:
+                    self._admit(req)
+                self._retire_finished()          # max_new_tokens == 1: the prefill already produced it
+                if self.active:
+                    slots = sorted(self.active)
+                    toks = torch.tensor([self.active[s]["last"] for s in slots], dtype=torch.int32, device=self.eng.device)
+                    nxt = self.eng.decode_slots(toks, slots)["next_ids"].cpu().tolist()
+                    self.steps += 1
+                    self.max_joined = max(self.max_joined, len(slots))
+                    for s, t in zip(slots, nxt):
+                        self.active[s]["out"].append(int(t))
+                        self.active[s]["last"] = int(t)
+                    self._retire_finished()
+            except Exception as ex:   # a failed step fails the requests it carried, not the server
+                for r in joining + list(self.active.values()):
+                    if not r["done"].is_set():
+                        r["error"] = ex
+                        r["done"].set()
+                for s in list(self.active):
+                    self.free.append(s)
+                self.active.clear()
+
+
 def validate_split(dims: W.GPT2Dims, split_at: int):
     """The reference ships SPLIT_AT=2 on shard A and 1 on shard B (k8s/*-deployment.yaml:22-23),
     which silently runs block 1 twice; here the split must leave both shards non-empty."""
@@ -161,7 +254,8 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
         raise ValueError(f"GP_SAMPLING={cfg['GP_SAMPLING']!r} must be 'greedy' or 'reference'")
     sampled = cfg["GP_SAMPLING"] == "reference"
     lock = threading.Lock()   # an engine handle is not re-entrant; handlers run on a thread pool
-    state = {"engine": None, "requests": 0}
+    state = {"engine": None, "requests": 0, "scheduler": None}
+    max_batch = max(1, min(8, cfg["GP_MAX_BATCH"])) if role == "coordinator" else 1
 
     def engine():
         if state["engine"] is None:
@@ -173,15 +267,24 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
                 rng = (split, dims.n_layer, False, True)
             else:
                 rng = (0, dims.n_layer, True, True)
-            eng = StageEngine(dims, rng[0], rng[1], has_embed=rng[2], has_head=rng[3], dtype=dtype, max_batch=1)
+            eng = StageEngine(dims, rng[0], rng[1], has_embed=rng[2], has_head=rng[3], dtype=dtype, max_batch=max_batch)
             names = eng.weight_names()
             w = weights if weights is not None else W.init_weights(dims, cfg["GP_SEED"], "hf", only=names)
             eng.load_weights(w)
             state["engine"] = eng
         return state["engine"]
 
+    def scheduler():
+        """The continuous-batching scheduler, when this coordinator can use it: greedy selection on the bf16 persistent
+        kernel (head_dim 64, hidden size a multiple of 64) with more than one KV slot; else None (one request at a time)."""
+        if state["scheduler"] is None:
+            ok = (max_batch > 1 and not sampled and dtype == GP_BF16 and dims.head_dim == 64 and dims.n_embd % 64 == 0)
+            state["scheduler"] = BatchScheduler(engine(), max_batch) if ok else False
+        return state["scheduler"] or None
+
     app = FastAPI()
     app.state.cfg = cfg
+    app.state.gp = state
 
     def bad(msg):
         return HTTPException(status_code=400, detail=msg)
@@ -261,6 +364,14 @@ def create_app(env=None, dims: Optional[W.GPT2Dims] = None, weights=None, tokeni
                 else:
                     ids.append(int(torch.argmax(last)))
             return {"generated": tokenizer.decode(ids, skip_special_tokens=True)}
+        with lock:
+            sched = scheduler()
+        if sched is not None:
+            try:
+                out_ids = sched.submit(input_ids, n_new)
+            except Exception as ex:
+                raise HTTPException(status_code=500, detail=str(ex))
+            return {"generated": tokenizer.decode(out_ids, skip_special_tokens=True)}
         with lock:
             eng = engine()
             state["requests"] += 1

@@ -60,3 +60,49 @@ def test_two_stages_in_one_process():
     tokens = res[0][0].cpu()
     got = torch.cat([prompts, first.cpu().view(2, 1), tokens], dim=1)
     assert torch.equal(got, want)
+
+
+def test_pipeline_pod_serves_generate():
+    """The N-GPU pod of k8s/pipeline-pod.yaml (`torchrun -m llm_sharding_demo_b200.pod`): /healthz turns ready, and
+    /generate returns the text a single-GPU engine produces for the same prompt and weights."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import signal
+    import time
+    import requests
+    import llm_sharding_demo_b200 as L
+    from llm_sharding_demo_b200.server import ByteTokenizer
+    port = 5057
+    env = dict(os.environ, MODEL_ID="gpt2", GP_RANDOM_INIT="1", GP_SEED="3", SHARD_PORT=str(port), GP_MAX_CTX="96",
+               PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29688", "-m", "llm_sharding_demo_b200.pod"]
+    proc = subprocess.Popen(cmd, env=env, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, start_new_session=True)
+    try:
+        ready = False
+        for _ in range(240):
+            if proc.poll() is not None:
+                break
+            try:
+                if requests.get(f"http://127.0.0.1:{port}/healthz", timeout=1).status_code == 200:
+                    ready = True
+                    break
+            except Exception:
+                time.sleep(0.5)
+        assert ready, (proc.stdout.read().decode()[-2000:] if proc.poll() is not None else "pod never became ready")
+        r = requests.post(f"http://127.0.0.1:{port}/generate", json={"prompt": "Hi, ", "max_new_tokens": 12}, timeout=60)
+        assert r.status_code == 200, r.text
+        dims = L.PRESETS["gpt2"]
+        eng = L.StageEngine(dims, dtype=L.GP_BF16, max_batch=1, max_ctx=96)
+        eng.load_weights(L.init_weights(dims, 3, "hf"))
+        tok = ByteTokenizer()
+        want = eng.generate(torch.tensor([tok.encode("Hi, ")], dtype=torch.int32), 12)
+        assert r.json()["generated"] == tok.decode(want[0].tolist())
+        # the reference's default and its zero-token case
+        assert requests.post(f"http://127.0.0.1:{port}/generate", json={"prompt": "abc", "max_new_tokens": 0}, timeout=30).json() == {"generated": "abc"}
+    finally:
+        os.killpg(proc.pid, signal.SIGTERM)
+        try:
+            proc.wait(timeout=20)
+        except Exception:
+            os.killpg(proc.pid, signal.SIGKILL)

@@ -238,3 +238,82 @@ def test_server_serves_a_checkpoint_from_disk(tmp_path, golden_dir):
     from_dict = TestClient(S.create_app(env=dict(env, MODEL_ID="x"), dims=dims, weights=w, tokenizer=S.ByteTokenizer()))
     body = {"prompt": "Hi, ", "max_new_tokens": 8}
     assert from_disk.post("/generate", json=body).json() == from_dict.post("/generate", json=body).json()
+
+
+@pytest.mark.gpu
+def test_overlapping_generate_calls_are_batched_and_equal_their_solo_runs():
+    """the reference serves one /generate at a time (server.py:154-169).  Here requests that
+    overlap are decoded together, one persistent-kernel step for all of them, joining and leaving between steps -
+    and every request must still get exactly the text of its solo run."""
+    import threading
+    from oracle import gpt2_oracle as O
+    dims_o = O.PRESETS["mini"]
+    dims = L.GPT2Dims(**dims_o.to_dict())
+    w = O.init_weights(dims_o, 88, "dense")
+    env = {"SHARD_ROLE": "coordinator", "MODEL_ID": "x", "SPLIT_AT": "2", "GP_DTYPE": "bf16"}
+    batched = S.create_app(env=dict(env, GP_MAX_BATCH="4"), dims=dims, weights=w, tokenizer=S.ByteTokenizer())
+    solo = TestClient(S.create_app(env=dict(env, GP_MAX_BATCH="1"), dims=dims, weights=w, tokenizer=S.ByteTokenizer()))
+    client = TestClient(batched)
+    reqs = [("hello there", 40), ("A", 25), ("pipeline stages", 33), ("xyz!", 1), ("the quick brown fox", 18)]
+    want = [solo.post("/generate", json={"prompt": p, "max_new_tokens": n}).json()["generated"] for p, n in reqs]
+    got = [None] * len(reqs)
+
+    def call(i):
+        p, n = reqs[i]
+        r = client.post("/generate", json={"prompt": p, "max_new_tokens": n})
+        assert r.status_code == 200, r.text
+        got[i] = r.json()["generated"]
+    threads = [threading.Thread(target=call, args=(i,)) for i in range(len(reqs))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=120)
+    assert got == want
+    sched = batched.state.gp["scheduler"]
+    assert sched and sched.max_joined >= 2, "the requests never shared a decode step"
+    assert sorted(sched.free) == [0, 1, 2, 3] and not sched.active      # every KV slot was given back
+    # a sixth request after the burst still works (slots are reusable) and 0 tokens returns the prompt
+    r = client.post("/generate", json={"prompt": "again", "max_new_tokens": 3})
+    assert r.json()["generated"] == solo.post("/generate", json={"prompt": "again", "max_new_tokens": 3}).json()["generated"]
+    sched.close()
+
+
+@pytest.mark.gpu
+def test_checkpoint_on_disk_gives_the_oracle_logits(tmp_path):
+    """a Hugging Face-layout GPT-2 checkpoint (config.json + model.safetensors with the
+    `transformer.` prefix, Conv1D [in,out] matrices, tied lm_head) loaded by `weights.load_checkpoint` into the engine
+    must give the logits the ORACLE computes from the same file read independently (server.py:40-41 is the reference
+    side: from_pretrained)."""
+    import struct
+    from oracle import gpt2_oracle as O
+    dims_o = O.PRESETS["mini"]
+    w = O.init_weights(dims_o, 123, "dense")
+    sd = O.hf_state_dict(w)
+    # write the checkpoint by hand: safetensors container + config.json
+    header, blobs, off = {}, [], 0
+    for k, v in sd.items():
+        b = v.contiguous().numpy().astype(np.float32).tobytes()
+        header[k] = {"dtype": "F32", "shape": list(v.shape), "data_offsets": [off, off + len(b)]}
+        blobs.append(b)
+        off += len(b)
+    hj = json.dumps(header).encode()
+    d = tmp_path / "ckpt"
+    d.mkdir()
+    with open(d / "model.safetensors", "wb") as f:
+        f.write(struct.pack("<Q", len(hj)) + hj + b"".join(blobs))
+    with open(d / "config.json", "w") as f:
+        json.dump({"n_layer": dims_o.n_layer, "n_embd": dims_o.n_embd, "n_head": dims_o.n_head, "vocab_size": dims_o.vocab_size,
+                   "n_positions": dims_o.n_positions, "activation_function": "gelu_new", "layer_norm_epsilon": 1e-5}, f)
+    ck_dims, ck_w = L.load_checkpoint(str(d))
+    assert ck_dims == L.GPT2Dims(**dims_o.to_dict())
+    ids = torch.randint(0, dims_o.vocab_size, (2, 11), generator=torch.Generator().manual_seed(5))
+    # the oracle reads the file on its own: strip the prefix, drop the tied head
+    raw = L.weights._read_safetensors(str(d / "model.safetensors"))
+    ow = {k[len("transformer."):]: v for k, v in raw.items() if k.startswith("transformer.")}
+    ref = O.stage_forward(ow, dims_o, ids, 0, dims_o.n_layer, True, True, None, 0)      # logits [2, 11, V]
+    for dtype, tol in ((L.GP_F32, 3e-4), (L.GP_BF16, 0.06)):
+        eng = L.StageEngine(ck_dims, dtype=dtype, max_batch=2)
+        eng.load_weights(ck_w)
+        got = eng.prefill(ids.to("cuda:0", torch.int32), use_cache=False, want_logits="all")["logits"].cpu()
+        assert float((got - ref).abs().max()) <= tol, dtype
+        eng.close()
