@@ -29,15 +29,27 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
-WORKLOADS = {
+class _Workloads(dict):
+    """`custom:<preset>:<B per stream>:<P>:<n_new>` names a workload on the fly (configs[4] sweeps)."""
+    def __missing__(self, key):
+        if isinstance(key, str) and key.startswith("custom:"):
+            _, preset, B, P, n = key.split(":")
+            return (preset, int(B), int(P), int(n), 1234)
+        raise KeyError(key)
+
+    def __contains__(self, key):
+        return dict.__contains__(self, key) or (isinstance(key, str) and key.startswith("custom:"))
+METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
+
+
+WORKLOADS = _Workloads({
     # name: (preset, B per stream, P, n_new, weight seed).  N GPUs = N stages x N streams of B sequences.
     "tiny-gpt2-hi-n20": ("tiny-gpt2", 1, 4, 20, 0),               # BASELINE.json configs[0]: prompt "Hi, " (byte ids), 20 tokens
     "gpt2-124m-b1-p32-n128": ("gpt2", 1, 32, 128, 1234),          # BASELINE.json configs[1] (the metric's config)
     "gpt2-medium-b8-p512-n128": ("gpt2-medium", 2, 512, 128, 1234),  # configs[2]: 4 stages x 4 streams x 2 = batch 8
     "gpt2-xl-b32-p896-n128": ("gpt2-xl", 4, 896, 128, 1234),      # configs[3]: 8 stages x 8 streams x 4 = batch 32, ctx 1024
-}
+})
 DEFAULT_WORKLOAD = "gpt2-124m-b1-p32-n128"
-METRIC = "decode tokens/s & p50 per-token latency, GPT-2 pipeline at 1/2/4/8 B200"
 
 
 def ncu_traffic():
@@ -483,7 +495,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD,
+                    help="one of %s, or custom:<preset>:<B per stream>:<P>:<n_new>" % ", ".join(sorted(WORKLOADS)))
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ids-check", action="store_true")
@@ -492,6 +505,8 @@ def main():
     ap.add_argument("--streams", type=int, default=0,
                     help="micro-batches in flight (default: one per stage; more hide the stage-boundary latency)")
     args = ap.parse_args()
+    if args.workload not in WORKLOADS:
+        ap.error(f"unknown workload {args.workload!r}")
     if args.warmup < 3:
         args.warmup = 3   # timing rule: at least 3 warm-up steps
     if args.impl == "reference":

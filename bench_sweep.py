@@ -24,13 +24,17 @@ CASES = [  # model, B, P, n_new
 ]
 
 
+CFG5 = [("gpt2", B, P, 64) for P in (32, 512, 960) for B in (1, 2, 4, 8, 16, 32, 64, 128, 256)]   # BASELINE.json configs[4], one stage
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
+    ap.add_argument("--cfg5", action="store_true", help="the 124M batch x prompt grid of BASELINE.json configs[4] on one GPU")
     args = ap.parse_args()
     peak, kind = measured_peaks()
     engines = {}
-    for model, B, P, n_new in CASES:
+    for model, B, P, n_new in (CFG5 if args.cfg5 else CASES):
         if args.only and args.only not in model:
             continue
         dims = L.PRESETS[model]
@@ -38,7 +42,8 @@ def main():
         if key not in engines:
             engines.clear()          # one model resident at a time
             torch.cuda.empty_cache()
-            eng = L.StageEngine(dims, dtype=L.GP_BF16, max_batch=32, max_ctx=1024, max_tokens=32 * 512)
+            mb = 256 if args.cfg5 else 32
+            eng = L.StageEngine(dims, dtype=L.GP_BF16, max_batch=mb, max_ctx=1024, max_tokens=mb * (960 if args.cfg5 else 512))
             eng.load_weights(L.init_weights(dims, 1234, "hf"))
             engines[key] = eng
         eng = engines[key]
@@ -51,7 +56,15 @@ def main():
         t_ctx = P + n_new // 2
         bytes_step = algorithmic_bytes_per_step(dims, B, t_ctx, 1, 2)
         achieved = bytes_step / (step_ms * 1e-3) / 1e9
-        print(json.dumps({"model": model, "B": B, "P": P, "n_new": n_new, "prefill_ms": round(tm["prefill_ms"], 3),
+        cpu = None
+        if args.cfg5 and B == 1:
+            # the reference's compute-only CPU figure for the same point (its own ShardA / ShardB when oracle/_ref is there)
+            from bench import cpu_reference_tokens_per_s
+            torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+            v, _, info = cpu_reference_tokens_per_s(model, 1234, 1, P, n_new, 2)
+            cpu = {"tokens_per_s": round(v, 2), "kind": info["kind"], "cores": torch.get_num_threads()}
+        print(json.dumps({"model": model, "B": B, "P": P, "n_new": n_new, "stages": 1, "cpu_reference": cpu,
+                          "prefill_ms": round(tm["prefill_ms"], 3),
                           "decode_tokens_per_s": round(B * 1000.0 / step_ms, 1), "p50_step_ms": round(step_ms, 4),
                           "launches_per_request": eng.last_launch_count(),
                           "algorithmic_mb_per_step": round(bytes_step / 1e6, 1), "achieved_gbs": round(achieved, 1),

@@ -352,7 +352,9 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
     std::vector<long long> t((size_t)e->num_sms * kTraceCap);
     CK(e, cudaStreamSynchronize(s));
     CK(e, cudaMemcpy(t.data(), e->trace, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
-    FILE* f = fopen(trace_path, "wb");
+    char path[512];
+    snprintf(path, sizeof path, trace_path, c.device);   // "%d" in GP_MEGA_TRACE = device ordinal (one file per pipeline stage)
+    FILE* f = fopen(path, "wb");
     if (f) { fwrite(t.data(), sizeof(long long), t.size(), f); fclose(f); }
   }
   return GP_OK;

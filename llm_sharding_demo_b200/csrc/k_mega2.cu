@@ -869,6 +869,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
     const uint32_t cep = p.comm_epoch0 + (uint32_t)round;   // epoch of this item's words on the stage boundary
     const uint32_t ep_item = p.epoch0 + (uint32_t)item * ep_per_item;
     const u64* in_hid = p.inbox_hid ? p.inbox_hid + (size_t)strm * B * H : nullptr;
+    cx.tracing = (p.trace != nullptr && item == n_items - 1);
+    cx.stamp(7 * 16 + 3);
     // ---- position and (stage 0) token of every sequence of this item
     if (tid < B) {
       s_pos[tid] = min(s_pos0[strm * B + tid] + round, p.max_ctx - 1);
@@ -902,8 +904,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
       hloc[b * kOwnMax + (col - c0)] = hv;
       ll_store(p.h_ll + ll_off((size_t)b * H + col, cx.ll_shift), __float_as_uint(hv), ep_item);
     }
-    cx.tracing = (p.trace != nullptr && item == n_items - 1);
-    cx.stamp(7 * 16 + 0);
+    cx.stamp(7 * 16 + 0, __float_as_uint(hloc[0]));
     Best best{-INFINITY, 0x7fffffff};
     int li = 0, kind = (L > 0) ? K_QKV : K_HEAD;
     for (int ph = 0; ph < n_ph; ++ph) {

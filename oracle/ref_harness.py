@@ -101,7 +101,10 @@ def load_reference_server(role: str, split_at: int, dims, weights, tag: str = ""
             spec = importlib.util.spec_from_file_location(name, REFERENCE_SERVER)
             mod = importlib.util.module_from_spec(spec)
             sys.modules[name] = mod
-            spec.loader.exec_module(mod)
+            # server.py:27 prints its role at import; keep stdout clean for callers that emit JSON lines
+            import contextlib
+            with contextlib.redirect_stdout(sys.stderr):
+                spec.loader.exec_module(mod)
     finally:
         for k, v in old.items():
             if v is None:

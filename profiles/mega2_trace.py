@@ -26,7 +26,7 @@ def name(tag):
     if ph == 1:
         return "attn:" + ["entered", "q-ok", "loop-done", "done"][ev]
     if ph == 7:
-        return "step:" + ["start", "end", "partials"][ev]
+        return "step:" + ["start", "end", "partials", "item-begin"][ev]
     return f"{PH.get(ph, ph)}:{EV.get(ev, ev)}"
 
 
