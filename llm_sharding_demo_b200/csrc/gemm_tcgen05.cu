@@ -293,7 +293,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
-int g_num_sms = 148;
+int g_num_sms = 148;   // replaced by the queried SM count in init_gemm_tc()
 std::mutex g_mu;
 std::map<std::tuple<const void*, int, int, int>, CUtensorMap> g_maps;
 
@@ -346,7 +346,7 @@ cudaError_t launch_t(const CUtensorMap& tw, const CUtensorMap& ta, const float* 
   if (e != cudaSuccess || splits <= 1) return e;
   size_t mn = (size_t)M * N;
   int g = (int)((mn + 255) / 256);
-  if (g > 148 * 8) g = 148 * 8;
+  if (g > g_num_sms * 8) g = g_num_sms * 8;
   splitk_epilogue_kernel<OT><<<g, 256, 0, s>>>(partial, splits, bias, residual, ldr, (OT*)out, ldo, M, N, flags);
   return cudaGetLastError();
 }
@@ -382,7 +382,7 @@ int gemm_tc_splits(int M, int N, int K, size_t partial_floats) {
   const int BM = (M <= 32) ? 32 : (M < 512 ? 128 : 256);
   const int tiles = ((N + kBlockN - 1) / kBlockN) * ((M + BM - 1) / BM);
   const int nk = (K + kBlockK - 1) / kBlockK;
-  int s = 148 / tiles;
+  int s = g_num_sms / tiles;
   if (s > 8) s = 8;
   if (s > nk / 2) s = nk / 2;   // at least two k-blocks per CTA
   if (s < 2) return 1;

@@ -285,7 +285,7 @@ cudaError_t launch_gemv(const GemvParams& p, int dtype, cudaStream_t s) {
   const size_t smem = (size_t)padded_batch(p.B) * p.K * sizeof(float);
   // one output row per warp while that still fills the GPU, two beyond
   int grid = (p.N + kWarps - 1) / kWarps;
-  const int cap = 148 * 8;
+  const int cap = device_sm_count() * 8;
   if (grid > cap) grid = cap;
   return dtype == GP_BF16 ? gemv_dispatch<bf16>(p, grid, smem, s) : gemv_dispatch<float>(p, grid, smem, s);
 }

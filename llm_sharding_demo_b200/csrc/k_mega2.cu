@@ -391,6 +391,7 @@ __device__ __forceinline__ void stage_copy(Ctx<TR>& cx, const u64* src, uint32_t
 // ([hf] modeling_gpt2.py:252,254,505: biased variance, eps inside the square root.)
 template <int BT, bool TR>
 __device__ __forceinline__ void stage_ln(Ctx<TR>& cx, const u64* src, uint32_t epoch, const float* ln_g, int K, int tag) {
+  constexpr int BH = (BT > 4) ? 4 : BT;   // sequences handled per pass (register budget)
   const int tid = threadIdx.x, w = tid >> 5, l = tid & 31, B = cx.B;
   const int halfK = K >> 1;
   float2 gg[kLnPairs];
@@ -400,54 +401,61 @@ __device__ __forceinline__ void stage_ln(Ctx<TR>& cx, const u64* src, uint32_t e
     gg[i] = (q < halfK) ? *reinterpret_cast<const float2*>(ln_g + 2 * q) : make_float2(0.f, 0.f);
   }
   cx.stamp(tag + 0);
-  float x[BT][kLnPairs][2];
-  unsigned spins = 0;
-  bool ok;
-  do {
-    ok = true;
+#pragma unroll 1
+  for (int b0 = 0; b0 < BT; b0 += BH) {
+    if (b0 >= B) break;
+    float x[BH][kLnPairs][2];
+    unsigned spins = 0;
+    bool ok;
+    do {
+      ok = true;
 #pragma unroll
-    for (int i = 0; i < kLnPairs; ++i)
+      for (int i = 0; i < kLnPairs; ++i)
 #pragma unroll
-      for (int b = 0; b < BT; ++b) {
+        for (int bb = 0; bb < BH; ++bb) {
+          const int b = b0 + bb, q = tid + i * kConsumers;
+          const bool live = q < halfK && b < B;
+          u64 a, c;
+          ll_load2_if(src + ll_off((size_t)b * K + 2 * q, cx.ll_shift), live, false, a, c);
+          x[bb][i][0] = __uint_as_float((uint32_t)a);
+          x[bb][i][1] = __uint_as_float((uint32_t)c);
+          ok = ok && (!live || ((uint32_t)(a >> 32) == epoch && (uint32_t)(c >> 32) == epoch));
+        }
+    } while (!ok && !cx.give_up(spins));
+    if (b0 == 0) {
+      cx.warp_mark(tag >> 4, cx.dbg_layer, __float_as_uint(x[0][0][0]));
+      cx.stamp(tag + 1);
+    }
+    float s[BH], ss[BH];
+#pragma unroll
+    for (int bb = 0; bb < BH; ++bb) {
+      const int b = b0 + bb;
+      s[bb] = 0.f; ss[bb] = 0.f;
+#pragma unroll
+      for (int i = 0; i < kLnPairs; ++i) {
         const int q = tid + i * kConsumers;
-        const bool live = q < halfK && b < B;
-        u64 a, c;
-        ll_load2_if(src + ll_off((size_t)b * K + 2 * q, cx.ll_shift), live, false, a, c);
-        x[b][i][0] = __uint_as_float((uint32_t)a);
-        x[b][i][1] = __uint_as_float((uint32_t)c);
-        ok = ok && (!live || ((uint32_t)(a >> 32) == epoch && (uint32_t)(c >> 32) == epoch));
-      }
-  } while (!ok && !cx.give_up(spins));
-  cx.warp_mark(tag >> 4, cx.dbg_layer, __float_as_uint(x[0][0][0]));
-  cx.stamp(tag + 1);
-  float s[BT], ss[BT];
-#pragma unroll
-  for (int b = 0; b < BT; ++b) {
-    s[b] = 0.f; ss[b] = 0.f;
-#pragma unroll
-    for (int i = 0; i < kLnPairs; ++i) {
-      const int q = tid + i * kConsumers;
-      if (q < halfK && b < B) {
-        const float x0 = x[b][i][0], x1 = x[b][i][1];
-        s[b] += x0 + x1;
-        ss[b] = fmaf(x0, x0, fmaf(x1, x1, ss[b]));
-        uint32_t hi, lo;
-        split_hi_lo(x0 * gg[i].x, x1 * gg[i].y, hi, lo);
-        sts32(cx.xs_hi + b * cx.xrow + 4 * q, hi);
-        if (BT <= 4) sts32(cx.xs_lo + b * cx.xrow + 4 * q, lo);
+        if (q < halfK && b < B) {
+          const float x0 = x[bb][i][0], x1 = x[bb][i][1];
+          s[bb] += x0 + x1;
+          ss[bb] = fmaf(x0, x0, fmaf(x1, x1, ss[bb]));
+          uint32_t hi, lo;
+          split_hi_lo(x0 * gg[i].x, x1 * gg[i].y, hi, lo);
+          sts32(cx.xs_hi + b * cx.xrow + 4 * q, hi);
+          if (BT <= 4) sts32(cx.xs_lo + b * cx.xrow + 4 * q, lo);
+        }
       }
     }
-  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1)
+    for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
-    for (int b = 0; b < BT; ++b) {
-      s[b] += __shfl_xor_sync(FULL_MASK, s[b], o);
-      ss[b] += __shfl_xor_sync(FULL_MASK, ss[b], o);
+      for (int bb = 0; bb < BH; ++bb) {
+        s[bb] += __shfl_xor_sync(FULL_MASK, s[bb], o);
+        ss[bb] += __shfl_xor_sync(FULL_MASK, ss[bb], o);
+      }
+    if (l == 0) {
+#pragma unroll
+      for (int bb = 0; bb < BH; ++bb) cx.lnred[w * BT + b0 + bb] = make_float2(s[bb], ss[bb]);
     }
-  if (l == 0) {
-#pragma unroll
-    for (int b = 0; b < BT; ++b) cx.lnred[w * BT + b] = make_float2(s[b], ss[b]);
   }
 }
 

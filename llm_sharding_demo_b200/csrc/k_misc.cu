@@ -358,7 +358,7 @@ cudaError_t launch_convert(const float* src, void* dst, int R, int C, bool trans
   } else {
     const size_t n = (size_t)R * C;
     int grid = (int)((n + 255) / 256);
-    if (grid > 148 * 16) grid = 148 * 16;
+    if (grid > device_sm_count() * 16) grid = device_sm_count() * 16;
     if (dtype == GP_BF16) convert_kernel<bf16><<<grid, 256, 0, s>>>(src, (bf16*)dst, n);
     else convert_kernel<float><<<grid, 256, 0, s>>>(src, (float*)dst, n);
   }
@@ -374,6 +374,17 @@ cudaError_t launch_argmax_rows(const float* logits, int ldl, int B, int V, int32
 cudaError_t launch_gather_last(const float* src, float* dst, int B, int T, int H, cudaStream_t s) {
   gather_last_kernel<<<B, 256, 0, s>>>(src, dst, T, H);
   return cudaGetLastError();
+}
+
+int device_sm_count() {
+  static thread_local int cached_dev = -1, cached = 148;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return cached;
+  if (dev != cached_dev) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) { cached = n; cached_dev = dev; }
+  }
+  return cached;
 }
 
 }  // namespace gp

@@ -137,6 +137,9 @@ cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s);
 cudaError_t launch_ln_fold(const void* W, const float* g, const float* b, const float* bias, float* u, float* c, int N, int K,
                            cudaStream_t s);
 
+// SM count of the current device (queried once per device; 148 on B200)
+int device_sm_count();
+
 // stores `msg` as this thread's last error (what gp_last_error(NULL) returns); engine.cu
 void record_error(const char* msg);
 
