@@ -1164,10 +1164,12 @@ cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s) {
   if (const char* env = getenv("GP_MEGA_POLL_NS")) p.poll_ns = atoi(env);
   if (const char* env = getenv("GP_MEGA_ABLATE")) p.ablate = atoi(env);   // timing experiments only: results are wrong
   const size_t smem = fixed_smem2(BT, p.H, p.L) + (size_t)n_slots * (data + (2 * kSlotWin));
-  if (BT == 1) return launch2_t<1>(p, num_sms, smem, s);
-  if (BT == 2) return launch2_t<2>(p, num_sms, smem, s);
-  if (BT == 4) return launch2_t<4>(p, num_sms, smem, s);
-  return launch2_t<8>(p, num_sms, smem, s);
+  int grid = num_sms;
+  if (const char* env = getenv("GP_MEGA_CTAS")) { int v = atoi(env); if (v >= p.B * p.nh && v >= 16 && v < num_sms) grid = v; }   // experiment: fewer participants
+  if (BT == 1) return launch2_t<1>(p, grid, smem, s);
+  if (BT == 2) return launch2_t<2>(p, grid, smem, s);
+  if (BT == 4) return launch2_t<4>(p, grid, smem, s);
+  return launch2_t<8>(p, grid, smem, s);
 }
 
 }  // namespace gp
