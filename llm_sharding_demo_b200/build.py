@@ -10,7 +10,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libgpt2pipe.so")
-SOURCES = ["engine.cu", "k_gemv.cu", "k_attn.cu", "k_misc.cu", "gemm_tcgen05.cu", "k_mega.cu", "k_mega2.cu", "k_sample.cu"]
+SOURCES = ["engine.cu", "k_gemv.cu", "k_attn.cu", "k_attn_mma.cu", "k_misc.cu", "gemm_tcgen05.cu", "k_mega.cu", "k_mega2.cu", "k_sample.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 

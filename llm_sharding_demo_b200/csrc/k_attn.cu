@@ -3,6 +3,8 @@
 // [hf] integrations/sdpa_attention.py:65,77,92-101 / modeling_gpt2.py:96-100,186-222.
 // KV cache layout: [slot, head, max_ctx, d], d contiguous, so one (slot, head) is a single
 // contiguous stream for the decode kernel.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -310,6 +312,9 @@ cudaError_t launch_attn_decode(const float* q, const void* kc, const void* vc, c
 cudaError_t launch_attn_prefill(const void* qkv, void* out, int B, int T, int nh, int d, int dtype,
                                 cudaStream_t s) {
   if (B <= 0 || T <= 0 || nh <= 0 || d <= 0 || T > 8192) return cudaErrorInvalidValue;
+  // bf16 storage, head_dim 64: the tensor-core kernel (k_attn_mma.cu); GP_ATTN_SIMT=1 keeps the SIMT kernel for A/B runs
+  static const bool force_simt = getenv("GP_ATTN_SIMT") != nullptr;
+  if (dtype == GP_BF16 && d == 64 && !force_simt) return launch_attn_prefill64_mma(qkv, out, B, T, nh, s);
   return dtype == GP_BF16 ? prefill_launch<bf16>(qkv, out, B, T, nh, d, s)
                           : prefill_launch<float>(qkv, out, B, T, nh, d, s);
 }

@@ -56,6 +56,8 @@ cudaError_t launch_attn_decode(const float* q, const void* kc, const void* vc, c
 cudaError_t launch_attn_prefill(const void* qkv, void* out, int B, int T, int nh, int d, int dtype,
                                 cudaStream_t s);
 cudaError_t init_attn_attrs();
+// causal prefill attention on mma.sync tensor cores: qkv bf16 [B,T,3H] -> out bf16 [B,T,H], head_dim 64 (k_attn_mma.cu)
+cudaError_t launch_attn_prefill64_mma(const void* qkv, void* out, int B, int T, int nh, cudaStream_t s);
 
 // ---- misc
 cudaError_t launch_embed(const int32_t* ids, const int32_t* pos, int pos0, int T, const int32_t* lens,

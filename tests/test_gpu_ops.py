@@ -126,7 +126,7 @@ def test_attn_decode(ops, dt, B, nh, d, max_ctx, lens):
 
 
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("B,T,nh,d", [(1, 32, 12, 64), (2, 100, 2, 64), (1, 4, 2, 1), (2, 7, 3, 32), (1, 200, 3, 64)])
+@pytest.mark.parametrize("B,T,nh,d", [(1, 32, 12, 64), (2, 100, 2, 64), (1, 4, 2, 1), (2, 7, 3, 32), (1, 200, 3, 64), (2, 1000, 2, 64), (1, 1, 2, 64)])
 def test_attn_prefill(ops, dt, B, T, nh, d):
     H = nh * d
     qkv = rnd(B, T, 3 * H, seed=20)
