@@ -412,9 +412,26 @@ int prefill_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B
   }
   if (next_ids || seq_for_generate || (logits && !logits_all)) {
     LAUNCH(e, launch_gather_last(e->h, e->hlast, B, T, H, s));
-    // generate: the first new token goes to seq[b][len] with len (= T) unchanged
-    r = select_tokens(e, e->hlast, H, B, slot0, (logits && !logits_all) ? logits : nullptr, next_ids, nullptr, nullptr, T, s);
-    if (r != GP_OK) return r;
+    float* want_lg = (logits && !logits_all) ? logits : nullptr;
+    const bool tc_ok = bf(e) && !(c.flags & GP_FLAG_NO_TCGEN05) && B > kGemvMaxBatch && e->logits_ws != nullptr &&
+                       B <= c.max_batch && gemm_tc_supported(B, e->V, H) && (int64_t)B <= (int64_t)c.max_tokens;
+    if (tc_ok) {
+      // many sequences: ln_f -> tcgen05 GEMM over the tied head -> per-row selection, instead of streaming the 77 MB
+      // head once per 8 rows
+      float* lg = want_lg ? want_lg : e->logits_ws;
+      int32_t* ids_dst = next_ids ? next_ids : e->mailbox;
+      LAUNCH(e, launch_layernorm(e->hlast, H, e->lnf_g, e->lnf_b, e->xa, true, B, H, c.ln_eps, s));
+      LAUNCH(e, gemm(e, e->xa, H, e->wte, nullptr, nullptr, 0, lg, e->V, B, e->V, H, 0u, s));
+      if (e->sampler_on)
+        LAUNCH(e, launch_sample_topk(lg, e->V, B, e->V, e->sampler_temperature, e->sampler_top_k, e->sampler_seed, slot0, T, ids_dst,
+                                     nullptr, slot0, nullptr, e->seq_stride, s));
+      else
+        LAUNCH(e, launch_argmax_rows(lg, e->V, B, e->V, ids_dst, nullptr, slot0, nullptr, e->seq_stride, s));
+    } else {
+      // generate: the first new token goes to seq[b][len] with len (= T) unchanged
+      r = select_tokens(e, e->hlast, H, B, slot0, want_lg, next_ids, nullptr, nullptr, T, s);
+      if (r != GP_OK) return r;
+    }
   }
   return GP_OK;
 }

@@ -38,7 +38,7 @@ template <int BM> struct Cfg {
   static constexpr int kStages = (BM <= 32) ? 8 : (BM <= 128 ? 6 : 4);
   static constexpr int kAccCols = BM < 32 ? 32 : BM;   // TMEM columns of one accumulator stage
   static constexpr int kTmemCols = 2 * kAccCols;       // two stages: epilogue of tile i overlaps main loop of tile i+1
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiWarps * 1024 /*epilogue transpose*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiWarps * 2048 /*epilogue transpose*/;
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -145,7 +145,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
   uint64_t* tfull = empty + C::kStages;     // [2] accumulator stage complete (MMA -> epilogue)
   uint64_t* tempty = tfull + 2;             // [2] accumulator stage drained  (epilogue -> MMA)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  uint8_t* epi_stage = smem + C::kStages * C::kStageBytes + 256;   // [kEpiWarps][1 KB]: 16 rows x 32 columns of bf16 per warp
+  uint8_t* epi_stage = smem + C::kStages * C::kStageBytes + 256;   // [kEpiWarps][2 KB]: 16 rows x 32 columns (bf16 or fp32) per warp
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + kBlockN - 1) / kBlockN;
@@ -249,29 +249,51 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
       const float bv = (!split && bias != nullptr && n_ok) ? bias[n] : 0.f;
       float* pz = split ? partial + (size_t)z * M * N : nullptr;
       const uint32_t tcol = tmem_base + as * C::kAccCols + ((uint32_t)(q * 32) << 16);
-      // bf16 output, whole 16 x 32 chunk inside the matrix: transpose through shared memory so that every lane
-      // writes two 16-byte vectors (8 consecutive columns of one row) instead of sixteen 2-byte values
-      const bool vec_ok = sizeof(OT) == 2 && !split && (n0 + q * 32 + 32 <= N) && (ldo % 8 == 0);
-      uint8_t* my_stage = epi_stage + (warp - 2) * 1024;
+      // Whole 16 x 32 chunk inside the matrix: transpose through shared memory so that every lane moves 16-byte vectors
+      // (8 bf16 / 4 fp32 consecutive columns of one row) instead of sixteen scalar values; the fp32 residual is added on
+      // the vector side.
+      const bool vec_ok = !split && (n0 + q * 32 + 32 <= N) && (ldo % 8 == 0) && (residual == nullptr || ldr % 4 == 0);
+      uint8_t* my_stage = epi_stage + (warp - 2) * 2048;
 #pragma unroll 1
       for (int c0 = chunk0 * 16; c0 < BM; c0 += 32) {
         if (m0 + c0 >= M) break;  // warp-uniform
         uint32_t r[16];
         tc_ld16(tcol + (uint32_t)c0, r);
         if (vec_ok && m0 + c0 + 16 <= M) {
+          if (sizeof(OT) == 2) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float v = __uint_as_float(r[j]) + bv;
-            if (gelu) v = gelu_epi<OT>(v);
-            if (residual != nullptr) v += residual[(size_t)(m0 + c0 + j) * ldr + n];
-            reinterpret_cast<bf16*>(my_stage)[j * 32 + lane] = __float2bfloat16_rn(v);
-          }
-          __syncwarp();
+            for (int j = 0; j < 16; ++j) {
+              float v = __uint_as_float(r[j]) + bv;
+              if (gelu) v = gelu_epi<OT>(v);
+              if (residual != nullptr) v += residual[(size_t)(m0 + c0 + j) * ldr + n];
+              reinterpret_cast<bf16*>(my_stage)[j * 32 + lane] = __float2bfloat16_rn(v);
+            }
+            __syncwarp();
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            const int c = lane + i * 32, row = c >> 2, col = (c & 3) * 8;
-            const uint4 vv = *reinterpret_cast<const uint4*>(my_stage + row * 64 + col * 2);
-            *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(out) + (size_t)(m0 + c0 + row) * ldo + n0 + q * 32 + col) = vv;
+            for (int i = 0; i < 2; ++i) {
+              const int c = lane + i * 32, row = c >> 2, col = (c & 3) * 8;
+              const uint4 vv = *reinterpret_cast<const uint4*>(my_stage + row * 64 + col * 2);
+              *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(out) + (size_t)(m0 + c0 + row) * ldo + n0 + q * 32 + col) = vv;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              float v = __uint_as_float(r[j]) + bv;
+              if (gelu) v = gelu_epi<OT>(v);
+              reinterpret_cast<float*>(my_stage)[j * 32 + lane] = v;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int c = lane + i * 32, row = c >> 3, col = (c & 7) * 4;
+              float4 vv = *reinterpret_cast<const float4*>(my_stage + row * 128 + col * 4);
+              const size_t m = (size_t)(m0 + c0 + row);
+              if (residual != nullptr) {
+                const float4 rr = *reinterpret_cast<const float4*>(residual + m * ldr + n0 + q * 32 + col);
+                vv.x += rr.x; vv.y += rr.y; vv.z += rr.z; vv.w += rr.w;
+              }
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + m * ldo + n0 + q * 32 + col) = vv;
+            }
           }
           __syncwarp();
           continue;
