@@ -328,6 +328,11 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
     p.slot_map = pipe.slot_indexed ? e->slot_map : nullptr;
     p.abort_flag = e->ctrl; p.progress = reinterpret_cast<unsigned int*>(e->ctrl + 1);
     p.ll_shift = kLLShiftMax;
+    {  // the host mirror of the cache lengths bounds the contexts of this launch (callers may already have advanced it)
+      int longest = 0;
+      for (int32_t v : e->hlens) longest = v > longest ? v : longest;
+      p.ctx_hint = longest + n_steps < c.max_ctx ? longest + n_steps : c.max_ctx;
+    }
     if (const char* env = getenv("GP_MEGA_LLSHIFT")) { int v = atoi(env); if (v >= 2 && v <= kLLShiftMax) p.ll_shift = v; }
     CK(e, cudaMemsetAsync(e->ctrl, 0, 2 * sizeof(int), s));
     cudaError_t le = launch_decode_mega2(p, e->num_sms, s);
@@ -664,11 +669,13 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
     // most 8 sequences over L2 slices (one 32-byte sector per (4 << (shift - 2)) words, k_mega2.cu ll_off)
     auto ll_bytes = [&](size_t width) {
       const size_t dense = MB * width * 8;
-      const size_t rows = MB < 8 ? MB : 8;
+      const size_t rows = 8;   // the kernel addresses up to 8 sequences (and the attention partials behind 8 rows) whatever max_batch is
       const size_t spread = cfg->dtype == GP_BF16 ? ((rows * width + 3) / 4 << kLLShiftMax) * 8 + 64 : 0;
       return dense > spread ? dense : spread;
     };
-    e->ll_bytes[0] = ll_bytes(3 * H); e->ll_bytes[1] = ll_bytes(H); e->ll_bytes[2] = ll_bytes(H); e->ll_bytes[3] = ll_bytes(F);
+    e->ll_bytes[0] = ll_bytes(3 * H);
+    e->ll_bytes[1] = ll_bytes(H + (size_t)e->nh * 4 * 72);   // + the partials of split attention tasks (k_mega2.cu: kMaxSplit x kPartStride per head)
+    e->ll_bytes[2] = ll_bytes(H); e->ll_bytes[3] = ll_bytes(F);
     e->ll_bytes[4] = ll_bytes(H);
     TRY(alloc((void**)&e->qkv_ll, e->ll_bytes[0])); TRYCK(cudaMemsetAsync(e->qkv_ll, 0, e->ll_bytes[0], e->stream));
     TRY(alloc((void**)&e->attn_ll, e->ll_bytes[1])); TRYCK(cudaMemsetAsync(e->attn_ll, 0, e->ll_bytes[1], e->stream));

@@ -49,6 +49,9 @@ constexpr int kLnPairs = 2;                // LayerNorm: element pairs per threa
 constexpr int kFlagStride = 256;
 constexpr int kD = 64;                     // head dimension
 constexpr int kVPre = 3;                   // P.V iterations (4 keys each) of a warp prefetched before q arrives: contexts up to 180
+constexpr int kMaxSplit = 4;                // CTAs that may share one (sequence, head) attention task at long contexts
+constexpr int kPartStride = 72;            // exchange words of one attention partial: 64 outputs, (max, sum) at 64, 65
+constexpr int kSplitMinCtx = 256;          // contexts shorter than this are never split
 constexpr int kSpinCheck = 255;            // spin loops look at the abort word every 256 polls
 
 enum { K_QKV = 0, K_ATTN = 1, K_PROJ = 2, K_FC = 3, K_PROJ2 = 4, K_HEAD = 5 };
@@ -597,7 +600,7 @@ __device__ __forceinline__ void run_rows(Ctx<TR>& cx, const PhaseOut& po, const 
 }
 
 struct AttnArgs {
-  bf16 *kc, *vc; const u64* qkv_ll; u64* attn_ll; uint32_t ep_qkv, ep_attn;
+  bf16 *kc, *vc; const u64* qkv_ll; u64* attn_ll; uint32_t ep_qkv, ep_attn; size_t part_base;
   int nh, max_ctx; float *part, *pm, *pl, *q_s; uint32_t* kv_s;   // kv_s: new K row then new V row, packed bf16 (2 x 32 words)
 };
 
@@ -607,17 +610,20 @@ struct AttnArgs {
 // the first kVPre V values of the warp's keys are in registers before q is waited for.  Per warp: scores -> warp
 // max -> weights -> P.V over the warp's keys (weights broadcast by shuffle, V rows read coalesced, lane = output
 // dimensions 2 lane, 2 lane + 1), online across rounds; the 15 (max, sum, acc) partials merge through shared memory.
-template <bool TR>
-__device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, int b, int head, int slot) {
+template <bool TR, bool SP>
+__device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, int b, int head, int slot, int split, int n_split) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int H = cx.H;
   const size_t base = ((size_t)slot * a.nh + head) * (size_t)a.max_ctx * kD;
   bf16* Kc = a.kc + base;
   bf16* Vc = a.vc + base;
   const int pos = cx.s_pos[b];                      // the new token's position = number of cached rows
-  const int j0 = lane * kNW + warp;                 // my key of round 0
+  // keys [k_begin, k_end) of the pos + 1 this task sees (all of them unless the task is split over several CTAs)
+  const int chunk = SP ? (pos + n_split) / n_split : pos + 1;      // ceil((pos + 1) / n_split)
+  const int k_begin = SP ? split * chunk : 0, k_end = SP ? min(pos + 1, k_begin + chunk) : pos + 1;
+  const int j0 = k_begin + lane * kNW + warp;       // my key of round 0
   uint4 kr[8];
-  if (j0 < pos) {
+  if (j0 < min(pos, k_end)) {
     const uint4* src = reinterpret_cast<const uint4*>(Kc + (size_t)j0 * kD);
 #pragma unroll
     for (int i = 0; i < 8; ++i) kr[i] = src[i];
@@ -628,8 +634,8 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
   uint4 vq[kVPre];
 #pragma unroll
   for (int it = 0; it < kVPre; ++it) {
-    const int jj = warp + (it * 4 + sub) * kNW;
-    vq[it] = (jj < pos) ? *reinterpret_cast<const uint4*>(Vc + (size_t)jj * kD + dg * 8) : make_uint4(0, 0, 0, 0);
+    const int jj = k_begin + warp + (it * 4 + sub) * kNW;
+    vq[it] = (jj < min(pos, k_end)) ? *reinterpret_cast<const uint4*>(Vc + (size_t)jj * kD + dg * 8) : make_uint4(0, 0, 0, 0);
   }
   consumer_sync();          // the previous user of the scratch area (red) is done
   cx.stamp(K_ATTN * 16 + 0);
@@ -641,7 +647,7 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
       a.q_s[i] = val * 0.125f;                      // 64^-0.5
     } else {
       const bf16 r = __float2bfloat16_rn(val);      // the new row joins the cache storage-rounded like every row
-      if (pos < a.max_ctx) (which == 1 ? Kc : Vc)[(size_t)pos * kD + i] = r;
+      if (pos < a.max_ctx && pos >= k_begin && pos < k_end) (which == 1 ? Kc : Vc)[(size_t)pos * kD + i] = r;   // the split that owns the new key stores it
       reinterpret_cast<bf16*>(a.kv_s)[(which - 1) * kD + i] = r;
     }
   }
@@ -651,18 +657,18 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
   const uint4 vnew = reinterpret_cast<const uint4*>(a.kv_s)[8 + dg];   // dimensions [8 dg, 8 dg + 8) of the new V row
-  for (int rnd = 0; rnd * kConsumers <= ((cx.ablate & 4) ? -1 : pos); ++rnd) {
+  for (int rnd = 0; k_begin + rnd * kConsumers < ((cx.ablate & 4) ? 0 : k_end); ++rnd) {
     const int j = rnd * kConsumers + j0;
     if (j == pos) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) kr[i] = reinterpret_cast<const uint4*>(a.kv_s)[i];
-    } else if (rnd > 0 && j < pos) {
+    } else if (rnd > 0 && j < k_end) {
       const uint4* src = reinterpret_cast<const uint4*>(Kc + (size_t)j * kD);
 #pragma unroll
       for (int i = 0; i < 8; ++i) kr[i] = src[i];
     }
     float sc = -INFINITY;
-    if (j <= pos) {
+    if (j < k_end) {
       float d0 = 0.f, d1 = 0.f;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -676,15 +682,15 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
       sc = d0 + d1;
     }
     // keys of this warp in this round: lane slots [0, nl)
-    const int first = rnd * kConsumers + warp;      // lane slot 0's key
-    const int nl = (first <= pos) ? min(32, (pos - first) / kNW + 1) : 0;
+    const int first = k_begin + rnd * kConsumers + warp;      // lane slot 0's key
+    const int nl = (first < k_end) ? min(32, (k_end - 1 - first) / kNW + 1) : 0;
     if (nl > 0) {
       float mx = sc;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(FULL_MASK, mx, o));
       const float m_new = fmaxf(m_run, mx);
       const float scale = __expf(m_run - m_new);    // 0 on the first round (m_run = -inf)
-      const float pme = (j <= pos) ? __expf(sc - m_new) : 0.f;
+      const float pme = (j < k_end) ? __expf(sc - m_new) : 0.f;
       l_run *= scale;
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i] *= scale;
@@ -713,7 +719,7 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const int jj = first + ((i0 + u) * 4 + sub) * kNW;
-          vv[u] = (i0 + u < n_it && jj < pos) ? *reinterpret_cast<const uint4*>(Vc + (size_t)jj * kD + dg * 8) : make_uint4(0, 0, 0, 0);
+          vv[u] = (i0 + u < n_it && jj < min(pos, k_end)) ? *reinterpret_cast<const uint4*>(Vc + (size_t)jj * kD + dg * 8) : make_uint4(0, 0, 0, 0);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u)
@@ -750,11 +756,83 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
     float o = 0.f;
 #pragma unroll
     for (int ww = 0; ww < kNW; ++ww) o = fmaf(a.part[ww * kD + tid], __shfl_sync(FULL_MASK, cw, ww), o);
-    ll_store(a.attn_ll + ll_off((size_t)b * H + head * kD + tid, cx.ll_shift), __float_as_uint(o / Lsum), a.ep_attn);
+    if (!SP || n_split == 1) {
+      ll_store(a.attn_ll + ll_off((size_t)b * H + head * kD + tid, cx.ll_shift), __float_as_uint(o / Lsum), a.ep_attn);
+    } else {
+      // unnormalised partial of this key range: 64 outputs + (max, sum); the consumers of the c_proj phase merge them
+      u64* pp = a.attn_ll + ll_off(a.part_base + ((size_t)(b * a.nh + head) * kMaxSplit + split) * kPartStride, cx.ll_shift);
+      const size_t pbase = a.part_base + ((size_t)(b * a.nh + head) * kMaxSplit + split) * kPartStride;
+      (void)pp;
+      ll_store(a.attn_ll + ll_off(pbase + tid, cx.ll_shift), __float_as_uint(o), a.ep_attn);
+      if (tid == 0) ll_store(a.attn_ll + ll_off(pbase + 64, cx.ll_shift), __float_as_uint(M), a.ep_attn);
+      if (tid == 1) ll_store(a.attn_ll + ll_off(pbase + 65, cx.ll_shift), __float_as_uint(Lsum), a.ep_attn);
+    }
   }
 }
 
-template <int BT, bool TR>
+// ---- staging of the attention c_proj phase when the tasks were split: element pair q of sequence b belongs to head
+// q / 32; its n_split partials (unnormalised outputs + (max, sum) per partial) are merged like the partials of the
+// warps inside a task: out = sum_s o_s e^(m_s - M) / sum_s l_s e^(m_s - M).
+// Kept out of line on purpose: inlined, its 16 outstanding 16-byte loads per thread changed the register allocation of
+// the whole phase loop (the kernel sits at the 128-register cap of 512 threads) and cost 15 % per token.  Scalar
+// arguments, not a struct: a by-value struct lives in local memory and every asm with a memory clobber re-reads it.
+__device__ __noinline__ void stage_attn_merge(const u64* attn_ll, size_t part_base, uint32_t epoch, int H, int nh, int n_split,
+                                              int B, int ll_shift, uint32_t xs_hi, uint32_t xs_lo, uint32_t xrow,
+                                              volatile int* s_abort, const int* g_abort) {
+  const int tid = threadIdx.x;
+  const int halfK = H >> 1;
+  for (int q = tid; q < halfK; q += kConsumers) {
+    const int head = q >> 5, i = (2 * q) & 63;
+#pragma unroll 1
+    for (int b = 0; b < B; ++b) {
+      const size_t pbase = part_base + ((size_t)(b * nh + head) * kMaxSplit) * kPartStride;
+      u64 oa[kMaxSplit], ob[kMaxSplit], ma[kMaxSplit], la[kMaxSplit];
+      unsigned spins = 0;
+      bool ok;
+      do {
+        ok = true;
+#pragma unroll
+        for (int sp = 0; sp < kMaxSplit; ++sp) {
+          const bool live = sp < n_split;
+          ll_load2_if(attn_ll + ll_off(pbase + (size_t)sp * kPartStride + i, ll_shift), live, false, oa[sp], ob[sp]);
+          ll_load2_if(attn_ll + ll_off(pbase + (size_t)sp * kPartStride + 64, ll_shift), live, false, ma[sp], la[sp]);
+          ok = ok && (!live || ((uint32_t)(oa[sp] >> 32) == epoch && (uint32_t)(ob[sp] >> 32) == epoch &&
+                                (uint32_t)(ma[sp] >> 32) == epoch && (uint32_t)(la[sp] >> 32) == epoch));
+        }
+        if (!ok) {   // the watchdog's abort word, as in Ctx::give_up
+          if (*s_abort) break;
+          if ((++spins & kSpinCheck) == 0 && g_abort != nullptr) {
+            int a;
+            asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(a) : "l"(g_abort) : "memory");
+            if (a) { *s_abort = 1; break; }
+          }
+        }
+      } while (!ok);
+      float M = -INFINITY;
+#pragma unroll
+      for (int sp = 0; sp < kMaxSplit; ++sp)
+        if (sp < n_split) M = fmaxf(M, __uint_as_float((uint32_t)ma[sp]));
+      float L = 0.f, o0 = 0.f, o1 = 0.f;
+#pragma unroll
+      for (int sp = 0; sp < kMaxSplit; ++sp)
+        if (sp < n_split) {
+          const float ms = __uint_as_float((uint32_t)ma[sp]);
+          const float wgt = (ms == -INFINITY) ? 0.f : __expf(ms - M);
+          L = fmaf(__uint_as_float((uint32_t)la[sp]), wgt, L);
+          o0 = fmaf(__uint_as_float((uint32_t)oa[sp]), wgt, o0);
+          o1 = fmaf(__uint_as_float((uint32_t)ob[sp]), wgt, o1);
+        }
+      const float inv = 1.f / L;
+      uint32_t hi, lo;
+      split_hi_lo(o0 * inv, o1 * inv, hi, lo);
+      sts32(xs_hi + b * xrow + 4 * q, hi);
+      if (xs_lo != 0) sts32(xs_lo + b * xrow + 4 * q, lo);
+    }
+  }
+}
+
+
+template <int BT, bool TR, bool SP>
 __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int G = gridDim.x, cta = blockIdx.x;
@@ -894,6 +972,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
       }
     }
     consumer_sync();
+    // long contexts with few (sequence, head) tasks: several CTAs share a task, each taking a range of the keys
+    int n_split = 1;
+    if constexpr (SP) {
+      int t_max = 0;
+      for (int bb = 0; bb < B; ++bb) t_max = max(t_max, s_pos[bb] + 1);
+      if (t_max >= p.split_min) n_split = max(1, min(min(kMaxSplit, G / (B * nh)), (t_max + p.split_keys - 1) / p.split_keys));
+    }
     // ---- the stage's input: every CTA produces the slice of the residual stream it owns (embedding rows on stage 0,
     // the words the previous stage wrote into the inbox, or the caller's buffer), keeps it in shared memory and
     // publishes it like a phase output, so the first phase stages its input exactly like every other phase
@@ -919,14 +1004,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
       const uint32_t ep_dst = ep_item + (uint32_t)ph + 1u;     // data produced by phase ph; phase ph consumes epoch ep_dst - 1
       const MegaLayer& w = s_layers[li];
       if (kind == K_ATTN) {
-        if (cta < B * nh) {
+        if (cta < B * nh * n_split) {
           AttnArgs a;
           a.kc = reinterpret_cast<bf16*>(w.kc); a.vc = reinterpret_cast<bf16*>(w.vc); a.qkv_ll = p.qkv_ll; a.attn_ll = p.attn_ll;
           a.ep_qkv = ep_dst - 1u; a.ep_attn = ep_dst; a.nh = nh; a.max_ctx = p.max_ctx;
-          a.part = at_part; a.pm = at_pm; a.pl = at_pl; a.q_s = at_q; a.kv_s = at_kv;
-          for (int task = cta; task < B * nh; task += G) {
-            const int b = task / nh, head = task - b * nh;
-            attention_task(cx, a, b, head, s_slot[strm * B + b]);
+          a.part = at_part; a.pm = at_pm; a.pl = at_pl; a.q_s = at_q; a.kv_s = at_kv; a.part_base = (size_t)8 * H;
+          for (int task = cta; task < B * nh * n_split; task += G) {
+            const int split = task / (B * nh), rest = task - split * (B * nh);
+            const int b = rest / nh, head = rest - b * nh;
+            attention_task<TR, SP>(cx, a, b, head, s_slot[strm * B + b], split, n_split);
           }
         }
         cx.stamp(K_ATTN * 16 + 3);
@@ -947,6 +1033,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
       if (ki.ln) {
         const float* g = (kind == K_QKV) ? w.ln1_g : (kind == K_FC) ? w.ln2_g : p.lnf_g;
         stage_ln<BT, TR>(cx, src, ep_dst - 1u, g, ki.K, kind * 16);
+      } else if (SP && kind == K_PROJ && n_split > 1) {
+        cx.stamp(kind * 16 + 0);
+        stage_attn_merge(p.attn_ll, (size_t)8 * H, ep_dst - 1u, H, nh, n_split, B, cx.ll_shift, cx.xs_hi, BT <= 4 ? cx.xs_lo : 0u,
+                         cx.xrow, cx.s_abort, cx.g_abort);
+        cx.stamp(kind * 16 + 1);
       } else {
         stage_copy<BT, TR>(cx, src, ep_dst - 1u, ki.K, ki.copy_items, kind * 16);
       }
@@ -1098,16 +1189,24 @@ int pick_slot(int BT, int H, int L, int* n_slots, int V = 50257, int G = 148) {
   return 0;
 }
 
+// SP (several CTAs per attention task at long contexts) is a separate instantiation: the kernel sits at the register
+// cap and the split code costs ~4 % per token at short contexts where it never runs.  Only for <= 4 sequences (8
+// sequences have at least 96 tasks).
+template <int BT, bool TR, bool SP> const void* kernel_ptr() { return (const void*)decode_mega2_kernel<BT, TR, (BT <= 4) && SP>; }
 template <int BT>
-cudaError_t launch2_t(const MegaParams& p, int grid, size_t smem, cudaStream_t s) {
+cudaError_t launch2_t(const MegaParams& p, bool split, int grid, size_t smem, cudaStream_t s) {
   void* args[] = {const_cast<MegaParams*>(&p)};
-  const void* fn = (p.trace != nullptr) ? (const void*)decode_mega2_kernel<BT, true> : (const void*)decode_mega2_kernel<BT, false>;
+  const void* fn = (p.trace != nullptr) ? (split ? kernel_ptr<BT, true, true>() : kernel_ptr<BT, true, false>())
+                                        : (split ? kernel_ptr<BT, false, true>() : kernel_ptr<BT, false, false>());
   return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, smem, s);
 }
 template <int BT> cudaError_t set_attr2() {
-  cudaError_t e = cudaFuncSetAttribute(decode_mega2_kernel<BT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(decode_mega2_kernel<BT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  return e;
+  const void* fns[4] = {kernel_ptr<BT, false, false>(), kernel_ptr<BT, true, false>(), kernel_ptr<BT, false, true>(), kernel_ptr<BT, true, true>()};
+  for (const void* fn : fns) {
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 }  // namespace
@@ -1145,8 +1244,8 @@ int mega2_max_coresident(int B, int H, int L) {
   if (data <= 0) return 0;
   const size_t smem = fixed_smem2(BT, H, L) + (size_t)n_slots * (data + (2 * kSlotWin));
   int per_sm = 0;
-  const void* fn = BT == 1 ? (const void*)decode_mega2_kernel<1, false> : BT == 2 ? (const void*)decode_mega2_kernel<2, false>
-                 : BT == 4 ? (const void*)decode_mega2_kernel<4, false> : (const void*)decode_mega2_kernel<8, false>;
+  const void* fn = BT == 1 ? kernel_ptr<1, false, true>() : BT == 2 ? kernel_ptr<2, false, true>()
+                 : BT == 4 ? kernel_ptr<4, false, true>() : kernel_ptr<8, false, false>();
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kThreads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
   return per_sm;
 }
@@ -1162,14 +1261,20 @@ cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s) {
   p.n_slots = n_slots;
   p.slot_data = data;
   if (const char* env = getenv("GP_MEGA_POLL_NS")) p.poll_ns = atoi(env);
+  p.split_min = kSplitMinCtx; p.split_keys = 128;
+  if (const char* env = getenv("GP_MEGA_SPLIT_MIN")) p.split_min = atoi(env);
+  if (const char* env = getenv("GP_MEGA_SPLIT_KEYS")) p.split_keys = atoi(env) > 0 ? atoi(env) : 128;
   if (const char* env = getenv("GP_MEGA_ABLATE")) p.ablate = atoi(env);   // timing experiments only: results are wrong
   const size_t smem = fixed_smem2(BT, p.H, p.L) + (size_t)n_slots * (data + (2 * kSlotWin));
   int grid = num_sms;
   if (const char* env = getenv("GP_MEGA_CTAS")) { int v = atoi(env); if (v >= p.B * p.nh && v >= 16 && v < num_sms) grid = v; }   // experiment: fewer participants
-  if (BT == 1) return launch2_t<1>(p, grid, smem, s);
-  if (BT == 2) return launch2_t<2>(p, grid, smem, s);
-  if (BT == 4) return launch2_t<4>(p, grid, smem, s);
-  return launch2_t<8>(p, grid, smem, s);
+  // a launch whose contexts can reach split_min, with CTAs to spare, takes the instantiation that can split tasks
+  const int ctx = p.ctx_hint > 0 ? p.ctx_hint : p.max_ctx;
+  const bool split = !(p.ablate & 8) && BT <= 4 && ctx >= p.split_min && grid >= 2 * p.B * p.nh;
+  if (BT == 1) return launch2_t<1>(p, split, grid, smem, s);
+  if (BT == 2) return launch2_t<2>(p, split, grid, smem, s);
+  if (BT == 4) return launch2_t<4>(p, split, grid, smem, s);
+  return launch2_t<8>(p, split, grid, smem, s);
 }
 
 }  // namespace gp

@@ -490,3 +490,38 @@ def test_pipeline_watchdog_aborts_a_stalled_stage_and_leaves_the_engine_usable(L
     assert torch.equal(a["logits"], b["logits"])
     x = torch.randn(1, dims.n_embd, generator=torch.Generator().manual_seed(2)).to(DEV)
     assert torch.equal(stage_b.decode(x, want_logits=True)["logits"], fresh.decode(x, want_logits=True)["logits"])
+
+
+@pytest.mark.parametrize("B", [1, 2])
+def test_long_context_decode_splits_attention_tasks(L, B):
+    """At contexts >= 256 with few (sequence, head) tasks several CTAs share a task (a key range each) and the c_proj
+    staging merges their partials.  124M, context 300..520: the cached decode must keep agreeing with a stateless
+    full-sequence pass (an independent code path) and with the per-op kernels, step by step."""
+    dims = O.PRESETS["gpt2"]
+    w = O.init_weights(dims, 1234, "hf")
+    pd = L.GPT2Dims(**dims.to_dict())
+    P, n_new = 300, 6
+    g = torch.Generator().manual_seed(11)
+    prompt = torch.randint(0, dims.vocab_size, (B, P), generator=g)
+    mega = L.StageEngine(pd, dtype=L.GP_BF16, max_batch=B, max_ctx=P + n_new + 250, max_tokens=B * (P + 256))
+    ops = L.StageEngine(pd, dtype=L.GP_BF16, max_batch=B, max_ctx=P + n_new + 250, max_tokens=B * (P + 256), flags=4)
+    for e in (mega, ops):
+        e.load_weights(w)
+    a, _ = run_prefill([mega], prompt)
+    b, _ = run_prefill([ops], prompt)
+    assert torch.equal(a["logits"], b["logits"])
+    tok = a["next_ids"].cpu()
+    for t in range(n_new):
+        a = run_decode([mega], tok)
+        b = run_decode([ops], tok)
+        assert float((a["logits"] - b["logits"]).abs().max()) <= 5e-3, t
+        tok = b["next_ids"].cpu()
+    # a second prompt length that puts the new key into a different split, through the whole-loop entry
+    P2 = 513
+    prompt2 = torch.randint(0, dims.vocab_size, (B, P2), generator=g, dtype=torch.int32)
+    out = mega.generate(prompt2, 8)
+    full = mega.prefill(out[:, :-1].to(DEV), use_cache=False, want_logits="all")["logits"][:, P2 - 1:]
+    top2 = torch.topk(full, 2, dim=-1)
+    firm = ((top2.values[..., 0] - top2.values[..., 1]) > 2 * TOL_BF16).cpu()
+    assert int(firm.sum()) >= 2
+    assert torch.equal(top2.indices[..., 0].cpu().to(torch.int32)[firm], out[:, P2:][firm])
