@@ -147,9 +147,11 @@ int gp_generate(gp_engine* e, const int32_t* prompt_ids_host, int32_t B, int32_t
  * a pure function of (seed, KV slot of the sequence, position of the new token) - Philox4x32-10,
  * key = seed, counter = (position, slot, 0, 0) - so a request is reproducible and independent of
  * batch composition.  Applies to gp_stage_prefill / gp_stage_decode / gp_generate on a stage with
- * the lm_head; sampled decode steps run the per-op kernels (the persistent kernel fuses the greedy
- * argmax), and gp_pipeline_decode refuses while the sampler is on.  temperature <= 0 or
- * top_k <= 0 restores greedy.  top_k <= 64. */
+ * the lm_head, and to gp_pipeline_decode on the last stage.  In bf16 storage the persistent decode
+ * kernel draws the token itself (CTA b selects for sequence b from the logits the kernel has just
+ * written, then publishes the token to the other CTAs / to stage 0); in fp32 storage sampled steps run
+ * the per-op kernels and gp_pipeline_decode answers GP_ESTATE while the sampler is on.
+ * temperature <= 0 or top_k <= 0 restores greedy.  top_k <= 64. */
 int gp_set_sampler(gp_engine* e, float temperature, int32_t top_k, uint64_t seed);
 
 /* ---- stage boundary on the device (replaces the HTTP/JSON hops of server.py:172-181).

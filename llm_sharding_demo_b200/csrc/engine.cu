@@ -235,8 +235,9 @@ bool use_mega2(const gp_engine* e, int B) {
   return !force_v1 && e->cfg.dtype == GP_BF16 && mega2_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms);
 }
 bool use_mega(const gp_engine* e, int B) {
-  // the persistent kernels fuse the greedy argmax; sampled decoding runs the per-op kernels
-  if (e->sampler_on || (e->cfg.flags & GP_FLAG_NO_MEGA) || !e->coop_ok) return false;
+  if ((e->cfg.flags & GP_FLAG_NO_MEGA) || !e->coop_ok) return false;
+  // the bf16 persistent kernel draws sampled tokens itself; the fp32 one fuses the greedy argmax only
+  if (e->sampler_on) return use_mega2(e, B) && (!e->cfg.has_head || e->logits_ws != nullptr);
   return use_mega2(e, B) || (e->L > 0 && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms));
 }
 
@@ -328,6 +329,11 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
     p.slot_map = pipe.slot_indexed ? e->slot_map : nullptr;
     p.abort_flag = e->ctrl; p.progress = reinterpret_cast<unsigned int*>(e->ctrl + 1);
     p.ll_shift = kLLShiftMax;
+    if (e->sampler_on && c.has_head) {
+      p.sampler_on = 1; p.sample_temperature = e->sampler_temperature; p.sample_top_k = e->sampler_top_k;
+      p.sample_seed_lo = (uint32_t)e->sampler_seed; p.sample_seed_hi = (uint32_t)(e->sampler_seed >> 32);
+      if (p.logits_out == nullptr) p.logits_out = e->logits_ws;   // the draw reads the logits back
+    }
     {  // the host mirror of the cache lengths bounds the contexts of this launch (callers may already have advanced it)
       int longest = 0;
       for (int32_t v : e->hlens) longest = v > longest ? v : longest;
@@ -1126,7 +1132,7 @@ int gp_pipeline_decode(gp_engine* e, const int32_t* first_ids, int32_t n_rounds,
   }
   if (!e->inbox || !e->peer_inbox) { set_err(e, "gp_pipeline_decode: stage boundary not connected (gp_comm_export / gp_comm_connect)"); return GP_ESTATE; }
   if (c.has_embed && (!first_ids || !tokens_out)) { set_err(e, "gp_pipeline_decode: stage 0 needs first_ids and tokens_out"); return GP_EINVAL; }
-  if (e->sampler_on) { set_err(e, "gp_pipeline_decode: the device-resident pipeline selects greedily; sampled decoding runs per step (gp_stage_decode)"); return GP_ESTATE; }
+  if (e->sampler_on && !use_mega2(e, B)) { set_err(e, "gp_pipeline_decode: sampled selection inside the device-resident pipeline needs bf16 storage (the fp32 kernel selects greedily); sample per step with gp_stage_decode"); return GP_ESTATE; }
   if (!use_mega(e, B)) { set_err(e, "gp_pipeline_decode: outside the persistent kernel's envelope (head_dim 64; B <= 8 in bf16 storage, <= 4 in fp32; cooperative launch available)"); return GP_EINVAL; }
   DeviceGuard dev_guard(c.device);
   CK(e, dev_guard.err);

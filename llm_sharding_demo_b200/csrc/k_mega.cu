@@ -1075,7 +1075,7 @@ bool mega_supported(int B, int H, int nh, int L, int dtype, int num_sms) {
 }
 
 uint32_t mega_epochs_per_launch(int L, int n_steps) { return (uint32_t)n_steps * (uint32_t)(L + 1) * 8u + 8u; }
-size_t mega_part_words() { return ((size_t)kGemvMaxBatch * 2 + 1) * kFlagStride; }   // + the counter row of k_mega2.cu
+size_t mega_part_words() { return ((size_t)kGemvMaxBatch * 2 + 2) * kFlagStride; }   // + the counter row and the sampled-token row of k_mega2.cu
 
 cudaError_t init_mega_attrs() {
   cudaError_t e;

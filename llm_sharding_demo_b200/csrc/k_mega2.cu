@@ -31,6 +31,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "sample.cuh"
 
 namespace gp {
 namespace {
@@ -1065,6 +1066,56 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
         ll_store(p.part_ll + ((size_t)tid * 2 + 1) * kFlagStride + cta, (uint32_t)r.i, ep_arg);
       }
       cx.stamp(7 * 16 + 2);
+      if (p.sampler_on) {
+        // ---- the reference's temperature / top-k / multinomial selection (k_sample.cu): CTA b draws for sequence b
+        // from the logits every CTA has just written (logits_out, read back through L2), then publishes the token.
+        // The counter in front of the logits: a CTA's stores, ordered by the barrier above, become visible with
+        // thread 0's fence before its increment.
+        float* lg = cx.logits_out;
+        u64* tok_ll = p.part_ll + (size_t)17 * kFlagStride;
+        if (tid == 0) { __threadfence(); red_add_u32(argmax_ctr, 1u); }
+        if (cta < B) {
+          const int b = cta;
+          consumer_sync();   // sbv is reused below
+          if (tid == 0) {
+            const uint32_t target = (uint32_t)s_misc[1] + (uint32_t)(item + 1) * (uint32_t)G;
+            unsigned spins = 0;
+            while ((int32_t)(ld_relaxed_u32(argmax_ctr) - target) < 0) {
+              if (cx.give_up(spins)) break;
+            }
+            __threadfence();
+          }
+          // a floor for the candidates: the top_k-th largest of the per-CTA maxima (each is a distinct logit)
+          if (tid < G) sbv[tid] = __uint_as_float(wait_word(cx, p.part_ll + ((size_t)b * 2 + 0) * kFlagStride + tid, ep_arg));
+          if (tid == 0) s_misc[2] = __float_as_int(-INFINITY);
+          consumer_sync();
+          const int kk = min(min(p.sample_top_k, kMaxTopK), p.V);
+          if (tid < G && kk <= G) {
+            const float v = sbv[tid];
+            int rank = 0;
+            for (int j = 0; j < G; ++j) {
+              const float vj = sbv[j];
+              rank += (vj > v || (vj == v && j < tid)) ? 1 : 0;
+            }
+            if (rank == kk - 1) s_misc[2] = __float_as_int(v);
+          }
+          consumer_sync();
+          const float floor_value = __int_as_float(s_misc[2]);
+          const int slot = s_slot[strm * B + b];
+          const int tok_raw = sample_row<kConsumers, true>(lg + (size_t)b * p.V, p.V, p.sample_temperature, p.sample_top_k, p.sample_seed_lo,
+                                                          p.sample_seed_hi, (uint32_t)(s_pos[b] + 1), (uint32_t)slot,
+                                                          reinterpret_cast<uint32_t*>(red), tid, floor_value);
+          if (tid == 0) {
+            const int tok = min(max(tok_raw, 0), p.V - 1);
+            p.ids_out[strm * B + b] = tok;
+            if (p.seq != nullptr) p.seq[(size_t)(strm * B + b) * p.seq_stride + s_pos[b] + 1] = tok;
+            if (p.peer_ids != nullptr) ll_store_sys(p.peer_ids + strm * B + b, (uint32_t)tok, cep);
+            ll_store(tok_ll + b, (uint32_t)tok, ep_arg);
+          }
+        }
+        // the next step embeds the token: every CTA of an embedding stage waits for it (one more exchange)
+        if (p.has_embed && tid < B) s_ids[tid] = (int)wait_word(cx, tok_ll + tid, ep_arg);
+      } else {
       // every CTA reduces all partials itself (index tie-break => deterministic).  One counter sits in front of the
       // data: 148 warps polling the 19 lines that 148 producers are still writing delayed those writes.
       if (warp == 0) {
@@ -1112,6 +1163,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
           s_ids[b] = tok;
         }
       }
+      }   // greedy
       cx.stamp(7 * 16 + 1);
     }
     // ---- bookkeeping: the cache grew by one position
@@ -1253,6 +1305,8 @@ int mega2_max_coresident(int B, int H, int L) {
 cudaError_t launch_decode_mega2(MegaParams p, int num_sms, cudaStream_t s) {
   if (!mega2_supported(p.B, p.H, p.nh, p.L, GP_BF16, num_sms) || p.n_steps < 1 || p.epoch0 == 0 || p.n_streams < 1 ||
       p.n_streams * p.B > 64)
+    return cudaErrorInvalidValue;
+  if (p.sampler_on && (p.logits_out == nullptr || !(p.sample_temperature > 0.f) || p.sample_top_k < 1 || p.sample_top_k > kMaxTopK))
     return cudaErrorInvalidValue;
   const int BT = padded2(p.B);
   int n_slots = 0;

@@ -109,6 +109,12 @@ class PipelineRunner:
             self.dist = None
             self.transport = "none"
 
+    def set_sampler(self, temperature: float = 0.0, top_k: int = 0, seed: int = 0):
+        """The reference coordinator's temperature / top-k / multinomial selection instead of greedy (engine.set_sampler);
+        it lives on the stage that carries the lm_head, the other stages have nothing to switch."""
+        if self.last:
+            self.engine.set_sampler(temperature, top_k, seed)
+
     # ---- small collectives for the bench harness
     def barrier(self):
         if self.dist is not None:

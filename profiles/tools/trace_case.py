@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """One generation of a given (model, B, P, n_new) on one GPU; with GP_MEGA_TRACE=<file> the persistent kernel dumps its
-per-CTA phase trace of the last decode step (read it with profiles/mega2_trace.py <file> <B * n_head>)."""
+per-CTA phase trace of the last decode step (read it with profiles/mega2_trace.py <file> <B * n_head>).
+GP_SAMPLE=1 switches the reference's sampler on (temperature 0.6, top-k 40)."""
 import os
 import sys
 
@@ -14,6 +15,8 @@ model, B, P, n_new = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.ar
 dims = L.PRESETS[model]
 eng = L.StageEngine(dims, dtype=L.GP_BF16, max_batch=B, max_ctx=P + n_new, max_tokens=B * P)
 eng.load_weights(L.init_weights(dims, 1234, "hf"))
+if os.environ.get("GP_SAMPLE"):
+    eng.set_sampler(0.6, 40, seed=1)
 prompts = synthetic_prompts(B, P, dims.vocab_size).pin_memory()
 for _ in range(2):
     out, tm = eng.generate(prompts, n_new, timings=True)

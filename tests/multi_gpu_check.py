@@ -10,7 +10,9 @@ On identical seeded weights, for N = 2, 4, 8 stages:
      stream 0 against the fixture captured from the reference's own routes (tests/golden/gpt2_124m.npz) and every
      stream against a stateless full-sequence pass on a single-stage engine (bench.ids_check).  Stages whose
      weights exceed 96 MB stream them with the L2 evict-first hint and the others do not (engine.cu), so both
-     branches run at N = 2.
+     branches run at N = 2;
+  D. the same pipeline with the reference's sampler on the last stage: reproducible, different from greedy, and
+     identical to a single-stage engine stepping each sequence alone in the same KV slot.
 Prints one MULTI_GPU_CHECK_OK line with the counts."""
 import os
 import sys
@@ -98,6 +100,38 @@ def main():
         print("C", chk, flush=True)
         assert chk["mismatch"] == 0 and chk["golden_checked"] >= 4 and chk["checked"] >= world * 4, chk
         counts["C"] = chk["checked"]
+    dist.barrier()
+
+    # ---- D: the same pipeline with the reference's sampler (temperature 0.6, top-k 40) on the last stage: the token is
+    # drawn inside the last stage's persistent kernel and travels to stage 0 like a greedy one.  A draw is a pure
+    # function of (logits, seed, KV slot, position), so a single-stage engine stepping each sequence alone in the same
+    # slot must produce the same ids.
+    runner.set_sampler(0.6, 40, seed=77)
+    sampled = runner.generate(prompts, n_new)
+    again = runner.generate(prompts, n_new)
+    if rank == 0:
+        assert torch.equal(sampled, again), "sampled pipeline run is not reproducible"
+        assert not torch.equal(sampled, out), "the sampler changed nothing"
+        solo = L.StageEngine(gd, dtype=L.GP_BF16, max_batch=world, max_ctx=P + n_new, max_tokens=P, device=local)
+        solo.load_weights(L.init_weights(gd, 1234, "hf"))
+        solo.set_sampler(0.6, 40, seed=77)
+        same = total = 0
+        for m in range(world):
+            o = solo.prefill(prompts[m:m + 1].to(solo.device), slot0=m, use_cache=True, want_ids=True)
+            toks = [o["next_ids"]]
+            for _ in range(n_new - 1):
+                toks.append(solo.decode(toks[-1], slot0=m)["next_ids"].clone())
+            want = torch.cat(toks).cpu()
+            got = sampled[m, P:]
+            n_same = 0
+            while n_same < n_new and int(want[n_same]) == int(got[n_same]):
+                n_same += 1
+            same += n_same
+            total += n_new
+        print("D sampled: common prefix", same, "of", total, flush=True)
+        assert same == total, (same, total)
+        counts["D"] = same
+        del solo
     dist.barrier()
     if rank == 0:
         print(f"MULTI_GPU_CHECK_OK world={world} tokens_checked={counts}", flush=True)

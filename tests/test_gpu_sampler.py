@@ -175,3 +175,50 @@ def test_pipeline_decode_refuses_while_sampling(L):
     eng = L.StageEngine(L.GPT2Dims(**dims.to_dict()), 0, 2, has_embed=True, has_head=False, dtype=L.GP_BF16)
     with pytest.raises(L.GPError):
         eng.set_sampler(0.6, 40, 0)                                # no lm_head on this stage
+
+
+@pytest.mark.parametrize("B", [1, 3])
+@pytest.mark.parametrize("preset,k", [("mini", 40), ("gpt2", 40), ("mini", 64), ("mini", 1)])
+def test_persistent_kernel_draws_what_the_oracle_draws_from_its_logits(L, B, preset, k):
+    """bf16 storage: sampled decode steps stay inside the persistent kernel (CTA b draws for sequence b).  Step by
+    step, the token must be the oracle's seeded draw from the very logits the kernel returns (same candidates, same
+    order, same Philox counter = (position, slot)), wherever the draw is not within 1e-4 of a CDF step (expf of
+    the two implementations differs in the last bit)."""
+    dims, w, eng = _engine(L, preset, L.GP_BF16, B)
+    eng.set_sampler(0.7, k, seed=99)
+    g = torch.Generator().manual_seed(B + k)
+    P = 7
+    prompt = torch.randint(0, dims.vocab_size, (B, P), generator=g, dtype=torch.int32)
+    out = eng.prefill(prompt.to("cuda"), use_cache=True, want_ids=True)
+    tok = out["next_ids"]
+    firm = 0
+    for t in range(12):
+        out = eng.decode(tok, want_logits=True)
+        lg = out["logits"].float().cpu()
+        got = out["next_ids"].cpu().tolist()
+        assert eng.last_launch_count() <= 3, eng.last_launch_count()   # one persistent launch, not ~100 per-op kernels
+        for b in range(B):
+            want, margin = O.sample_select(lg[b], 0.7, k, 99, b, P + t + 1)
+            if margin > 1e-4:
+                firm += 1
+                assert got[b] == want, (t, b, got[b], want, margin)
+        tok = out["next_ids"]
+    assert firm >= 8 * B
+
+
+def test_sampled_generate_in_one_launch_equals_stepping(L):
+    """gp_generate with the sampler on (127 steps in one launch, the token fed back through the exchange word) gives
+    the tokens of prefill + single decode steps: both draw from bit-identical logits."""
+    dims, w, eng = _engine(L, "mini", L.GP_BF16, 2)
+    eng.set_sampler(0.8, 40, seed=2024)
+    g = torch.Generator().manual_seed(3)
+    prompt = torch.randint(0, dims.vocab_size, (2, 9), generator=g, dtype=torch.int32)
+    whole = eng.generate(prompt, 20)
+    out = eng.prefill(prompt.to("cuda"), use_cache=True, want_ids=True)
+    toks = [out["next_ids"].cpu()]
+    for _ in range(19):
+        out = eng.decode(toks[-1].to("cuda"))
+        toks.append(out["next_ids"].cpu())
+    assert torch.equal(whole[:, 9:], torch.stack(toks, 1).to(whole.dtype))
+    eng.set_sampler(0.8, 40, seed=2025)
+    assert not torch.equal(whole, eng.generate(prompt, 20))
