@@ -14,7 +14,7 @@ ncu --set full --clock-control none --import-source on -k regex:decode_mega2 -s 
 # every stand-alone kernel at a realistic size, through the C ABI
 PCMD="python profiles/kernel_probe.py"
 $PCMD > gpurun_out/plain_probe_$TAG.log 2>&1 &&
-for K in lmhead_argmax_kernel gemv_kernel layernorm_warp_kernel attn_decode64_kernel attn_prefill64_kernel sample_topk_kernel gemm_tc_kernel; do
+for K in lmhead_argmax_kernel gemv_kernel layernorm_warp_kernel attn_decode64_kernel attn_prefill64_mma_kernel sample_topk_kernel gemm_tc_kernel; do
   ncu --set full --clock-control none --import-source on -k regex:$K -s 3 -c 1 \
       -o gpurun_out/prof_${K}_$TAG -f $PCMD > gpurun_out/ncu_${K}_$TAG.log 2>&1
 done
