@@ -644,7 +644,7 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
   }
   if (cfg->has_head) {
     TRY(alloc((void**)&e->lnf_g, H * 4)); TRY(alloc((void**)&e->lnf_b, H * 4));
-    if (cfg->dtype == GP_BF16) { TRY(alloc((void**)&e->lnf_u, V * 4)); TRY(alloc((void**)&e->lnf_c, V * 4)); }
+    if (cfg->dtype == GP_BF16) { TRY(alloc((void**)&e->lnf_u, V * 4 + 16)); TRY(alloc((void**)&e->lnf_c, V * 4 + 16));   /* + 16: the kernel copies 16-byte aligned windows of these */ }
     e->required.insert("ln_f.weight"); e->required.insert("ln_f.bias");
     TRY(alloc(&e->lm_scratch, (size_t)gp_lmhead_scratch_bytes(kGemvMaxBatch, e->V)));
     TRYCK(cudaMemsetAsync(e->lm_scratch, 0, kLmheadScratchHeader, e->stream));

@@ -56,15 +56,51 @@ __device__ __noinline__ int sample_row(const float* row, int V, float temperatur
   uint32_t* s_scan = misc + 4 + 4 * kMaxTopK;
   const int k = min(min(top_k, kMaxTopK), V);
 
+  if (!(floor_value > -INFINITY) && k <= NT && V >= 4 * NT) {
+    // no floor from the caller: the k-th largest of the NT per-thread maxima is one (they are distinct elements)
+    static_assert(NT <= kSampleScratchWords, "the per-thread maxima alias the front of the scratch area");
+    float* tmax = reinterpret_cast<float*>(scratch);      // [NT], before anything else uses the scratch area
+    float mx = -INFINITY;
+    for (int i = tid; i < V; i += NT) mx = fmaxf(mx, __ldcg(row + i));
+    tmax[tid] = mx;
+    sample_sync<NT, NAMED>();
+    int rank = 0;
+    for (int j = 0; j < NT; ++j) {
+      const float vj = tmax[j];
+      rank += (vj > mx || (vj == mx && j < tid)) ? 1 : 0;
+    }
+    sample_sync<NT, NAMED>();
+    if (rank == k - 1) misc[0] = __float_as_uint(mx);
+    sample_sync<NT, NAMED>();
+    floor_value = __uint_as_float(misc[0]);
+    sample_sync<NT, NAMED>();
+  }
   bool ranked = false;
   if (floor_value > -INFINITY) {
     if (tid == 0) misc[2] = 0;
     sample_sync<NT, NAMED>();
-    for (int i = tid; i < V; i += NT) {
-      const float v = __ldcg(row + i);
+    auto keep = [&](float v, int i) {
       if (v >= floor_value) {
         const uint32_t at = atomicAdd(&misc[2], 1u);
         if (at < (uint32_t)kSampleCand) { cand_v[at] = v; cand_i[at] = i; }
+      }
+    };
+    // 16-byte loads over the aligned middle of the row, four in flight per thread; scalars at both ends
+    const int head = (int)((4u - ((uint32_t)(reinterpret_cast<uintptr_t>(row) >> 2) & 3u)) & 3u);
+    const int n4 = (V - min(head, V)) >> 2;
+    const float4* row4 = reinterpret_cast<const float4*>(row + head);
+    if (tid < head && tid < V) keep(__ldcg(row + tid), tid);
+    for (int i = head + 4 * n4 + tid; i < V; i += NT) keep(__ldcg(row + i), i);
+    for (int i0 = tid; i0 < n4; i0 += 4 * NT) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = (i0 + u * NT < n4) ? __ldcg(row4 + i0 + u * NT) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = head + 4 * (i0 + u * NT);
+        if (v[u].x >= floor_value || v[u].y >= floor_value || v[u].z >= floor_value || v[u].w >= floor_value) {
+          keep(v[u].x, i); keep(v[u].y, i + 1); keep(v[u].z, i + 2); keep(v[u].w, i + 3);
+        }
       }
     }
     sample_sync<NT, NAMED>();
@@ -183,20 +219,22 @@ __device__ __noinline__ int sample_row(const float* row, int V, float temperatur
 
   }   // !ranked
 
-  // ---- softmax over the k scaled values and one inverse-CDF draw (sequential fp32 sums: the oracle's order)
+  // ---- softmax over the k scaled values and one inverse-CDF draw.  The k weights are computed in parallel; their sum
+  // and the scan stay sequential in fp32, candidate order - the oracle's arithmetic.
+  const float inv_t = 1.0f / temperature;
+  if (tid < k) cv[tid] = expf(sv[tid] * inv_t - sv[0] * inv_t);
+  sample_sync<NT, NAMED>();
   int id = 0;
   if (tid == 0) {
-    const float inv_t = 1.0f / temperature;
-    const float m = sv[0] * inv_t;
     float sum = 0.f;
-    for (int j = 0; j < k; ++j) sum += expf(sv[j] * inv_t - m);
+    for (int j = 0; j < k; ++j) sum += cv[j];
     const uint32_t x = philox_first(position, row_id, 0u, 0u, seed_lo, seed_hi);
     const float u = (float)(x >> 8) * (1.0f / 16777216.0f);
     const float target = u * sum;
     float acc = 0.f;
     int pick = k - 1;
     for (int j = 0; j < k; ++j) {
-      acc += expf(sv[j] * inv_t - m);
+      acc += cv[j];
       if (target < acc) { pick = j; break; }
     }
     id = si[pick];
