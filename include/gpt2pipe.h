@@ -41,6 +41,13 @@ extern "C" {
 #define GP_FLAG_NO_TCGEN05 1u /* route every GEMM through the SIMT tile kernel      */
 #define GP_FLAG_NO_GRAPH 2u   /* gp_generate launches kernels directly (no CUDA graph) */
 #define GP_FLAG_NO_MEGA 4u    /* decode with one kernel per op instead of the persistent kernel */
+/* Stage boundaries inside a block (finer load balance for S-stage pipelines; the reference cuts between blocks
+ * only, server.py:63-64).  A GPT-2 block is x += attn(ln_1 x); x += mlp(ln_2 x): the residual stream between the two
+ * halves is as good a hand-off as the one between blocks.  BEGIN_HALF: block layer_begin contributes only its MLP
+ * half (its attention half ran on the previous stage, which carries END_HALF); END_HALF: block layer_end - 1
+ * contributes only its attention half.  Such a stage loads only the weights of the halves it runs. */
+#define GP_FLAG_BEGIN_HALF 16u
+#define GP_FLAG_END_HALF 32u
 
 /* epilogue / behaviour bits of the op-level entry points */
 #define GP_EPI_GELU 1u   /* gelu_new (tanh form) after bias, before the residual add */

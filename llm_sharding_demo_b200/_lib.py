@@ -10,6 +10,7 @@ LIB_PATH = os.path.join(HERE, "libgpt2pipe.so")
 GP_OK = 0
 GP_F32, GP_BF16 = 0, 1
 GP_FLAG_NO_TCGEN05, GP_FLAG_NO_GRAPH, GP_FLAG_NO_MEGA = 1, 2, 4
+GP_FLAG_BEGIN_HALF, GP_FLAG_END_HALF = 16, 32
 GP_EPI_GELU, GP_OUT_BF16, GP_GEMM_SIMT = 1, 2, 4
 
 

@@ -229,6 +229,11 @@ int slot_room(gp_engine* e, const char* who, int slot0, int n, int steps) {
   return GP_OK;
 }
 
+// half-block stage boundaries (GP_FLAG_BEGIN_HALF / GP_FLAG_END_HALF): which halves of block li this stage runs
+bool has_attn_half(const gp_engine* e, int li) { return !(li == 0 && (e->cfg.flags & GP_FLAG_BEGIN_HALF)); }
+bool has_mlp_half(const gp_engine* e, int li) { return !(li == e->L - 1 && (e->cfg.flags & GP_FLAG_END_HALF)); }
+bool half_cut(const gp_engine* e) { return (e->cfg.flags & (GP_FLAG_BEGIN_HALF | GP_FLAG_END_HALF)) != 0; }
+
 // second-generation persistent kernel (k_mega2.cu): bf16 storage, up to 8 sequences, tensor-core rows
 bool use_mega2(const gp_engine* e, int B) {
   static const bool force_v1 = getenv("GP_MEGA_V1") != nullptr;
@@ -238,7 +243,7 @@ bool use_mega(const gp_engine* e, int B) {
   if ((e->cfg.flags & GP_FLAG_NO_MEGA) || !e->coop_ok) return false;
   // the bf16 persistent kernel draws sampled tokens itself; the fp32 one fuses the greedy argmax only
   if (e->sampler_on) return use_mega2(e, B) && (!e->cfg.has_head || e->logits_ws != nullptr);
-  return use_mega2(e, B) || (e->L > 0 && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms));
+  return use_mega2(e, B) || (e->L > 0 && !half_cut(e) && mega_supported(B, e->H, e->nh, e->L, e->cfg.dtype, e->num_sms));
 }
 
 int upload_mega_layers(gp_engine* e) {
@@ -248,8 +253,8 @@ int upload_mega_layers(gp_engine* e) {
     const int H = e->H;
     for (int i = 0; i < e->L; ++i) {
       const LayerW& w = e->layers[i];
-      CK(e, launch_ln_fold(w.attn_w, w.ln1_g, w.ln1_b, w.attn_b, w.attn_u, w.attn_c, 3 * H, H, e->stream));
-      CK(e, launch_ln_fold(w.fc_w, w.ln2_g, w.ln2_b, w.fc_b, w.fc_u, w.fc_c, e->F, H, e->stream));
+      if (has_attn_half(e, i)) CK(e, launch_ln_fold(w.attn_w, w.ln1_g, w.ln1_b, w.attn_b, w.attn_u, w.attn_c, 3 * H, H, e->stream));
+      if (has_mlp_half(e, i)) CK(e, launch_ln_fold(w.fc_w, w.ln2_g, w.ln2_b, w.fc_b, w.fc_u, w.fc_c, e->F, H, e->stream));
     }
     if (e->cfg.has_head) CK(e, launch_ln_fold(e->wte, e->lnf_g, e->lnf_b, nullptr, e->lnf_u, e->lnf_c, e->V, H, e->stream));
   }
@@ -329,6 +334,7 @@ int decode_mega(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
     p.slot_map = pipe.slot_indexed ? e->slot_map : nullptr;
     p.abort_flag = e->ctrl; p.progress = reinterpret_cast<unsigned int*>(e->ctrl + 1);
     p.ll_shift = kLLShiftMax;
+    p.begin_half = (c.flags & GP_FLAG_BEGIN_HALF) ? 1 : 0; p.end_half = (c.flags & GP_FLAG_END_HALF) ? 1 : 0;
     if (e->sampler_on && c.has_head) {
       p.sampler_on = 1; p.sample_temperature = e->sampler_temperature; p.sample_top_k = e->sampler_top_k;
       p.sample_seed_lo = (uint32_t)e->sampler_seed; p.sample_seed_hi = (uint32_t)(e->sampler_seed >> 32);
@@ -402,14 +408,18 @@ int prefill_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B
   }
   for (int li = 0; li < e->L; ++li) {
     LayerW& w = e->layers[li];
-    LAUNCH(e, launch_layernorm(e->h, H, w.ln1_g, w.ln1_b, e->xa, obf, M, H, c.ln_eps, s));
-    LAUNCH(e, gemm(e, e->xa, H, w.attn_w, w.attn_b, nullptr, 0, e->qkv, 3 * H, M, 3 * H, H, oflag, s));
-    if (use_cache) LAUNCH(e, launch_kv_scatter(e->qkv, w.kc, w.vc, B, T, slot0, H, e->nh, e->d, c.max_ctx, c.dtype, s));
-    LAUNCH(e, launch_attn_prefill(e->qkv, e->xa, B, T, e->nh, e->d, c.dtype, s));
-    LAUNCH(e, gemm(e, e->xa, H, w.proj_w, w.proj_b, e->h, H, e->h, H, M, H, H, 0u, s));
-    LAUNCH(e, launch_layernorm(e->h, H, w.ln2_g, w.ln2_b, e->xa, obf, M, H, c.ln_eps, s));
-    LAUNCH(e, gemm(e, e->xa, H, w.fc_w, w.fc_b, nullptr, 0, e->act, F, M, F, H, oflag | GP_EPI_GELU, s));
-    LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, e->h, H, e->h, H, M, H, F, 0u, s));
+    if (has_attn_half(e, li)) {
+      LAUNCH(e, launch_layernorm(e->h, H, w.ln1_g, w.ln1_b, e->xa, obf, M, H, c.ln_eps, s));
+      LAUNCH(e, gemm(e, e->xa, H, w.attn_w, w.attn_b, nullptr, 0, e->qkv, 3 * H, M, 3 * H, H, oflag, s));
+      if (use_cache) LAUNCH(e, launch_kv_scatter(e->qkv, w.kc, w.vc, B, T, slot0, H, e->nh, e->d, c.max_ctx, c.dtype, s));
+      LAUNCH(e, launch_attn_prefill(e->qkv, e->xa, B, T, e->nh, e->d, c.dtype, s));
+      LAUNCH(e, gemm(e, e->xa, H, w.proj_w, w.proj_b, e->h, H, e->h, H, M, H, H, 0u, s));
+    }
+    if (has_mlp_half(e, li)) {
+      LAUNCH(e, launch_layernorm(e->h, H, w.ln2_g, w.ln2_b, e->xa, obf, M, H, c.ln_eps, s));
+      LAUNCH(e, gemm(e, e->xa, H, w.fc_w, w.fc_b, nullptr, 0, e->act, F, M, F, H, oflag | GP_EPI_GELU, s));
+      LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, e->h, H, e->h, H, M, H, F, 0u, s));
+    }
   }
   if (use_cache) LAUNCH(e, launch_set_lens(e->lens, slot0, B, T, 0, s));
   if (!c.has_head) {
@@ -485,42 +495,54 @@ int decode_impl(gp_engine* e, const int32_t* ids, const float* hidden_in, int B,
   for (int li = 0; li < e->L; ++li) {
     LayerW& w = e->layers[li];
     const bool last = (li == e->L - 1);
-    float* dst = (last && !c.has_head) ? hidden_out : e->h;
+    const bool attn_half = has_attn_half(e, li), mlp_half = has_mlp_half(e, li);
+    float* dst = (last && !c.has_head) ? hidden_out : e->h;          // where the stage's last residual add writes
+    float* attn_dst = mlp_half ? e->h : dst;                          // the attention residual is the output of a cut block
     if (use_gemv) {
-      GemvParams p;
-      // ln_1 + c_attn, q -> e->q, k/v -> cache[pos = len]
-      p.x = cur; p.ldx = H; p.Wt = w.attn_w; p.bias = w.attn_b; p.B = B; p.N = 3 * H; p.K = H;
-      p.ln_g = w.ln1_g; p.ln_b = w.ln1_b; p.eps = c.ln_eps; p.mode = 1; p.q_out = e->q; p.kcache = w.kc;
-      p.vcache = w.vc; p.lens = e->lens; p.slot0 = slot0; p.H = H; p.nh = e->nh; p.d = e->d; p.max_ctx = c.max_ctx;
-      LAUNCH(e, launch_gemv(p, c.dtype, s));
-      LAUNCH(e, launch_attn_decode(e->q, w.kc, w.vc, e->lens, 1, slot0, e->attn_f, false, B, e->nh, e->d, c.max_ctx, c.dtype, s));
-      // attention c_proj + residual
-      GemvParams p2;
-      p2.x = e->attn_f; p2.ldx = H; p2.Wt = w.proj_w; p2.bias = w.proj_b; p2.residual = cur; p2.ldr = H;
-      p2.out = e->h; p2.ldo = H; p2.B = B; p2.N = H; p2.K = H;
-      LAUNCH(e, launch_gemv(p2, c.dtype, s));
-      cur = e->h;
-      // ln_2 + c_fc + gelu_new
-      GemvParams p3;
-      p3.x = e->h; p3.ldx = H; p3.Wt = w.fc_w; p3.bias = w.fc_b; p3.out = e->act_f; p3.ldo = F; p3.B = B; p3.N = F;
-      p3.K = H; p3.ln_g = w.ln2_g; p3.ln_b = w.ln2_b; p3.eps = c.ln_eps; p3.flags = GP_EPI_GELU;
-      LAUNCH(e, launch_gemv(p3, c.dtype, s));
-      // mlp c_proj + residual
-      GemvParams p4;
-      p4.x = e->act_f; p4.ldx = F; p4.Wt = w.mproj_w; p4.bias = w.mproj_b; p4.residual = e->h; p4.ldr = H;
-      p4.out = dst; p4.ldo = H; p4.B = B; p4.N = H; p4.K = F;
-      LAUNCH(e, launch_gemv(p4, c.dtype, s));
+      if (attn_half) {
+        GemvParams p;
+        // ln_1 + c_attn, q -> e->q, k/v -> cache[pos = len]
+        p.x = cur; p.ldx = H; p.Wt = w.attn_w; p.bias = w.attn_b; p.B = B; p.N = 3 * H; p.K = H;
+        p.ln_g = w.ln1_g; p.ln_b = w.ln1_b; p.eps = c.ln_eps; p.mode = 1; p.q_out = e->q; p.kcache = w.kc;
+        p.vcache = w.vc; p.lens = e->lens; p.slot0 = slot0; p.H = H; p.nh = e->nh; p.d = e->d; p.max_ctx = c.max_ctx;
+        LAUNCH(e, launch_gemv(p, c.dtype, s));
+        LAUNCH(e, launch_attn_decode(e->q, w.kc, w.vc, e->lens, 1, slot0, e->attn_f, false, B, e->nh, e->d, c.max_ctx, c.dtype, s));
+        // attention c_proj + residual
+        GemvParams p2;
+        p2.x = e->attn_f; p2.ldx = H; p2.Wt = w.proj_w; p2.bias = w.proj_b; p2.residual = cur; p2.ldr = H;
+        p2.out = attn_dst; p2.ldo = H; p2.B = B; p2.N = H; p2.K = H;
+        LAUNCH(e, launch_gemv(p2, c.dtype, s));
+        cur = attn_dst;
+      }
+      if (mlp_half) {
+        // ln_2 + c_fc + gelu_new
+        GemvParams p3;
+        p3.x = cur; p3.ldx = H; p3.Wt = w.fc_w; p3.bias = w.fc_b; p3.out = e->act_f; p3.ldo = F; p3.B = B; p3.N = F;
+        p3.K = H; p3.ln_g = w.ln2_g; p3.ln_b = w.ln2_b; p3.eps = c.ln_eps; p3.flags = GP_EPI_GELU;
+        LAUNCH(e, launch_gemv(p3, c.dtype, s));
+        // mlp c_proj + residual
+        GemvParams p4;
+        p4.x = e->act_f; p4.ldx = F; p4.Wt = w.mproj_w; p4.bias = w.mproj_b; p4.residual = cur; p4.ldr = H;
+        p4.out = dst; p4.ldo = H; p4.B = B; p4.N = H; p4.K = F;
+        LAUNCH(e, launch_gemv(p4, c.dtype, s));
+        cur = dst;
+      }
     } else {
       if (B > c.max_tokens) { set_err(e, "decode: B=%d exceeds max_tokens=%d", B, c.max_tokens); return GP_EINVAL; }
-      LAUNCH(e, launch_layernorm(cur, H, w.ln1_g, w.ln1_b, e->xa, obf, B, H, c.ln_eps, s));
-      LAUNCH(e, gemm(e, e->xa, H, w.attn_w, w.attn_b, nullptr, 0, e->qkv, 3 * H, B, 3 * H, H, oflag, s));
-      LAUNCH(e, launch_qkv_split_decode(e->qkv, e->q, w.kc, w.vc, e->lens, B, slot0, H, e->nh, e->d, c.max_ctx, c.dtype, s));
-      LAUNCH(e, launch_attn_decode(e->q, w.kc, w.vc, e->lens, 1, slot0, e->xa, obf, B, e->nh, e->d, c.max_ctx, c.dtype, s));
-      LAUNCH(e, gemm(e, e->xa, H, w.proj_w, w.proj_b, cur, H, e->h, H, B, H, H, 0u, s));
-      cur = e->h;
-      LAUNCH(e, launch_layernorm(e->h, H, w.ln2_g, w.ln2_b, e->xa, obf, B, H, c.ln_eps, s));
-      LAUNCH(e, gemm(e, e->xa, H, w.fc_w, w.fc_b, nullptr, 0, e->act, F, B, F, H, oflag | GP_EPI_GELU, s));
-      LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, e->h, H, dst, H, B, H, F, 0u, s));
+      if (attn_half) {
+        LAUNCH(e, launch_layernorm(cur, H, w.ln1_g, w.ln1_b, e->xa, obf, B, H, c.ln_eps, s));
+        LAUNCH(e, gemm(e, e->xa, H, w.attn_w, w.attn_b, nullptr, 0, e->qkv, 3 * H, B, 3 * H, H, oflag, s));
+        LAUNCH(e, launch_qkv_split_decode(e->qkv, e->q, w.kc, w.vc, e->lens, B, slot0, H, e->nh, e->d, c.max_ctx, c.dtype, s));
+        LAUNCH(e, launch_attn_decode(e->q, w.kc, w.vc, e->lens, 1, slot0, e->xa, obf, B, e->nh, e->d, c.max_ctx, c.dtype, s));
+        LAUNCH(e, gemm(e, e->xa, H, w.proj_w, w.proj_b, cur, H, attn_dst, H, B, H, H, 0u, s));
+        cur = attn_dst;
+      }
+      if (mlp_half) {
+        LAUNCH(e, launch_layernorm(cur, H, w.ln2_g, w.ln2_b, e->xa, obf, B, H, c.ln_eps, s));
+        LAUNCH(e, gemm(e, e->xa, H, w.fc_w, w.fc_b, nullptr, 0, e->act, F, B, F, H, oflag | GP_EPI_GELU, s));
+        LAUNCH(e, gemm(e, e->act, F, w.mproj_w, w.mproj_b, cur, H, dst, H, B, H, F, 0u, s));
+        cur = dst;
+      }
     }
   }
   if (c.has_head && !use_gemv && tc_ok && e->logits_ws != nullptr && gemm_tc_supported(B, e->V, H)) {
@@ -585,6 +607,17 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
     set_err(nullptr, "gp_engine_create: invalid configuration");
     return GP_EINVAL;
   }
+  {
+    // half-block boundaries: a stage may start at the MLP half of its first block and / or stop after the attention
+    // half of its last one; such a stage needs a block to cut and neither the embeddings before nor the head after it
+    const bool bh = cfg->flags & GP_FLAG_BEGIN_HALF, eh = cfg->flags & GP_FLAG_END_HALF;
+    const int nl = cfg->layer_end - cfg->layer_begin;
+    if ((bh && (cfg->has_embed || nl < 1)) || (eh && (cfg->has_head || nl < 1)) || (bh && eh && nl < 2)) {
+      set_err(nullptr, "gp_engine_create: GP_FLAG_BEGIN_HALF / GP_FLAG_END_HALF do not fit this stage (blocks [%d,%d), has_embed=%d, has_head=%d)",
+              cfg->layer_begin, cfg->layer_end, cfg->has_embed, cfg->has_head);
+      return GP_EINVAL;
+    }
+  }
   int ndev = 0;
   cudaError_t ce = cudaGetDeviceCount(&ndev);
   if (ce != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
@@ -629,10 +662,14 @@ int gp_engine_create(const gp_config* cfg, gp_engine** out) {
       TRY(alloc((void**)&w.attn_u, 3 * H * 4)); TRY(alloc((void**)&w.attn_c, 3 * H * 4));
       TRY(alloc((void**)&w.fc_u, F * 4)); TRY(alloc((void**)&w.fc_c, F * 4));
     }
-    for (const char* n : {"ln_1.weight", "ln_1.bias", "attn.c_attn.weight", "attn.c_attn.bias", "attn.c_proj.weight",
-                          "attn.c_proj.bias", "ln_2.weight", "ln_2.bias", "mlp.c_fc.weight", "mlp.c_fc.bias",
-                          "mlp.c_proj.weight", "mlp.c_proj.bias"})
-      e->required.insert(p + n);
+    if (has_attn_half(e, li))
+      for (const char* n : {"ln_1.weight", "ln_1.bias", "attn.c_attn.weight", "attn.c_attn.bias", "attn.c_proj.weight",
+                            "attn.c_proj.bias"})
+        e->required.insert(p + n);
+    if (has_mlp_half(e, li))
+      for (const char* n : {"ln_2.weight", "ln_2.bias", "mlp.c_fc.weight", "mlp.c_fc.bias", "mlp.c_proj.weight",
+                            "mlp.c_proj.bias"})
+        e->required.insert(p + n);
   }
   if (cfg->has_embed || cfg->has_head) {
     TRY(alloc(&e->wte, V * H * esz));

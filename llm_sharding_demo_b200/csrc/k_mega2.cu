@@ -916,10 +916,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
     for (int item = 0; item < n_items; ++item) {
       for (int li = 0; li < L; ++li) {
         const MegaLayer& w = s_layers[li];
-        produce_phase(rg, w.attn_w, w.attn_u, w.attn_c, s_kind[K_QKV], p.slot_data, policy, lane);
-        produce_phase(rg, w.proj_w, w.proj_b, nullptr, s_kind[K_PROJ], p.slot_data, policy, lane);
-        produce_phase(rg, w.fc_w, w.fc_u, w.fc_c, s_kind[K_FC], p.slot_data, policy, lane);
-        produce_phase(rg, w.mproj_w, w.mproj_b, nullptr, s_kind[K_PROJ2], p.slot_data, policy, lane);
+        if (!(li == 0 && p.begin_half)) {        // a stage may start at the MLP half of its first block ...
+          produce_phase(rg, w.attn_w, w.attn_u, w.attn_c, s_kind[K_QKV], p.slot_data, policy, lane);
+          produce_phase(rg, w.proj_w, w.proj_b, nullptr, s_kind[K_PROJ], p.slot_data, policy, lane);
+        }
+        if (!(li == L - 1 && p.end_half)) {      // ... and stop after the attention half of its last one
+          produce_phase(rg, w.fc_w, w.fc_u, w.fc_c, s_kind[K_FC], p.slot_data, policy, lane);
+          produce_phase(rg, w.mproj_w, w.mproj_b, nullptr, s_kind[K_PROJ2], p.slot_data, policy, lane);
+        }
       }
       if (p.has_head) produce_phase(rg, p.wte, p.lnf_u, p.lnf_c, s_kind[K_HEAD], p.slot_data, policy, lane);
     }
@@ -948,7 +952,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
   int c0, c1;                                        // residual rows this CTA owns (same split as the N = H phases)
   rows_of(cta, G, H, c0, c1);
   cx.c0 = c0;
-  const int n_ph = 5 * L + (p.has_head ? 1 : 0);
+  const int n_ph = 5 * L + (p.has_head ? 1 : 0) - (p.begin_half ? 3 : 0) - (p.end_half ? 2 : 0);   // phases of one item on this stage
   const uint32_t ep_per_item = (uint32_t)(5 * L + 2);
 
   for (int item = 0; item < n_items; ++item) {
@@ -995,12 +999,17 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
       } else {
         hv = __ldcg(p.hidden_in + (size_t)b * H + col);
       }
-      hloc[b * kOwnMax + (col - c0)] = hv;
-      ll_store(p.h_ll + ll_off((size_t)b * H + col, cx.ll_shift), __float_as_uint(hv), ep_item);
+      if (p.begin_half) {   // the input is the residual stream after the attention half: what the c_fc phase expects
+        h2loc[b * kOwnMax + (col - c0)] = hv;
+        ll_store(p.h2_ll + ll_off((size_t)b * H + col, cx.ll_shift), __float_as_uint(hv), ep_item);
+      } else {
+        hloc[b * kOwnMax + (col - c0)] = hv;
+        ll_store(p.h_ll + ll_off((size_t)b * H + col, cx.ll_shift), __float_as_uint(hv), ep_item);
+      }
     }
     cx.stamp(7 * 16 + 0, __float_as_uint(hloc[0]));
     Best best{-INFINITY, 0x7fffffff};
-    int li = 0, kind = (L > 0) ? K_QKV : K_HEAD;
+    int li = 0, kind = (L > 0) ? (p.begin_half ? K_FC : K_QKV) : K_HEAD;
     for (int ph = 0; ph < n_ph; ++ph) {
       const uint32_t ep_dst = ep_item + (uint32_t)ph + 1u;     // data produced by phase ph; phase ph consumes epoch ep_dst - 1
       const MegaLayer& w = s_layers[li];
@@ -1027,11 +1036,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega2_kernel(const MegaPar
       PhaseOut po;
       po.kind = kind; po.dst_plain = nullptr; po.dst_sys = 0; po.dst_epoch = ep_dst;
       po.dst_ll = (kind == K_QKV) ? p.qkv_ll : (kind == K_PROJ) ? p.h2_ll : (kind == K_FC) ? p.act_ll : p.h_ll;
-      if (kind == K_PROJ2 && li == L - 1 && !p.has_head) {
+      if (ph == n_ph - 1 && !p.has_head) {   // the stage's last phase (c_proj of the MLP, or of the attention when the block is cut)
         if (p.peer_hid != nullptr) { po.dst_ll = p.peer_hid + (size_t)strm * B * H; po.dst_epoch = cep; po.dst_sys = 1; }
         else po.dst_plain = p.hidden_out;
       }
-      if (ki.ln) {
+      if (ki.r0 >= ki.r1) {
+        // no rows of this phase here (fewer rows than CTAs: toy widths only): nothing to stage.  Staging anyway would
+        // let this CTA fall behind by a phase nobody waits for it in, and meet words of the next item.
+      } else if (ki.ln) {
         const float* g = (kind == K_QKV) ? w.ln1_g : (kind == K_FC) ? w.ln2_g : p.lnf_g;
         stage_ln<BT, TR>(cx, src, ep_dst - 1u, g, ki.K, kind * 16);
       } else if (SP && kind == K_PROJ && n_split > 1) {

@@ -124,6 +124,7 @@ struct MegaParams {
   int ablate = 0;                                            // timing experiments (GP_MEGA_ABLATE): parts of the kernel skipped, results wrong
   // token selection: 0 = greedy argmax; 1 = temperature / top-k / multinomial (k_sample.cu), needs logits_out
   int sampler_on = 0; float sample_temperature = 1.f; int sample_top_k = 0; uint32_t sample_seed_lo = 0, sample_seed_hi = 0;
+  int begin_half = 0, end_half = 0;                          // the first block starts at its MLP half / the last block stops after its attention half
   int ctx_hint = 0;                                          // longest context this launch can reach (0: unknown, max_ctx is assumed)
   int split_min = 256, split_keys = 128;                     // attention tasks are split over CTAs from this context on, one CTA per split_keys keys
   int poll_ns = 0;                                           // back-off between polls of the exchange words (0: spin)

@@ -8,7 +8,7 @@ from typing import Dict, Optional
 import torch
 
 from . import _lib
-from ._lib import GPConfig, GPError, GP_BF16, GP_F32, check, load_library
+from ._lib import GPConfig, GPError, GP_BF16, GP_F32, GP_FLAG_BEGIN_HALF, GP_FLAG_END_HALF, check, load_library
 from .weights import GPT2Dims, stage_weight_names
 
 
@@ -31,7 +31,10 @@ class StageEngine:
 
     def __init__(self, dims: GPT2Dims, layer_begin: int = 0, layer_end: Optional[int] = None,
                  has_embed: bool = True, has_head: bool = True, dtype: int = GP_BF16, max_batch: int = 1,
-                 max_ctx: Optional[int] = None, max_tokens: int = 0, device: int = 0, flags: int = 0):
+                 max_ctx: Optional[int] = None, max_tokens: int = 0, device: int = 0, flags: int = 0,
+                 begin_half: bool = False, end_half: bool = False):
+        """begin_half / end_half: the stage starts at the MLP half of block `layer_begin` / stops after the attention
+        half of block `layer_end - 1` (GP_FLAG_BEGIN_HALF / GP_FLAG_END_HALF, weights.balanced_split_halves)."""
         _require_cuda()
         self.lib = load_library()
         self.dims = dims
@@ -40,6 +43,8 @@ class StageEngine:
         self.has_embed, self.has_head = bool(has_embed), bool(has_head)
         self.dtype = dtype
         self.max_batch = max_batch
+        self.begin_half, self.end_half = bool(begin_half), bool(end_half)
+        flags |= (GP_FLAG_BEGIN_HALF if begin_half else 0) | (GP_FLAG_END_HALF if end_half else 0)
         self.max_ctx = dims.n_positions if max_ctx is None else max_ctx
         self.device = torch.device("cuda", device)
         cfg = GPConfig(dims.n_layer, dims.n_embd, dims.n_head, dims.vocab_size, dims.n_positions,
@@ -62,7 +67,8 @@ class StageEngine:
             pass
 
     def weight_names(self):
-        return stage_weight_names(self.dims, self.layer_begin, self.layer_end, self.has_embed, self.has_head)
+        return stage_weight_names(self.dims, self.layer_begin, self.layer_end, self.has_embed, self.has_head,
+                                  self.begin_half, self.end_half)
 
     def load_weights(self, weights: Dict[str, torch.Tensor]):
         """`weights`: GPT2Model.state_dict()-style fp32 tensors (`transformer.` prefix optional)."""

@@ -14,7 +14,8 @@ from typing import List, Optional, Tuple
 import torch
 
 from ._lib import GP_BF16
-from .weights import GPT2Dims, balanced_split, init_weights, split_layers, stage_weight_names
+from .weights import (GPT2Dims, balanced_split, balanced_split_halves, half_costs_us, init_weights, split_layers, stage_costs_us,
+                      stage_flags, stage_weight_names)
 
 
 def tick_schedule(n_stages: int, n_streams: int, n_rounds: int) -> List[List[Optional[Tuple[int, int]]]]:
@@ -67,13 +68,27 @@ def run_ticks(rank: int, n_stages: int, n_streams: int, n_rounds: int, exchange,
             pending = compute(item[0], item[1], got)
 
 
+def _slowest(dims: GPT2Dims, stages) -> float:
+    """Predicted time of the slowest stage of a split (weights.stage_costs_us / half_costs_us), boundaries in blocks."""
+    t_a, t_m = half_costs_us(dims)
+    t_head = stage_costs_us(dims)[1]
+    worst = 0.0
+    for k, (b, e) in enumerate(stages):
+        c = sum(t_a if i % 2 == 0 else t_m for i in range(int(round(2 * b)), int(round(2 * e))))
+        worst = max(worst, c + (t_head if k == len(stages) - 1 else 0.0))
+    return worst
+
+
 class PipelineRunner:
     def __init__(self, dims: GPT2Dims, seed: int = 0, dtype: int = GP_BF16, batch_per_stream: int = 1,
                  max_ctx: Optional[int] = None, rank: int = 0, world: int = 1, device: int = 0, recipe: str = "hf",
-                 weights=None, flags: int = 0, transport: str = "p2p", split: str = "auto", n_streams: Optional[int] = None):
+                 weights=None, flags: int = 0, transport: str = "p2p", split="auto", n_streams: Optional[int] = None):
         """split: "even" = equal block counts (the reference's SPLIT_AT rule generalised), "balanced" = block counts
         chosen so that the stage that also carries ln_f + lm_head is not the slowest (it may get no block at all),
-        "auto" = balanced where the bf16 persistent kernel runs (it is what executes a head-only stage), else even."""
+        "halves" = the same with boundaries also allowed between the attention and the MLP half of a block
+        (self.stages then holds x.5 values), "auto" = where the bf16 persistent kernel runs (it is what executes a
+        head-only stage and a cut block at full speed) halves when that makes the slowest stage at least 2 % lighter,
+        else balanced; even everywhere else.  A list of (begin, end) pairs in blocks sets the boundaries explicitly."""
         from .engine import StageEngine
         self.dims, self.rank, self.world, self.B = dims, rank, world, batch_per_stream
         self.n_streams = n_streams or world
@@ -82,15 +97,26 @@ class PipelineRunner:
         self.device = torch.device("cuda", device)
         if split == "auto":
             ok = dtype == GP_BF16 and dims.head_dim == 64 and dims.n_embd % 64 == 0 and batch_per_stream <= 8 and transport == "p2p"
-            split = "balanced" if ok else "even"
-        self.stages = balanced_split(dims, world) if split == "balanced" else split_layers(dims.n_layer, world)
-        b, e = self.stages[rank]
+            split = "even"
+            if ok and world > 1:
+                split = "halves" if _slowest(dims, balanced_split_halves(dims, world)) < 0.98 * _slowest(dims, balanced_split(dims, world)) \
+                    else "balanced"
+        if isinstance(split, (list, tuple)):       # explicit stage boundaries in blocks (x.5 = inside block x)
+            self.stages = [(float(b), float(e)) for b, e in split]
+            if len(self.stages) != world or self.stages[0][0] != 0 or self.stages[-1][1] != dims.n_layer or \
+                    any(self.stages[k][1] != self.stages[k + 1][0] for k in range(world - 1)):
+                raise ValueError(f"stage boundaries {split} do not cover blocks [0, {dims.n_layer}] contiguously in {world} stages")
+        elif split == "halves":
+            self.stages = balanced_split_halves(dims, world)
+        else:
+            self.stages = balanced_split(dims, world) if split == "balanced" else split_layers(dims.n_layer, world)
+        b, e, begin_half, end_half = stage_flags(*self.stages[rank])
         self.first, self.last = rank == 0, rank == world - 1
         self.engine = StageEngine(dims, b, e, has_embed=self.first, has_head=self.last, dtype=dtype,
                                   max_batch=batch_per_stream * self.n_streams, max_ctx=max_ctx,
                                   max_tokens=batch_per_stream * (max_ctx or dims.n_positions), device=device,
-                                  flags=flags)
-        names = stage_weight_names(dims, b, e, self.first, self.last)
+                                  flags=flags, begin_half=begin_half, end_half=end_half)
+        names = self.engine.weight_names()
         w = weights if weights is not None else init_weights(dims, seed, recipe, only=names)
         self.engine.load_weights(w)
         if world > 1:

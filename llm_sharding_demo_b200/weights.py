@@ -114,11 +114,72 @@ def balanced_split(dims: GPT2Dims, n_stages: int, esz: int = 2) -> List[Tuple[in
     return out
 
 
-def stage_weight_names(dims: GPT2Dims, layer_begin: int, layer_end: int, has_embed: bool, has_head: bool) -> List[str]:
+_ATTN_HALF = ("ln_1.", "attn.")     # tensors of a block's attention half; the rest (ln_2, mlp) is its MLP half
+
+
+def half_costs_us(dims: GPT2Dims, esz: int = 2) -> Tuple[float, float]:
+    """(attention half, MLP half) of one block, same calibration as stage_costs_us (they add up to its block cost):
+    three dependent phases + the attention itself against two phases, 4 H^2 against 8 H^2 weights."""
+    H = dims.n_embd
+    return 5.4 + esz * (4 * H * H + 6 * H) / 5.5e6, 3.6 + esz * (8 * H * H + 7 * H) / 5.5e6
+
+
+def stage_flags(begin: float, end: float) -> Tuple[int, int, bool, bool]:
+    """(layer_begin, layer_end, begin_half, end_half) of a stage given in blocks, x.5 = a cut between the attention and
+    the MLP half of block x (balanced_split_halves)."""
+    return int(math.floor(begin)), int(math.ceil(end)), begin != math.floor(begin), end != math.floor(end)
+
+
+def balanced_split_halves(dims: GPT2Dims, n_stages: int, esz: int = 2) -> List[Tuple[float, float]]:
+    """Like balanced_split, with stage boundaries allowed between the two halves of a block (x += attn(ln_1 x) |
+    x += mlp(ln_2 x): the residual stream is a complete hand-off there too).  Boundaries are in blocks, 3.5 = after the
+    attention half of block 3.  Minimises the slowest stage; every stage but the last gets at least one half, the last
+    one carries ln_f + lm_head and may get none.  124M on 4 stages: 3.5 blocks instead of 4 on the slowest stage."""
+    L = dims.n_layer
+    if n_stages == 1:
+        return [(0.0, float(L))]
+    if not 2 <= n_stages <= 2 * L + 1:
+        raise ValueError(f"cannot split {L} layers into {n_stages} stages")
+    t_a, t_m = half_costs_us(dims, esz)
+    _, t_head = stage_costs_us(dims, esz)
+    n = 2 * L
+    pre = [0.0]
+    for i in range(n):
+        pre.append(pre[-1] + (t_a if i % 2 == 0 else t_m))
+    INF = float("inf")
+    # best[s][i]: smallest possible slowest-stage cost when the first s stages cover halves [0, i)
+    best = [[INF] * (n + 1) for _ in range(n_stages + 1)]
+    cut = [[0] * (n + 1) for _ in range(n_stages + 1)]
+    best[0][0] = 0.0
+    for s in range(1, n_stages + 1):
+        last = s == n_stages
+        for i in range(n + 1):
+            for j in range(i + 1 if not last else i + 0, -1, -1):
+                if j > i or (not last and j == i) or best[s - 1][j] == INF:
+                    continue
+                c = max(best[s - 1][j], pre[i] - pre[j] + (t_head if last else 0.0))
+                if c < best[s][i] - 1e-9:
+                    best[s][i], cut[s][i] = c, j
+    bounds, i = [n], n
+    for s in range(n_stages, 0, -1):
+        i = cut[s][i]
+        bounds.append(i)
+    bounds.reverse()
+    return [(bounds[k] / 2.0, bounds[k + 1] / 2.0) for k in range(n_stages)]
+
+
+def stage_weight_names(dims: GPT2Dims, layer_begin: int, layer_end: int, has_embed: bool, has_head: bool,
+                       begin_half: bool = False, end_half: bool = False) -> List[str]:
+    """Tensors a stage holds.  begin_half: block `layer_begin` contributes only its MLP half (its attention half ran
+    on the previous stage); end_half: block `layer_end - 1` contributes only its attention half (GP_FLAG_*_HALF)."""
     names = []
     for name, _, _ in weight_names(dims):
         if name.startswith("h."):
-            if layer_begin <= int(name.split(".")[1]) < layer_end:
+            li = int(name.split(".")[1])
+            if layer_begin <= li < layer_end:
+                attn = name.split(".", 2)[2].startswith(_ATTN_HALF)
+                if (begin_half and li == layer_begin and attn) or (end_half and li == layer_end - 1 and not attn):
+                    continue
                 names.append(name)
         elif name == "wte.weight":
             if has_embed or has_head:  # tied lm_head: the last stage keeps its own copy

@@ -11,6 +11,7 @@ On identical seeded weights, for N = 2, 4, 8 stages:
      stream against a stateless full-sequence pass on a single-stage engine (bench.ids_check).  Stages whose
      weights exceed 96 MB stream them with the L2 evict-first hint and the others do not (engine.cu), so both
      branches run at N = 2;
+  E. case B again with stage boundaries inside blocks (explicit x.5 boundaries): identical ids;
   D. the same pipeline with the reference's sampler on the last stage: reproducible, different from greedy, and
      identical to a single-stage engine stepping each sequence alone in the same KV slot.
 Prints one MULTI_GPU_CHECK_OK line with the counts."""
@@ -84,6 +85,22 @@ def main():
         assert torch.equal(first, second), "the same request twice gave different ids"
         counts["B"] = oracle_agreement(second, w, odims, prompts, n_new, 0.12)
         assert counts["B"] >= world * 2, counts
+    dist.barrier()
+    del runner
+
+    # ---- E: the same request through a pipeline whose stage boundaries may fall INSIDE a block (after its attention
+    # half; GP_FLAG_END_HALF / GP_FLAG_BEGIN_HALF): the hidden state crossing NVLink is then the mid-block residual
+    # stream.  Same kernels, same row ownership, so the ids must equal case B's.
+    runner = PipelineRunner(dims, dtype=L.GP_BF16, batch_per_stream=B, max_ctx=P + n_new, rank=rank, world=world,
+                            device=local, weights=w, transport="p2p",
+                            split={2: [(0, 1.5), (1.5, 4)], 4: [(0, 0.5), (0.5, 2), (2, 3.5), (3.5, 4)],
+                                   8: [(0, 0.5), (0.5, 1.5), (1.5, 3), (3, 3.5), (3.5, 5), (5, 6.5), (6.5, 7.5), (7.5, 8)]}[world])
+    cut = runner.generate(prompts, n_new)
+    if rank == 0:
+        assert any(x != int(x) for be in runner.stages for x in be), runner.stages    # at least one boundary is x.5
+        assert torch.equal(cut, second), "a boundary inside a block changed the ids"
+        print("E", [list(x) for x in runner.stages], flush=True)
+        counts["E"] = int(cut.numel())
     dist.barrier()
     del runner
 

@@ -525,3 +525,44 @@ def test_long_context_decode_splits_attention_tasks(L, B):
     firm = ((top2.values[..., 0] - top2.values[..., 1]) > 2 * TOL_BF16).cpu()
     assert int(firm.sum()) >= 2
     assert torch.equal(top2.indices[..., 0].cpu().to(torch.int32)[firm], out[:, P2:][firm])
+
+
+@pytest.mark.parametrize("dtype_name,flags", [("bf16", 0), ("bf16", 4), ("f32", 0)])
+@pytest.mark.parametrize("ranges", [[(0, 1.5), (1.5, 3.0), (3.0, 3.5), (3.5, 4.0)], [(0, 0.5), (0.5, 2.5), (2.5, 4.0)]])
+def test_stage_boundaries_inside_a_block(L, dtype_name, flags, ranges):
+    """GP_FLAG_BEGIN_HALF / GP_FLAG_END_HALF: a stage may stop after the attention half of its last block and the next
+    one start at that block's MLP half (weights.balanced_split_halves).  Covered here: a stage cut at its end, at its
+    beginning, at both, an attention-half-only and an MLP-half-only (+ head) stage; the persistent kernel (bf16), the
+    per-op kernels (bf16 with GP_FLAG_NO_MEGA, fp32).  The chain must reproduce the single-stage engine: prefill logits
+    exactly, cached decode steps to the tolerance the head-only-stage test uses."""
+    dims = O.PRESETS["mini"]
+    w = O.init_weights(dims, 53, "dense")
+    pd = L.GPT2Dims(**dims.to_dict())
+    dtype = L.GP_BF16 if dtype_name == "bf16" else L.GP_F32
+    engines = []
+    for i, (b, e) in enumerate(ranges):
+        lb, le, bh, eh = L.stage_flags(b, e)
+        eng = L.StageEngine(pd, lb, le, has_embed=(i == 0), has_head=(i == len(ranges) - 1), dtype=dtype, max_batch=2,
+                            flags=flags, begin_half=bh, end_half=eh)
+        names = eng.weight_names()
+        assert (f"h.{lb}.attn.c_attn.weight" in names) == (not bh) and (f"h.{le - 1}.mlp.c_fc.weight" in names) == (not eh)
+        eng.load_weights(w)
+        engines.append(eng)
+    single = L.StageEngine(pd, dtype=dtype, max_batch=2, flags=flags)
+    single.load_weights(w)
+    prompt = torch.tensor([[7, 99, 1040, 3, 512], [1, 2, 3, 4, 5]])
+    a, _ = run_prefill(engines, prompt)
+    b, _ = run_prefill([single], prompt)
+    assert torch.equal(a["logits"], b["logits"])
+    for _ in range(4):
+        tok = b["next_ids"].cpu()
+        a = run_decode(engines, tok)
+        b = run_decode([single], tok)
+        assert float((a["logits"] - b["logits"]).abs().max()) <= (2e-3 if dtype_name == "bf16" else 2e-5)
+        assert torch.equal(a["next_ids"], b["next_ids"])
+    # what cannot be cut: the embedding stage's beginning, the head stage's end, a one-block stage at both ends
+    for kw in (dict(layer_begin=0, layer_end=2, has_embed=True, has_head=False, begin_half=True),
+               dict(layer_begin=2, layer_end=4, has_embed=False, has_head=True, end_half=True),
+               dict(layer_begin=1, layer_end=2, has_embed=False, has_head=False, begin_half=True, end_half=True)):
+        with pytest.raises(L.GPError):
+            L.StageEngine(pd, dtype=dtype, **kw)

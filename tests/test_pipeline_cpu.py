@@ -109,3 +109,37 @@ def test_ring_pipeline_over_gloo(world):
     assert len(got) == R * M
     for (r, m), ids in got.items():
         assert ids == ref[m][r].tolist(), (r, m)
+
+
+def test_half_block_splits_cover_the_model_and_partition_its_weights():
+    """weights.balanced_split_halves: contiguous stages in half-block units that cover [0, n_layer]; every stage but
+    the last has work; the stage flags and the per-stage tensor lists partition the model's tensors exactly (the tied
+    wte is held by the first and the last stage); a cut never makes the predicted slowest stage slower than the
+    block-granular split."""
+    import llm_sharding_demo_b200 as L
+    from llm_sharding_demo_b200.pipeline import _slowest
+    from llm_sharding_demo_b200.weights import weight_names
+    for name in ("gpt2", "gpt2-medium", "gpt2-xl", "mini"):
+        dims = L.PRESETS[name] if name in L.PRESETS else None
+        if dims is None:
+            continue
+        for S in (1, 2, 4, 8):
+            if S > 2 * dims.n_layer + 1:
+                continue
+            st = L.balanced_split_halves(dims, S)
+            assert len(st) == S and st[0][0] == 0.0 and st[-1][1] == float(dims.n_layer)
+            assert all(st[k][1] == st[k + 1][0] for k in range(S - 1))
+            assert all(e > b for b, e in st[:-1]) and st[-1][1] >= st[-1][0]
+            assert all((2 * x) == int(2 * x) for be in st for x in be)
+            if 2 <= S <= dims.n_layer + 1:
+                assert _slowest(dims, st) <= _slowest(dims, L.balanced_split(dims, S)) + 1e-6
+            held = []
+            for k, (b, e) in enumerate(st):
+                lb, le, bh, eh = L.stage_flags(b, e)
+                held += L.stage_weight_names(dims, lb, le, k == 0, k == S - 1, bh, eh)
+            every = [n for n, _, _ in weight_names(dims)]
+            extra_wte = 1 if S > 1 else 0
+            assert sorted(held) == sorted(every + ["wte.weight"] * extra_wte)
+    assert L.balanced_split_halves(L.PRESETS["gpt2"], 4) == [(0.0, 3.5), (3.5, 7.0), (7.0, 10.5), (10.5, 12.0)]
+    assert L.stage_flags(3.5, 7.0) == (3, 7, True, False) and L.stage_flags(0.0, 3.5) == (0, 4, False, True)
+    assert L.stage_flags(12.0, 12.0) == (12, 12, False, False)
