@@ -78,10 +78,10 @@ def split_layers(n_layer: int, n_stages: int) -> List[Tuple[int, int]]:
 def stage_costs_us(dims: GPT2Dims, esz: int = 2) -> Tuple[float, float]:
     """(one block, ln_f + lm_head) in microseconds of a batch-1 decode step on one B200: a fixed part for the
     dependent phases (5 exchanges per block, the argmax exchange of the head) plus the weight stream at ~5.5-6 TB/s.
-    Calibrated on the phase trace of the persistent kernel (profiles/r02_results.md: 124M 11.5 / 17 us); only the
+    Calibrated on the persistent kernel (profiles/r02_results.md: 124M 12.8 / 17 us per token of 170.7); only the
     RATIO matters for the split."""
     H, V = dims.n_embd, dims.vocab_size
-    return 9.0 + esz * (12 * H * H + 13 * H) / 5.5e6, 4.0 + esz * V * H / 6.0e6
+    return 10.2 + esz * (12 * H * H + 13 * H) / 5.5e6, 4.0 + esz * V * H / 6.0e6
 
 
 def balanced_split(dims: GPT2Dims, n_stages: int, esz: int = 2) -> List[Tuple[int, int]]:
@@ -121,7 +121,7 @@ def half_costs_us(dims: GPT2Dims, esz: int = 2) -> Tuple[float, float]:
     """(attention half, MLP half) of one block, same calibration as stage_costs_us (they add up to its block cost):
     three dependent phases + the attention itself against two phases, 4 H^2 against 8 H^2 weights."""
     H = dims.n_embd
-    return 5.4 + esz * (4 * H * H + 6 * H) / 5.5e6, 3.6 + esz * (8 * H * H + 7 * H) / 5.5e6
+    return 6.1 + esz * (4 * H * H + 6 * H) / 5.5e6, 4.1 + esz * (8 * H * H + 7 * H) / 5.5e6
 
 
 def stage_flags(begin: float, end: float) -> Tuple[int, int, bool, bool]:
