@@ -566,3 +566,35 @@ def test_stage_boundaries_inside_a_block(L, dtype_name, flags, ranges):
                dict(layer_begin=1, layer_end=2, has_embed=False, has_head=False, begin_half=True, end_half=True)):
         with pytest.raises(L.GPError):
             L.StageEngine(pd, dtype=dtype, **kw)
+
+
+def test_split_attention_with_mixed_context_lengths(L):
+    """Continuous batching puts a 300-token context and a 3-token context into the same decode step: the step's
+    attention tasks are split over CTAs by the LONGEST context, so the short sequence's tasks have empty pieces and its
+    new key lands in whichever piece covers it.  Step by step the persistent kernel (slot-indexed) must match the
+    per-op kernels decoding each sequence alone."""
+    pd = L.GPT2Dims(n_layer=2, n_embd=128, n_head=2, vocab_size=1041, n_positions=512)
+    w = L.init_weights(pd, 77, "dense")
+    mega = L.StageEngine(pd, dtype=L.GP_BF16, max_batch=4, max_ctx=400, max_tokens=400)
+    ops = L.StageEngine(pd, dtype=L.GP_BF16, max_batch=4, max_ctx=400, max_tokens=400, flags=4)
+    for e in (mega, ops):
+        e.load_weights(w)
+    g = torch.Generator().manual_seed(5)
+    lens, slots = [300, 3], [2, 0]
+    prompts = [torch.randint(0, pd.vocab_size, (1, n), generator=g, dtype=torch.int32).to(DEV) for n in lens]
+    tok = []
+    for p, s in zip(prompts, slots):
+        a = mega.prefill(p, slot0=s, use_cache=True, want_ids=True)
+        b = ops.prefill(p, slot0=s, use_cache=True, want_ids=True)
+        assert torch.equal(a["next_ids"], b["next_ids"])
+        tok.append(int(b["next_ids"][0]))
+    for t in range(6):
+        ids = torch.tensor(tok, dtype=torch.int32, device=DEV)
+        out = mega.decode_slots(ids, slots, want_logits=True)
+        assert mega.last_launch_count() <= 3
+        for i, s in enumerate(slots):
+            ref = ops.decode(ids[i:i + 1], slot0=s, want_logits=True)
+            assert float((out["logits"][i] - ref["logits"][0]).abs().max()) <= 5e-3, (t, i)
+            tok[i] = int(ref["next_ids"][0])
+    kv = mega.kv_lengths()
+    assert [kv[s] for s in slots] == [n + 6 for n in lens]
