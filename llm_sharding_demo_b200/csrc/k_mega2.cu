@@ -761,9 +761,7 @@ __device__ __forceinline__ void attention_task(Ctx<TR>& cx, const AttnArgs& a, i
       ll_store(a.attn_ll + ll_off((size_t)b * H + head * kD + tid, cx.ll_shift), __float_as_uint(o / Lsum), a.ep_attn);
     } else {
       // unnormalised partial of this key range: 64 outputs + (max, sum); the consumers of the c_proj phase merge them
-      u64* pp = a.attn_ll + ll_off(a.part_base + ((size_t)(b * a.nh + head) * kMaxSplit + split) * kPartStride, cx.ll_shift);
       const size_t pbase = a.part_base + ((size_t)(b * a.nh + head) * kMaxSplit + split) * kPartStride;
-      (void)pp;
       ll_store(a.attn_ll + ll_off(pbase + tid, cx.ll_shift), __float_as_uint(o), a.ep_attn);
       if (tid == 0) ll_store(a.attn_ll + ll_off(pbase + 64, cx.ll_shift), __float_as_uint(M), a.ep_attn);
       if (tid == 1) ll_store(a.attn_ll + ll_off(pbase + 65, cx.ll_shift), __float_as_uint(Lsum), a.ep_attn);
