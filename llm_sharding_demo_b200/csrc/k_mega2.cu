@@ -16,10 +16,19 @@
 //    summed through shared memory in a fixed order (deterministic).  No shuffle reductions, no per-sequence FMA loop.
 //  * weight rows land in shared memory with a 16-byte pad per row (one cp.async.bulk per row, issued by the 32
 //    lanes of the producer warp), which makes both fragment loads bank-conflict free.
-//  * LayerNorm with one block-wide exchange: per-warp (count, mean, M2) merged with Chan's formula.
+//  * LayerNorm out of the critical path: the staging multiplies by gamma only and leaves per-warp (sum, sum of
+//    squares) in shared memory; the epilogue applies y = rstd (W.(gamma x) - mean u) + c with u = W.gamma and
+//    c = W.beta + bias precomputed per row (ln_fold_kernel), so nothing block-wide sits between "input arrived" and
+//    "first mma".
 //  * decode attention "scores first": every thread owns ONE cached key (its 64-wide row is prefetched into
 //    registers before q arrives), the softmax weights never leave the warp (online softmax per warp), P.V runs over
 //    the warp's own keys, and the 15 per-warp partials merge through shared memory - 2 block barriers per task.
+//    From 256 positions on, with CTAs to spare, up to 4 CTAs share a task (a key range each) and the c_proj staging
+//    merges their partials (stage_attn_merge; a separate instantiation, SP, chosen per launch).
+//  * token selection: greedy argmax (one 64-bit partial per CTA and sequence, every CTA reduces them itself) or the
+//    reference's temperature / top-k / multinomial draw (CTA b draws for sequence b, sample.cuh).
+//  * a stage runs a PHASE RANGE per item: it may start at the c_fc phase of its first block and stop after the
+//    attention c_proj of its last one (half-block stage boundaries, GP_FLAG_BEGIN_HALF / GP_FLAG_END_HALF).
 //  * every spin loop polls an abort word the host can set (watchdog), a progress word counts finished items, and
 //    the KV slot of each sequence comes from a slot table (non-contiguous batches for continuous batching).
 //
