@@ -31,11 +31,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
     ap.add_argument("--cfg5", action="store_true", help="the 124M batch x prompt grid of BASELINE.json configs[4] on one GPU")
+    ap.add_argument("--min-batch", type=int, default=1, help="only the cases with at least this many sequences")
     args = ap.parse_args()
     peak, kind = measured_peaks()
     engines = {}
     for model, B, P, n_new in (CFG5 if args.cfg5 else CASES):
-        if args.only and args.only not in model:
+        if (args.only and args.only not in model) or B < args.min_batch:
             continue
         dims = L.PRESETS[model]
         key = model
