@@ -11,7 +11,8 @@ GPU to GPU over NVLink (gp_pipeline_decode).  This replaces the reference's thre
 SPLIT_AT of the stages cannot disagree (the reference ships SPLIT_AT=2 on shard A and 1 on shard B).
 
 Env (same names as the reference where they exist): MODEL_ID, SHARD_PORT; GP_WEIGHTS / GP_RANDOM_INIT / GP_SEED / GP_DTYPE
-as in `server.py`; GP_MAX_CTX (KV positions per request, default n_positions).
+as in `server.py`; GP_MAX_CTX (KV positions per request, default n_positions); GP_SAMPLING=reference draws every token
+with the reference's temperature 0.6 / top-k 40 sampler on the last stage (seed GP_SAMPLE_SEED + request number).
 `GET /healthz` answers 200 once every stage has its weights (readiness probe)."""
 from __future__ import annotations
 
@@ -24,7 +25,8 @@ import torch.distributed as dist
 from . import weights as W
 from ._lib import GP_BF16, GP_F32
 from .pipeline import PipelineRunner
-from .server import GenerateReq, ByteTokenizer, load_pretrained, load_tokenizer, read_env, _warn  # noqa: F401
+from .server import (GenerateReq, ByteTokenizer, REF_TEMPERATURE, REF_TOP_K, load_pretrained, load_tokenizer, read_env,  # noqa: F401
+                     _warn)
 
 
 def _load(cfg):
@@ -53,8 +55,14 @@ def main():
                             world=world, device=local, weights=weights, n_streams=1)
     ctl = dist.new_group(backend="gloo")      # request broadcast (host objects) stays off the NCCL stream
 
-    def step(ids, n_new):
+    sampled = cfg["GP_SAMPLING"] == "reference"
+    if sampled and dtype != GP_BF16:
+        raise ValueError("GP_SAMPLING=reference in the pod server needs GP_DTYPE=bf16 (the fp32 pipeline kernel selects greedily)")
+
+    def step(ids, n_new, seed=None):
         """Runs on every rank with the same arguments."""
+        if seed is not None:      # the sampler lives on the stage with the lm_head; a no-op elsewhere
+            runner.set_sampler(REF_TEMPERATURE, min(REF_TOP_K, dims.vocab_size), seed)
         prompts = torch.tensor([ids], dtype=torch.int32)
         return runner.generate(prompts, n_new)
 
@@ -72,6 +80,7 @@ def main():
     from fastapi import FastAPI, HTTPException
     tokenizer = load_tokenizer(cfg["MODEL_ID"])
     lock = threading.Lock()
+    served = [0]
     app = FastAPI()
 
     @app.get("/healthz")
@@ -89,9 +98,11 @@ def main():
         if len(ids) + n_new - 1 > max_ctx:
             raise HTTPException(status_code=400, detail=f"prompt of {len(ids)} tokens + {n_new} new tokens exceeds {max_ctx} positions")
         with lock:
-            dist.broadcast_object_list([(ids, n_new)], src=0, group=ctl)
+            served[0] += 1
+            seed = cfg["GP_SAMPLE_SEED"] + served[0] - 1 if sampled else None
+            dist.broadcast_object_list([(ids, n_new, seed)], src=0, group=ctl)
             try:
-                out = step(ids, n_new)
+                out = step(ids, n_new, seed)
             except Exception as ex:
                 raise HTTPException(status_code=500, detail=str(ex))
         return {"generated": tokenizer.decode(out[0].tolist(), skip_special_tokens=True)}

@@ -62,9 +62,12 @@ def test_two_stages_in_one_process():
     assert torch.equal(got, want)
 
 
-def test_pipeline_pod_serves_generate():
+@pytest.mark.parametrize("sampling", ["greedy", "reference"])
+def test_pipeline_pod_serves_generate(sampling):
     """The N-GPU pod of k8s/pipeline-pod.yaml (`torchrun -m llm_sharding_demo_b200.pod`): /healthz turns ready, and
-    /generate returns the text a single-GPU engine produces for the same prompt and weights."""
+    /generate returns the text a single-GPU engine produces for the same prompt and weights - greedy, and with the
+    reference's sampler (GP_SAMPLING=reference: drawn inside the last stage's kernel, seed GP_SAMPLE_SEED + request
+    number, KV slot 0 - the draw a single-stage engine makes with the same seed)."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import signal
@@ -73,10 +76,12 @@ def test_pipeline_pod_serves_generate():
     import llm_sharding_demo_b200 as L
     from llm_sharding_demo_b200.server import ByteTokenizer
     port = 5057
+    port += sampling == "reference"
     env = dict(os.environ, MODEL_ID="gpt2", GP_RANDOM_INIT="1", GP_SEED="3", SHARD_PORT=str(port), GP_MAX_CTX="96",
+               GP_SAMPLING=sampling, GP_SAMPLE_SEED="41",
                PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29688", "-m", "llm_sharding_demo_b200.pod"]
+           "--master-port", str(29688 + (sampling == "reference")), "-m", "llm_sharding_demo_b200.pod"]
     proc = subprocess.Popen(cmd, env=env, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, start_new_session=True)
     try:
         ready = False
@@ -95,6 +100,8 @@ def test_pipeline_pod_serves_generate():
         dims = L.PRESETS["gpt2"]
         eng = L.StageEngine(dims, dtype=L.GP_BF16, max_batch=1, max_ctx=96)
         eng.load_weights(L.init_weights(dims, 3, "hf"))
+        if sampling == "reference":
+            eng.set_sampler(0.6, 40, seed=41)          # first request of the pod: GP_SAMPLE_SEED + 0
         tok = ByteTokenizer()
         want = eng.generate(torch.tensor([tok.encode("Hi, ")], dtype=torch.int32), 12)
         assert r.json()["generated"] == tok.decode(want[0].tolist())
