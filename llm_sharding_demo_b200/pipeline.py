@@ -111,6 +111,9 @@ class PipelineRunner:
         else:
             self.stages = balanced_split(dims, world) if split == "balanced" else split_layers(dims.n_layer, world)
         b, e, begin_half, end_half = stage_flags(*self.stages[rank])
+        if any(x != int(x) for be in self.stages for x in be) and dtype != GP_BF16 and transport == "p2p" and world > 1:
+            raise ValueError("stage boundaries inside a block need bf16 storage with the device-side transport (the fp32 "
+                             "persistent kernel runs whole blocks only); use transport='nccl' or a block-granular split")
         self.first, self.last = rank == 0, rank == world - 1
         self.engine = StageEngine(dims, b, e, has_embed=self.first, has_head=self.last, dtype=dtype,
                                   max_batch=batch_per_stream * self.n_streams, max_ctx=max_ctx,
